@@ -1,0 +1,255 @@
+/*
+ * tsdf_b200.h — C ABI of the B200-native TSDF volumetric fusion engine.
+ *
+ * This is the drop-in boundary for semantic-slam's TSDF integration hot path.
+ * Every entry point is `extern "C"`, takes plain pointers and sizes, returns an
+ * `int` status (0 = TSDF_OK) and never throws, exits or resets the device.
+ *
+ * Reference interfaces replaced (paths relative to the reference tree):
+ *   class TSDF          include/tsdf.hpp:22-98      (ctor src/tsdf.cu:62-96,
+ *                        Integrate :135-168, dtor/readback :98-133,
+ *                        SaveVoxelGrid2SurfacePointCloud :170-218)
+ *   class TSDFfusion    include/TSDFfusion.hpp:25-65 (src/TSDFfusion.cpp:74-105 ->
+ *                        src/TSDFfusion.py.in:21-53 -> third-party fusion.TSDFVolume)
+ *   Object::Object      src/Object.cpp:23-49  (per-instance base pose + origin)
+ *   Engine::Run         src/Engine.cpp:192-193 (per-instance masked depth)
+ *
+ * Conventions:
+ *   depth  : fp32 metres, row-major H x W, 0 (or <0, or > max_depth) = invalid
+ *   rgb    : 8-bit x 3 interleaved, row-major H x W x 3, channel order "as given";
+ *            folded as c2*65536 + c1*256 + c0 (src/TSDFfusion.py.in:43 -> upstream)
+ *   poses  : row-major 4x4 camera-to-world (Twc = KF->GetPoseInverse(),
+ *            src/Object.cpp:23,162)
+ *   K      : row-major 3x3, only [0],[2],[4],[5] are used (src/tsdf.cu:41-42)
+ *
+ * Threading: a handle is single-writer; different handles may be driven from
+ * different host threads (each owns its non-default stream).
+ * Pointers passed to *_async calls are borrowed until tsdf_sync() unless the
+ * call documents a copy.  Host pointers may be pageable or pinned; device
+ * pointers (cudaMalloc) are accepted wherever a frame is taken and skip the
+ * upload.
+ */
+#ifndef TSDF_B200_H
+#define TSDF_B200_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define TSDF_B200_VERSION 100 /* 0.1.0 */
+
+/* ---- status codes ------------------------------------------------------ */
+enum {
+  TSDF_OK = 0,
+  TSDF_E_INVALID = 1,    /* bad argument / config                           */
+  TSDF_E_CUDA = 2,       /* CUDA runtime error (text in tsdf_last_error())  */
+  TSDF_E_NOMEM = 3,      /* host or device allocation failed                */
+  TSDF_E_CAPACITY = 4,   /* caller output buffer too small (count returned) */
+  TSDF_E_IO = 5,         /* file open/read/write failed                     */
+  TSDF_E_NCCL = 6,       /* NCCL missing or returned an error               */
+  TSDF_E_SINGULAR = 7,   /* base2world not invertible (src/tsdf.cu:394-395) */
+  TSDF_E_NODEVICE = 8    /* no CUDA device: there is NO CPU fallback        */
+};
+
+/* ---- semantics / layout ------------------------------------------------ */
+/* TSDF_SEM_TSDFCU  : exactly src/tsdf.cu:15-60 — depth only, weight += 1,
+ *                    skip diff <= -trunc, linear index z*Dy*Dx + y*Dx + x
+ *                    (x fastest), extraction/points in the BASE frame.
+ * TSDF_SEM_FUSIONPY: the TSDFfusion plugin surface (src/TSDFfusion.py.in:43):
+ *                    colour + obs_weight, skip diff < -trunc, linear index
+ *                    x*Dy*Dz + y*Dz + z (z fastest, numpy C order of
+ *                    [Dx,Dy,Dz]); volume lives in the world frame.         */
+enum { TSDF_SEM_TSDFCU = 0, TSDF_SEM_FUSIONPY = 1 };
+
+/* Extraction predicate (K5):
+ * TSDF_PRED_NONZERO : fabs(tsdf) != 0 && weight > weight_thresh  (src/tsdf.cu:179,198)
+ * TSDF_PRED_ABS_LT  : fabs(tsdf) <  tsdf_thresh && weight > weight_thresh
+ *                     (Zeng's original, src/obselete/tsdf.cpp:16,33)       */
+enum { TSDF_PRED_NONZERO = 0, TSDF_PRED_ABS_LT = 1 };
+
+/* Raw depth sample formats accepted by tsdf_integrate_raw. */
+enum { TSDF_DEPTH_F32 = 0, TSDF_DEPTH_U16 = 1 };
+
+typedef struct tsdf_vol tsdf_vol;     /* one volume (or one z-slab of it) on one GPU */
+typedef struct tsdf_comm tsdf_comm;   /* one NCCL rank                              */
+typedef struct tsdf_batch tsdf_batch; /* N per-instance volumes, one launch          */
+
+typedef struct tsdf_config {
+  int32_t dim_x, dim_y, dim_z; /* GLOBAL grid dims (include/tsdf.hpp:65-67: 200^3)   */
+  float voxel_size;            /* include/tsdf.hpp:63: 0.004                         */
+  float trunc_margin;          /* include/tsdf.hpp:64: 5*voxel_size                  */
+  float origin[3];             /* grid origin in the base frame (src/tsdf.cu:66-68)  */
+  float base2world[16];        /* row-major; identity => volume in the world frame   */
+  int32_t im_h, im_w;          /* frame shape (ctor h,w — src/tsdf.cu:62-63)         */
+  float K[9];                  /* include/tsdf.hpp:96 (TUM3)                         */
+  float max_depth;             /* src/tsdf.cu:46: 6.0; +inf disables                 */
+  int32_t semantics;           /* TSDF_SEM_*                                         */
+  int32_t with_color;          /* allocate + integrate the packed-RGB array          */
+  int32_t device;              /* CUDA device ordinal                                */
+  int32_t z_begin, z_end;      /* slab [z_begin,z_end) owned by this handle;
+                                  0,0 => whole grid                                  */
+  int32_t id;                  /* mnId: names tsdf<id>.ply / tsdf<id>.bin            */
+  int32_t reserved[7];
+} tsdf_config;
+
+typedef struct tsdf_stats {
+  int64_t voxels_visited;  /* voxels evaluated by the last integrate on this handle  */
+  int64_t voxels_written;  /* voxels whose weight/tsdf were updated (exact)          */
+  int64_t frames;          /* frames integrated since create/reset                   */
+  float last_kernel_ms;    /* CUDA-event time of the last integrate launch(es)       */
+  float last_upload_ms;    /* CUDA-event time of the last frame upload + prep        */
+  int64_t bytes_algorithmic; /* 24|16 B * written + frame bytes          */
+} tsdf_stats;
+
+/* ---- library ----------------------------------------------------------- */
+int tsdf_version(void);
+const char* tsdf_last_error(void);       /* thread-local text of the last failure */
+int tsdf_device_count(int* n);           /* TSDF_E_NODEVICE when none             */
+
+/* ---- configuration ----------------------------------------------------- */
+/* Defaults = the reference's in-class initialisers (include/tsdf.hpp:63-67,96):
+ * 200^3, 4 mm, trunc 5*vs, TUM3 K, 480x640, max_depth 6, identity base pose. */
+void tsdf_config_default(tsdf_config* cfg);
+/* fusion.py rule (src/TSDFfusion.py.in:23-29 -> upstream ctor):
+ * dims = ceil((max-min)/voxel_size) in float64, origin = mins (as fp32),
+ * trunc = 5*voxel_size, FUSIONPY semantics, colour on, max_depth = +inf.
+ * vol_bnds is row-major 3x2 {xmin,xmax, ymin,ymax, zmin,zmax}.              */
+int tsdf_config_from_bounds(const double vol_bnds[6], double voxel_size, tsdf_config* cfg);
+
+/* ---- lifecycle (K3, K4) -------------------------------------------------- */
+int tsdf_create(const tsdf_config* cfg, tsdf_vol** out);
+int tsdf_destroy(tsdf_vol* v);           /* frees everything the handle owns */
+int tsdf_reset(tsdf_vol* v);             /* tsdf=1, weight=0, colour=0 (src/tsdf.cu:79-81) */
+int tsdf_get_config(const tsdf_vol* v, tsdf_config* cfg);
+
+/* ---- integration (K1, K2, K8, K10) ---------------------------------------- */
+/* One frame.  depth: H*W fp32; rgb: H*W*3 u8 or NULL; K: 9 floats or NULL
+ * (=> config K); T_wc: 16 floats; obs_weight: 1.0f for the TSDF class.
+ * cam2base = inv(base2world) * T_wc is composed on the host exactly as
+ * src/tsdf.cu:142,253-403 does (skipped when base2world is the identity).
+ * tsdf_integrate = tsdf_integrate_async + tsdf_sync.                       */
+int tsdf_integrate(tsdf_vol* v, const float* depth, const uint8_t* rgb,
+                   const float* K, const float* T_wc, float obs_weight);
+int tsdf_integrate_async(tsdf_vol* v, const float* depth, const uint8_t* rgb,
+                         const float* K, const float* T_wc, float obs_weight);
+/* Raw sensor samples: depth_fmt TSDF_DEPTH_U16 applies d = (float)u16 * scale
+ * on the device (examples/label_instance_rgbd.cpp:99-100: scale = 1.0f/5000.0f);
+ * subsample_cols/rows > 1 keep only pixels with col%sc==0 && row%sr==0 and zero
+ * the rest (examples/label_instance_rgbd.cpp:89-97: 3,4).                    */
+int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int depth_fmt, float depth_scale,
+                             int subsample_cols, int subsample_rows, const uint8_t* rgb,
+                             const float* K, const float* T_wc, float obs_weight);
+/* k frames fused into ONE pass over the volume: voxel state is
+ * read once, updated k times in frame order in registers, written once.
+ * Results are bit-identical to k successive tsdf_integrate calls.
+ * depth: k*H*W, rgb: k*H*W*3 or NULL, K: 9 or NULL, T_wc: k*16.             */
+int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth, const uint8_t* rgb,
+                               const float* K, const float* T_wc, float obs_weight);
+int tsdf_sync(tsdf_vol* v);
+int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s); /* syncs the handle's stream */
+
+/* ---- readback (K4, K5, K7) ------------------------------------------------ */
+/* Copies this handle's slab to host arrays in the semantics' reference order.
+ * global_layout=0: pointers address a dense LOCAL slab array;
+ * global_layout=1: pointers address the GLOBAL Dx*Dy*Dz arrays and the slab
+ * is scattered into place (lets G handles fill one host mirror).
+ * Any pointer may be NULL.                                                  */
+int tsdf_download(tsdf_vol* v, float* tsdf, float* weight, float* color, int global_layout);
+int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, const float* color,
+                int global_layout);
+/* Surface/point extraction on the device (warp-ballot compaction), ascending
+ * reference linear index.  xyz: 3*cap floats (origin + (float)i*vs,
+ * src/tsdf.cu:206-208); rgb: 3*cap u8 {c0,c1,c2} or NULL; idx: cap int64
+ * GLOBAL reference linear indices or NULL.  *count receives the number of
+ * matching voxels even when cap is too small (then TSDF_E_CAPACITY and
+ * nothing is written).  Call with cap=0 to size the buffers.                */
+int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
+                        float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap, int64_t* count);
+/* Same, outputs stay on the device (pointers are device pointers).          */
+int tsdf_extract_points_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
+                               float* d_xyz, uint8_t* d_rgb, int64_t* d_idx, int64_t cap,
+                               int64_t* count);
+/* Byte-compatible writers: PLY header src/tsdf.cu:186-192 + float x,y,z;
+ * BIN = 8-float header + tsdf array (src/tsdf.cu:116-132).  Whole-grid
+ * handles only.  tsdf_load_bin restores tsdf (weights are not in the file). */
+int tsdf_save_ply(tsdf_vol* v, const char* path, int predicate, float tsdf_thresh,
+                  float weight_thresh);
+int tsdf_save_bin(tsdf_vol* v, const char* path);
+int tsdf_load_bin(tsdf_vol* v, const char* path);
+
+/* ---- per-instance setup on the device (K9, K11) ------------- */
+/* origin[k] = min over pixels with mask!=0 && depth>0 of the back-projected
+ * x=(c-cx)*z*(1/fx), y=(r-cy)*z*(1/fy), z  (src/Object.cpp:37-49), initial 1000.
+ * mask: H*W u8 (0 / non-zero) or NULL (= all ones).  depth/mask may be host or
+ * device pointers.                                                          */
+int tsdf_instance_origin(int device, const float* depth, const uint8_t* mask, int im_h, int im_w,
+                         const float K[9], float origin_out[3]);
+
+/* ---- batched per-instance volumes (config 5) ------------------------------ */
+/* n volumes that share one frame per integrate call; each has its own base
+ * pose, origin and 8-bit mask (masked depth = depth * (mask/255),
+ * src/Engine.cpp:192-193).  One launch covers all active instances.         */
+int tsdf_batch_create(const tsdf_config* cfgs, int n, tsdf_batch** out);
+int tsdf_batch_destroy(tsdf_batch* b);
+int tsdf_batch_size(const tsdf_batch* b, int* n);
+/* active: n_active instance ids; masks: n_active * H*W u8 (host or device).  */
+int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
+                               const int32_t* active, int n_active, const uint8_t* masks,
+                               const float* K, const float* T_wc, float obs_weight);
+int tsdf_batch_sync(tsdf_batch* b);
+int tsdf_batch_get_stats(tsdf_batch* b, tsdf_stats* s);
+int tsdf_batch_download(tsdf_batch* b, int instance, float* tsdf, float* weight, float* color);
+int tsdf_batch_extract_points(tsdf_batch* b, int instance, int predicate, float tsdf_thresh,
+                              float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx,
+                              int64_t cap, int64_t* count);
+
+/* ---- multi-GPU: z-slabs + NCCL -------------------------------- */
+/* One tsdf_comm per rank (one process per GPU, or G handles in one process).
+ * uid: 128 bytes from tsdf_comm_unique_id on one rank, shipped to the others
+ * by the caller (torch.distributed store, MPI, a file...).                  */
+int tsdf_comm_unique_id(void* uid128);
+int tsdf_comm_create(const void* uid128, int nranks, int rank, int device, tsdf_comm** out);
+int tsdf_comm_destroy(tsdf_comm* c);
+/* Slab of `rank` out of `nranks` for a grid with dim_z slices: contiguous,
+ * sizes differ by at most one 4-slice group (keeps 128-bit alignment).      */
+void tsdf_slab_range(int dim_z, int nranks, int rank, int* z_begin, int* z_end);
+/* Collective over all ranks of `c`: the root's frame (depth/rgb/K/T_wc/
+ * obs_weight; ignored elsewhere, may be NULL) is broadcast over NVLink as ONE
+ * packed buffer, then every rank integrates its own slab.                   */
+int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float* depth,
+                               const uint8_t* rgb, const float* K, const float* T_wc,
+                               float obs_weight);
+/* Collective: every rank extracts its slab; the root receives all points,
+ * merged to ascending GLOBAL reference index.  Non-root ranks pass NULL/0
+ * buffers and get their LOCAL count in *count; the root gets the total.     */
+int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predicate, float tsdf_thresh,
+                       float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap,
+                       int64_t* count);
+
+/* ---- pinned host memory helpers (frame upload path) ----------------------- */
+int tsdf_host_alloc(void** p, size_t bytes); /* cudaHostAlloc: uploads skip the staging copy */
+int tsdf_host_free(void* p);
+int tsdf_device_alloc(int device, void** p, size_t bytes);
+int tsdf_device_free(int device, void* p);
+int tsdf_memcpy_h2d(int device, void* dst, const void* src, size_t bytes);
+int tsdf_memcpy_d2h(int device, void* dst, const void* src, size_t bytes);
+
+/* ---- host-side helpers restated from the reference (K6) -------------------- */
+void tsdf_multiply_matrix(const float m1[16], const float m2[16], float out[16]); /* src/tsdf.cu:253-273 */
+int tsdf_invert_matrix(const float m[16], float out[16]); /* src/tsdf.cu:276-403; TSDF_E_SINGULAR */
+
+/* ---- measurement hooks (used by bench.py; no effect on results) ------------ */
+/* Times `iters` back-to-back launches of the integrate kernel on the frame
+ * last uploaded to the handle (volume state keeps evolving) with CUDA events
+ * on the handle's stream; returns average ms per launch.                    */
+int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms);
+/* Selects a kernel variant for A/B evidence (0 = default).                  */
+int tsdf_set_variant(tsdf_vol* v, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TSDF_B200_H */

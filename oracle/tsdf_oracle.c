@@ -1,0 +1,318 @@
+/*
+ * tsdf_oracle.c — CPU restatement of the reference's TSDF hot path.
+ *
+ * THIS IS TEST INFRASTRUCTURE, NOT PRODUCT CODE.  Only tests/, __graft_entry__.smoke()
+ * and bench.py's cpu_baseline / --impl reference legs may load it.  The product
+ * (semantic-slam_b200/csrc) never links, calls or falls back to anything here.
+ *
+ * Parity status
+ *   SEM_TSDFCU  : restates first-party src/tsdf.cu:15-60 (update), :62-81 (init),
+ *                 :135-142 + :253-403 (pose composition), :170-218 (extraction),
+ *                 :116-132 (.bin).  The reference has NO tests/golden vectors for this
+ *                 path; the restatement is pinned against the reference's own
+ *                 source lines compiled as CPU C++ in oracle/_ref (see build_ref.sh,
+ *                 tests/test_oracle_vs_ref.py) and against tests/golden/ vectors made
+ *                 from that build.
+ *   SEM_FUSIONPY: colour + obs_weight arithmetic of the un-vendored third-party
+ *                 andyzeng/tsdf-fusion-python (no pinned version; call site
+ *                 src/TSDFfusion.py.in:43).  Its source is not available offline:
+ *                 PARITY UNPINNED for the colour/obs_weight extension.
+ *
+ * Arithmetic discipline: every operation is one IEEE-754 fp32 round-to-nearest-even op in
+ * the source order of the reference, with NO fused multiply-add.  Build with
+ * -ffp-contract=off (the Makefile does) — SURVEY §7.2(1), Appendix A.
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define SEM_TSDFCU 0
+#define SEM_FUSIONPY 1
+#define PRED_NONZERO 0
+#define PRED_ABS_LT 1
+
+typedef struct {
+  int32_t dim_x, dim_y, dim_z; /* global dims */
+  float voxel_size, trunc_margin;
+  float origin[3];
+  int32_t im_h, im_w;
+  float K[9];
+  float max_depth;
+  int32_t semantics;
+  int32_t z_begin, z_end; /* slab evaluated by this call; arrays are LOCAL to the slab */
+} oracle_params;
+
+/* 4x4 row-major product, each output a left-to-right 4-term fp32 sum.
+ * Follows src/tsdf.cu:253-273. */
+void oracle_multiply_matrix(const float* a, const float* b, float* o) {
+  for (int r = 0; r < 4; ++r)
+    for (int c = 0; c < 4; ++c) {
+      float s = a[r * 4 + 0] * b[0 * 4 + c];
+      s = s + a[r * 4 + 1] * b[1 * 4 + c];
+      s = s + a[r * 4 + 2] * b[2 * 4 + c];
+      s = s + a[r * 4 + 3] * b[3 * 4 + c];
+      o[r * 4 + c] = s;
+    }
+}
+
+/* 3x3 minor expansion helper: the reference spells every cofactor as a signed sum of six
+ * triple products evaluated left to right (src/tsdf.cu:280-390).  A triple product
+ * p*q*r is (p*q)*r; the six terms are accumulated in source order. */
+static float six(float a0, float a1, float a2, float b0, float b1, float b2, float c0, float c1,
+                 float c2, float d0, float d1, float d2, float e0, float e1, float e2, float f0,
+                 float f1, float f2, const int* sgn) {
+  /* sgn[i] in {+1,-1}; the first term's sign is applied to its first factor (unary minus
+   * on m[k] is exact), later terms are added or subtracted. */
+  float t = (sgn[0] > 0 ? a0 : -a0) * a1 * a2;
+  float u;
+  u = b0 * b1 * b2; t = sgn[1] > 0 ? t + u : t - u;
+  u = c0 * c1 * c2; t = sgn[2] > 0 ? t + u : t - u;
+  u = d0 * d1 * d2; t = sgn[3] > 0 ? t + u : t - u;
+  u = e0 * e1 * e2; t = sgn[4] > 0 ? t + u : t - u;
+  u = f0 * f1 * f2; t = sgn[5] > 0 ? t + u : t - u;
+  return t;
+}
+
+/* Cofactor inverse; det reciprocal in double then narrowed to float
+ * (src/tsdf.cu:392-400: `det = 1.0 / det`).  Returns 0 when singular (:394-395). */
+int oracle_invert_matrix(const float* m, float* out) {
+  static const int PMMPPM[6] = {+1, -1, -1, +1, +1, -1};
+  static const int MPPMMP[6] = {-1, +1, +1, -1, -1, +1};
+  float inv[16];
+#define S6(sg, a, b, c, d, e, f, g, h, i, j, k, l, mm, n, o, p, q, r) \
+  six(m[a], m[b], m[c], m[d], m[e], m[f], m[g], m[h], m[i], m[j], m[k], m[l], m[mm], m[n], m[o], \
+      m[p], m[q], m[r], sg)
+  inv[0] = S6(PMMPPM, 5, 10, 15, 5, 11, 14, 9, 6, 15, 9, 7, 14, 13, 6, 11, 13, 7, 10);
+  inv[4] = S6(MPPMMP, 4, 10, 15, 4, 11, 14, 8, 6, 15, 8, 7, 14, 12, 6, 11, 12, 7, 10);
+  inv[8] = S6(PMMPPM, 4, 9, 15, 4, 11, 13, 8, 5, 15, 8, 7, 13, 12, 5, 11, 12, 7, 9);
+  inv[12] = S6(MPPMMP, 4, 9, 14, 4, 10, 13, 8, 5, 14, 8, 6, 13, 12, 5, 10, 12, 6, 9);
+  inv[1] = S6(MPPMMP, 1, 10, 15, 1, 11, 14, 9, 2, 15, 9, 3, 14, 13, 2, 11, 13, 3, 10);
+  inv[5] = S6(PMMPPM, 0, 10, 15, 0, 11, 14, 8, 2, 15, 8, 3, 14, 12, 2, 11, 12, 3, 10);
+  inv[9] = S6(MPPMMP, 0, 9, 15, 0, 11, 13, 8, 1, 15, 8, 3, 13, 12, 1, 11, 12, 3, 9);
+  inv[13] = S6(PMMPPM, 0, 9, 14, 0, 10, 13, 8, 1, 14, 8, 2, 13, 12, 1, 10, 12, 2, 9);
+  inv[2] = S6(PMMPPM, 1, 6, 15, 1, 7, 14, 5, 2, 15, 5, 3, 14, 13, 2, 7, 13, 3, 6);
+  inv[6] = S6(MPPMMP, 0, 6, 15, 0, 7, 14, 4, 2, 15, 4, 3, 14, 12, 2, 7, 12, 3, 6);
+  inv[10] = S6(PMMPPM, 0, 5, 15, 0, 7, 13, 4, 1, 15, 4, 3, 13, 12, 1, 7, 12, 3, 5);
+  inv[14] = S6(MPPMMP, 0, 5, 14, 0, 6, 13, 4, 1, 14, 4, 2, 13, 12, 1, 6, 12, 2, 5);
+  inv[3] = S6(MPPMMP, 1, 6, 11, 1, 7, 10, 5, 2, 11, 5, 3, 10, 9, 2, 7, 9, 3, 6);
+  inv[7] = S6(PMMPPM, 0, 6, 11, 0, 7, 10, 4, 2, 11, 4, 3, 10, 8, 2, 7, 8, 3, 6);
+  inv[11] = S6(MPPMMP, 0, 5, 11, 0, 7, 9, 4, 1, 11, 4, 3, 9, 8, 1, 7, 8, 3, 5);
+  inv[15] = S6(PMMPPM, 0, 5, 10, 0, 6, 9, 4, 1, 10, 4, 2, 9, 8, 1, 6, 8, 2, 5);
+#undef S6
+  float det = m[0] * inv[0];
+  det = det + m[1] * inv[4];
+  det = det + m[2] * inv[8];
+  det = det + m[3] * inv[12];
+  if (det == 0) return 0;
+  det = (float)(1.0 / (double)det);
+  for (int i = 0; i < 16; ++i) out[i] = inv[i] * det;
+  return 1;
+}
+
+/* cam2base = inv(base2world) * cam2world — src/tsdf.cu:74,142. */
+int oracle_compose_cam2base(const float* base2world, const float* cam2world, float* cam2base) {
+  float binv[16];
+  if (!oracle_invert_matrix(base2world, binv)) return 0;
+  oracle_multiply_matrix(binv, cam2world, cam2base);
+  return 1;
+}
+
+/* Linear index of voxel (x,y,zl) inside a LOCAL slab array with dz_local slices, in the
+ * semantics' reference order: src/tsdf.cu:52 (x fastest) or numpy C order of [Dx,Dy,Dz]
+ * (z fastest) for the plugin surface. */
+static inline int64_t lin_index(int sem, int x, int y, int zl, int dx, int dy, int dzl) {
+  if (sem == SEM_TSDFCU) return ((int64_t)zl * dy + y) * dx + x;
+  return ((int64_t)x * dy + y) * dzl + zl;
+}
+
+/* (int)roundf(u) with the out-of-range cast made explicit: any u whose rounded value is
+ * outside [0,n) is "outside", whatever the float->int conversion would do (x86 gives
+ * INT_MIN, PTX saturates; both are out of bounds) — SURVEY §7.2(1). */
+static inline int round_pix(float u, int n, int* ok) {
+  float r = roundf(u); /* half away from zero, as CUDA roundf (src/tsdf.cu:41-42) */
+  if (!(r >= 0.0f && r < (float)n)) { *ok = 0; return 0; }
+  *ok = 1;
+  return (int)r;
+}
+
+/* One frame into one slab.  Follows src/tsdf.cu:21-59 line by line (Appendix A of
+ * SURVEY.md); SEM_FUSIONPY adds obs_weight, `<` truncation test and the colour average.
+ * depth: H*W fp32.  color_packed: H*W fp32 = c2*65536+c1*256+c0 (may be NULL => no colour).
+ * cam2base: 16 floats.  tsdf/weight/color: LOCAL slab arrays.
+ * Returns the number of voxels written. */
+int64_t oracle_integrate(const oracle_params* p, const float* cam2base, const float* depth,
+                         const float* color_packed, float obs_weight, float* tsdf, float* weight,
+                         float* color) {
+  const int dx = p->dim_x, dy = p->dim_y;
+  const int z0 = p->z_begin, z1 = p->z_end, dzl = z1 - z0;
+  const int W = p->im_w, H = p->im_h;
+  const float vs = p->voxel_size, trunc = p->trunc_margin;
+  const float* c = cam2base;
+  const float* K = p->K;
+  const int sem = p->semantics;
+  int64_t written = 0;
+#pragma omp parallel for collapse(2) schedule(static) reduction(+ : written)
+  for (int z = z0; z < z1; ++z)
+    for (int y = 0; y < dy; ++y)
+      for (int x = 0; x < dx; ++x) {
+        float bx = p->origin[0] + (float)x * vs; /* :27 */
+        float by = p->origin[1] + (float)y * vs; /* :28 */
+        float bz = p->origin[2] + (float)z * vs; /* :29 (global z) */
+        float t0 = bx - c[3], t1 = by - c[7], t2 = bz - c[11]; /* :33-35 */
+        float cx_ = c[0] * t0 + c[4] * t1; cx_ = cx_ + c[8] * t2;  /* :36 */
+        float cy_ = c[1] * t0 + c[5] * t1; cy_ = cy_ + c[9] * t2;  /* :37 */
+        float cz_ = c[2] * t0 + c[6] * t1; cz_ = cz_ + c[10] * t2; /* :38 */
+        if (cz_ <= 0) continue; /* :39 */
+        int okx, oky;
+        int px = round_pix(K[0] * (cx_ / cz_) + K[2], W, &okx); /* :41 */
+        int py = round_pix(K[4] * (cy_ / cz_) + K[5], H, &oky); /* :42 */
+        if (!okx || !oky) continue; /* :43 */
+        float d = depth[(int64_t)py * W + px]; /* :45 */
+        if (d <= 0 || d > p->max_depth) continue; /* :46 */
+        float diff = d - cz_; /* :48 */
+        if (sem == SEM_TSDFCU ? (diff <= -trunc) : (diff < -trunc)) continue; /* :49 */
+        int64_t idx = lin_index(sem, x, y, z - z0, dx, dy, dzl); /* :52 */
+        float dist = fminf(1.0f, diff / trunc); /* :53 */
+        float w0 = weight[idx]; /* :54 */
+        float w1 = w0 + obs_weight; /* :55 (1.0f in the TSDF class) */
+        weight[idx] = w1; /* :56 */
+        tsdf[idx] = (tsdf[idx] * w0 + dist) / w1; /* :57 */
+        ++written;
+        if (color && color_packed) {
+          /* upstream colour average on float-packed B*65536+G*256+R */
+          float oc = color[idx];
+          float ob = floorf(oc / 65536.0f);
+          float og = floorf((oc - ob * 65536.0f) / 256.0f);
+          float orr = oc - ob * 65536.0f - og * 256.0f;
+          float nc = color_packed[(int64_t)py * W + px];
+          float nb = floorf(nc / 65536.0f);
+          float ng = floorf((nc - nb * 65536.0f) / 256.0f);
+          float nr = nc - nb * 65536.0f - ng * 256.0f;
+          nb = fminf(roundf((ob * w0 + nb) / w1), 255.0f);
+          ng = fminf(roundf((og * w0 + ng) / w1), 255.0f);
+          nr = fminf(roundf((orr * w0 + nr) / w1), 255.0f);
+          color[idx] = nb * 65536.0f + ng * 256.0f + nr;
+        }
+      }
+  return written;
+}
+
+/* Fold H*W*3 u8 into the packed fp32 image: floor(c2*65536 + c1*256 + c0). */
+void oracle_pack_color(const uint8_t* rgb, int64_t n_pix, float* out) {
+  for (int64_t i = 0; i < n_pix; ++i)
+    out[i] = floorf((float)rgb[3 * i + 2] * 65536.0f + (float)rgb[3 * i + 1] * 256.0f +
+                    (float)rgb[3 * i + 0]);
+}
+
+/* Init: tsdf = 1, weight = 0 (src/tsdf.cu:79-81), colour = 0. */
+void oracle_init(int64_t n, float* tsdf, float* weight, float* color) {
+  for (int64_t i = 0; i < n; ++i) tsdf[i] = 1.0f;
+  memset(weight, 0, sizeof(float) * (size_t)n);
+  if (color) memset(color, 0, sizeof(float) * (size_t)n);
+}
+
+static inline int keep(int pred, float t, float w, float tsdf_thresh, float weight_thresh) {
+  if (pred == PRED_NONZERO) return fabsf(t) != 0.0f && w > weight_thresh; /* src/tsdf.cu:179,198 */
+  return fabsf(t) < tsdf_thresh && w > weight_thresh; /* src/obselete/tsdf.cpp:16,33 */
+}
+
+/* Extraction over a LOCAL slab, ascending local linear index (src/tsdf.cu:178-216).
+ * Emits xyz = origin + (float)i*vs (:206-208) with the GLOBAL z index, the GLOBAL
+ * reference linear index, and optionally rgb {c0,c1,c2}.  Returns the count; writes at
+ * most cap entries. */
+int64_t oracle_extract(const oracle_params* p, const float* tsdf, const float* weight,
+                       const float* color, int pred, float tsdf_thresh, float weight_thresh,
+                       float* xyz, uint8_t* rgb, int64_t* idx_out, int64_t cap) {
+  const int dx = p->dim_x, dy = p->dim_y, dz = p->dim_z;
+  const int z0 = p->z_begin, dzl = p->z_end - p->z_begin;
+  const int64_t n = (int64_t)dx * dy * dzl;
+  int64_t cnt = 0;
+  for (int64_t i = 0; i < n; ++i) {
+    if (!keep(pred, tsdf[i], weight[i], tsdf_thresh, weight_thresh)) continue;
+    if (cnt < cap) {
+      int x, y, zl;
+      if (p->semantics == SEM_TSDFCU) { /* :201-203 */
+        zl = (int)(i / ((int64_t)dx * dy));
+        y = (int)((i - (int64_t)zl * dx * dy) / dx);
+        x = (int)(i - (int64_t)zl * dx * dy - (int64_t)y * dx);
+      } else {
+        x = (int)(i / ((int64_t)dy * dzl));
+        y = (int)((i - (int64_t)x * dy * dzl) / dzl);
+        zl = (int)(i - (int64_t)x * dy * dzl - (int64_t)y * dzl);
+      }
+      int z = zl + z0;
+      if (xyz) {
+        xyz[3 * cnt + 0] = p->origin[0] + (float)x * p->voxel_size;
+        xyz[3 * cnt + 1] = p->origin[1] + (float)y * p->voxel_size;
+        xyz[3 * cnt + 2] = p->origin[2] + (float)z * p->voxel_size;
+      }
+      if (idx_out)
+        idx_out[cnt] = p->semantics == SEM_TSDFCU ? ((int64_t)z * dy + y) * dx + x
+                                                  : ((int64_t)x * dy + y) * dz + z;
+      if (rgb) {
+        float oc = color ? color[i] : 0.0f;
+        float ob = floorf(oc / 65536.0f);
+        float og = floorf((oc - ob * 65536.0f) / 256.0f);
+        float orr = oc - ob * 65536.0f - og * 256.0f;
+        rgb[3 * cnt + 0] = (uint8_t)orr;
+        rgb[3 * cnt + 1] = (uint8_t)og;
+        rgb[3 * cnt + 2] = (uint8_t)ob;
+      }
+    }
+    ++cnt;
+  }
+  return cnt;
+}
+
+/* Per-instance origin — src/Object.cpp:37-49 (initial 1000, min over depth>0 pixels of
+ * x=(c-cx)*z*(1/fx), y=(r-cy)*z*(1/fy), z).  mask NULL = all pixels; masked depth is
+ * depth*(mask/255) (src/Engine.cpp:192-193); OpenCV's 8-bit Mat/scalar rounds to nearest
+ * (saturate_cast), so mask>=128 -> 1 else 0; Mask-RCNN masks are 0/255 either way. */
+void oracle_instance_origin(const float* depth, const uint8_t* mask, int H, int W, const float* K,
+                            float* origin) {
+  origin[0] = origin[1] = origin[2] = 1000.0f;
+  const float ifx = 1.0f / K[0], ify = 1.0f / K[4];
+  for (int r = 0; r < H; ++r)
+    for (int cc = 0; cc < W; ++cc) {
+      float z = depth[(int64_t)r * W + cc];
+      if (mask) z = z * (mask[(int64_t)r * W + cc] >= 128 ? 1.0f : 0.0f);
+      if (z <= 0.0f) continue;
+      float x = ((float)cc - K[2]) * z * ifx;
+      float y = ((float)r - K[5]) * z * ify;
+      origin[0] = x < origin[0] ? x : origin[0];
+      origin[1] = y < origin[1] ? y : origin[1];
+      origin[2] = z < origin[2] ? z : origin[2];
+    }
+}
+
+/* .bin writer — src/tsdf.cu:116-132: dims as floats, origin, voxel_size, trunc, tsdf. */
+int oracle_save_bin(const char* path, const oracle_params* p, const float* tsdf) {
+  FILE* f = fopen(path, "wb");
+  if (!f) return 0;
+  float h[8] = {(float)p->dim_x, (float)p->dim_y, (float)p->dim_z, p->origin[0],
+                p->origin[1],    p->origin[2],    p->voxel_size,   p->trunc_margin};
+  fwrite(h, sizeof(float), 8, f);
+  fwrite(tsdf, sizeof(float), (size_t)p->dim_x * p->dim_y * p->dim_z, f);
+  fclose(f);
+  return 1;
+}
+
+/* .ply writer — src/tsdf.cu:184-217 (header then float x,y,z per kept voxel). */
+int oracle_save_ply(const char* path, const oracle_params* p, const float* tsdf,
+                    const float* weight, int pred, float tsdf_thresh, float weight_thresh) {
+  int64_t n = oracle_extract(p, tsdf, weight, NULL, pred, tsdf_thresh, weight_thresh, NULL, NULL,
+                             NULL, 0);
+  float* xyz = (float*)malloc(sizeof(float) * 3 * (size_t)(n ? n : 1));
+  if (!xyz) return 0;
+  oracle_extract(p, tsdf, weight, NULL, pred, tsdf_thresh, weight_thresh, xyz, NULL, NULL, n);
+  FILE* fp = fopen(path, "w");
+  if (!fp) { free(xyz); return 0; }
+  fprintf(fp, "ply\nformat binary_little_endian 1.0\nelement vertex %d\n", (int)n);
+  fprintf(fp, "property float x\nproperty float y\nproperty float z\nend_header\n");
+  fwrite(xyz, sizeof(float), 3 * (size_t)n, fp);
+  fclose(fp);
+  free(xyz);
+  return 1;
+}
