@@ -216,9 +216,11 @@ int tsdf_comm_destroy(tsdf_comm* c);
 /* Slab of `rank` out of `nranks` for a grid with dim_z slices: contiguous,
  * sizes differ by at most one 4-slice group (keeps 128-bit alignment).      */
 void tsdf_slab_range(int dim_z, int nranks, int rank, int* z_begin, int* z_end);
-/* Collective over all ranks of `c`: the root's frame (depth/rgb/K/T_wc/
- * obs_weight; ignored elsewhere, may be NULL) is broadcast over NVLink as ONE
- * packed buffer, then every rank integrates its own slab.                   */
+/* Collective over all ranks of `c`: the root's images (depth, rgb; ignored elsewhere, may be
+ * NULL there) are broadcast over NVLink into every rank's frame slot (one grouped NCCL
+ * launch), then every rank integrates its own slab.  The ~100 bytes of metadata (K, T_wc,
+ * obs_weight) travel on the caller's control plane: pass the SAME values on every rank.
+ * Colour is broadcast iff the volume was created with_color (then the root must pass rgb). */
 int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float* depth,
                                const uint8_t* rgb, const float* K, const float* T_wc,
                                float obs_weight);

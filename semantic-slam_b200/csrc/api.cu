@@ -1,0 +1,758 @@
+// api.cu — the C ABI of include/tsdf_b200.h: lifecycle, frame upload path, integrate
+// entry points, readback, file writers, host-side pose helpers (K2-K4, K6-K8, K10).
+// Host code is plain C++ calling the CUDA runtime; there is NO CPU fallback: every entry
+// point that needs a device fails with TSDF_E_NODEVICE / TSDF_E_CUDA when none is present.
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include <algorithm>
+#include <limits>
+
+#include "common.cuh"
+
+// ---- errors ------------------------------------------------------------------------------
+static thread_local char g_err[768] = "";
+void tsdf_set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+extern "C" const char* tsdf_last_error(void) { return g_err; }
+extern "C" int tsdf_version(void) { return TSDF_B200_VERSION; }
+
+extern "C" int tsdf_device_count(int* n) {
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (n) *n = (e == cudaSuccess) ? c : 0;
+  if (e != cudaSuccess || c == 0) {
+    cudaGetLastError();
+    tsdf_set_error("no CUDA device (%s); this library has no CPU fallback",
+                   e == cudaSuccess ? "count=0" : cudaGetErrorString(e));
+    return TSDF_E_NODEVICE;
+  }
+  return TSDF_OK;
+}
+
+// ---- host pose helpers (K6) ----------------------------------------------------------------
+// Restated from the algorithm of reference src/tsdf.cu:253-273 / :276-403 with the same
+// operation order (left-to-right fp32 sums; det reciprocal in double, narrowed to float).
+// This translation unit is compiled with -fmad=false and host code is never contracted.
+extern "C" void tsdf_multiply_matrix(const float a[16], const float b[16], float o[16]) {
+  float t[16];
+  for (int r = 0; r < 4; ++r)
+    for (int c = 0; c < 4; ++c) {
+      volatile float s = a[r * 4 + 0] * b[0 * 4 + c];
+      s = s + a[r * 4 + 1] * b[1 * 4 + c];
+      s = s + a[r * 4 + 2] * b[2 * 4 + c];
+      s = s + a[r * 4 + 3] * b[3 * 4 + c];
+      t[r * 4 + c] = s;
+    }
+  memcpy(o, t, sizeof(t));
+}
+
+namespace {
+// signed sum of six triple products, evaluated in source order
+struct Tri { int a, b, c; };
+float cof(const float* m, bool first_neg, const Tri (&t)[6]) {
+  // sign pattern of the reference: (+ - - + + -) or (- + + - - +)
+  static const int P[6] = {+1, -1, -1, +1, +1, -1};
+  volatile float acc = (first_neg ? -m[t[0].a] : m[t[0].a]) * m[t[0].b] * m[t[0].c];
+  for (int i = 1; i < 6; ++i) {
+    volatile float u = m[t[i].a] * m[t[i].b];
+    u = u * m[t[i].c];
+    int sg = first_neg ? -P[i] : P[i];
+    acc = sg > 0 ? acc + u : acc - u;
+  }
+  return acc;
+}
+}  // namespace
+
+extern "C" int tsdf_invert_matrix(const float m[16], float out[16]) {
+  float inv[16];
+  inv[0]  = cof(m, false, {{5,10,15},{5,11,14},{9,6,15},{9,7,14},{13,6,11},{13,7,10}});
+  inv[4]  = cof(m, true,  {{4,10,15},{4,11,14},{8,6,15},{8,7,14},{12,6,11},{12,7,10}});
+  inv[8]  = cof(m, false, {{4,9,15},{4,11,13},{8,5,15},{8,7,13},{12,5,11},{12,7,9}});
+  inv[12] = cof(m, true,  {{4,9,14},{4,10,13},{8,5,14},{8,6,13},{12,5,10},{12,6,9}});
+  inv[1]  = cof(m, true,  {{1,10,15},{1,11,14},{9,2,15},{9,3,14},{13,2,11},{13,3,10}});
+  inv[5]  = cof(m, false, {{0,10,15},{0,11,14},{8,2,15},{8,3,14},{12,2,11},{12,3,10}});
+  inv[9]  = cof(m, true,  {{0,9,15},{0,11,13},{8,1,15},{8,3,13},{12,1,11},{12,3,9}});
+  inv[13] = cof(m, false, {{0,9,14},{0,10,13},{8,1,14},{8,2,13},{12,1,10},{12,2,9}});
+  inv[2]  = cof(m, false, {{1,6,15},{1,7,14},{5,2,15},{5,3,14},{13,2,7},{13,3,6}});
+  inv[6]  = cof(m, true,  {{0,6,15},{0,7,14},{4,2,15},{4,3,14},{12,2,7},{12,3,6}});
+  inv[10] = cof(m, false, {{0,5,15},{0,7,13},{4,1,15},{4,3,13},{12,1,7},{12,3,5}});
+  inv[14] = cof(m, true,  {{0,5,14},{0,6,13},{4,1,14},{4,2,13},{12,1,6},{12,2,5}});
+  inv[3]  = cof(m, true,  {{1,6,11},{1,7,10},{5,2,11},{5,3,10},{9,2,7},{9,3,6}});
+  inv[7]  = cof(m, false, {{0,6,11},{0,7,10},{4,2,11},{4,3,10},{8,2,7},{8,3,6}});
+  inv[11] = cof(m, true,  {{0,5,11},{0,7,9},{4,1,11},{4,3,9},{8,1,7},{8,3,5}});
+  inv[15] = cof(m, false, {{0,5,10},{0,6,9},{4,1,10},{4,2,9},{8,1,6},{8,2,5}});
+  volatile float det = m[0] * inv[0];
+  det = det + m[1] * inv[4];
+  det = det + m[2] * inv[8];
+  det = det + m[3] * inv[12];
+  if (det == 0) {
+    tsdf_set_error("tsdf_invert_matrix: singular matrix");
+    return TSDF_E_SINGULAR;
+  }
+  float rdet = (float)(1.0 / (double)det);
+  for (int i = 0; i < 16; ++i) out[i] = inv[i] * rdet;
+  return TSDF_OK;
+}
+
+// ---- configuration ---------------------------------------------------------------------------
+extern "C" void tsdf_config_default(tsdf_config* c) {
+  memset(c, 0, sizeof(*c));
+  c->dim_x = c->dim_y = c->dim_z = 200;      // include/tsdf.hpp:65-67
+  c->voxel_size = 0.004f;                    // include/tsdf.hpp:63
+  c->trunc_margin = c->voxel_size * 5;       // include/tsdf.hpp:64
+  for (int i = 0; i < 4; ++i) c->base2world[i * 5] = 1.0f;
+  c->im_h = 480;
+  c->im_w = 640;
+  const float K[9] = {535.4f, 0, 320.1f, 0, 539.2f, 247.6f, 0, 0, 1};  // include/tsdf.hpp:96
+  memcpy(c->K, K, sizeof(K));
+  c->max_depth = 6.0f;                       // src/tsdf.cu:46
+  c->semantics = TSDF_SEM_TSDFCU;
+  c->with_color = 0;
+  c->device = 0;
+}
+
+extern "C" int tsdf_config_from_bounds(const double b[6], double voxel_size, tsdf_config* c) {
+  REQUIRE(b && c && voxel_size > 0, "null argument or voxel_size <= 0");
+  tsdf_config_default(c);
+  int dims[3];
+  for (int k = 0; k < 3; ++k) {
+    double ext = b[2 * k + 1] - b[2 * k];
+    REQUIRE(ext > 0, "empty bounds");
+    dims[k] = (int)ceil(ext / voxel_size);   // upstream: np.ceil((max-min)/voxel_size)
+    c->origin[k] = (float)b[2 * k];          // upstream: vol_bnds[:,0].astype(np.float32)
+  }
+  c->dim_x = dims[0]; c->dim_y = dims[1]; c->dim_z = dims[2];
+  c->voxel_size = (float)voxel_size;
+  c->trunc_margin = (float)(voxel_size * 5.0);  // upstream: trunc = 5*voxel_size (float64), used as fp32
+  c->max_depth = std::numeric_limits<float>::infinity();
+  c->semantics = TSDF_SEM_FUSIONPY;
+  c->with_color = 1;
+  return TSDF_OK;
+}
+
+extern "C" void tsdf_slab_range(int dim_z, int nranks, int rank, int* z_begin, int* z_end) {
+  // split in units of 4 slices so every slab keeps 128-bit alignment on a z-fast layout
+  int groups = (dim_z + 3) / 4;
+  int base = groups / nranks, rem = groups % nranks;
+  int g0 = rank * base + std::min(rank, rem);
+  int g1 = g0 + base + (rank < rem ? 1 : 0);
+  *z_begin = std::min(g0 * 4, dim_z);
+  *z_end = std::min(g1 * 4, dim_z);
+}
+
+// ---- lifecycle (K3, K4) -----------------------------------------------------------------------
+static bool is_identity(const float* m) {
+  for (int i = 0; i < 16; ++i)
+    if (m[i] != ((i % 5 == 0) ? 1.0f : 0.0f)) return false;
+  return true;
+}
+
+static void free_vol(tsdf_vol* v) {
+  if (!v) return;
+  DeviceGuard g(v->cfg.device);
+  if (v->s_compute) cudaStreamSynchronize(v->s_compute);
+  if (v->s_copy) cudaStreamSynchronize(v->s_copy);
+  for (FrameSlot& s : v->slot) {
+    if (s.h_pinned) cudaFreeHost(s.h_pinned);
+    if (s.d_raw) cudaFree(s.d_raw);
+    if (s.d_frame) cudaFree(s.d_frame);
+    if (s.uploaded) cudaEventDestroy(s.uploaded);
+    if (s.consumed) cudaEventDestroy(s.consumed);
+  }
+  cudaFree(v->d_tsdf); cudaFree(v->d_weight); cudaFree(v->d_color);
+  cudaFree(v->d_written); cudaFree(v->d_scratch);
+  if (v->h_written) cudaFreeHost(v->h_written);
+  for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1}) if (e) cudaEventDestroy(e);
+  if (v->s_compute) cudaStreamDestroy(v->s_compute);
+  if (v->s_copy) cudaStreamDestroy(v->s_copy);
+  delete v;
+}
+
+static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
+  v->cfg = *cfg;
+  tsdf_config& c = v->cfg;
+  if (c.z_begin == 0 && c.z_end == 0) c.z_end = c.dim_z;
+  REQUIRE(c.dim_x > 0 && c.dim_y > 0 && c.dim_z > 0, "non-positive grid dims");
+  REQUIRE(c.z_begin >= 0 && c.z_end > c.z_begin && c.z_end <= c.dim_z, "bad slab range");
+  REQUIRE(c.voxel_size > 0 && c.trunc_margin > 0, "voxel_size/trunc_margin must be > 0");
+  REQUIRE(c.im_h > 0 && c.im_w > 0, "bad image shape");
+  REQUIRE(c.semantics == TSDF_SEM_TSDFCU || c.semantics == TSDF_SEM_FUSIONPY, "bad semantics");
+  v->dzl = c.z_end - c.z_begin;
+  v->n_local = (int64_t)c.dim_x * c.dim_y * v->dzl;
+  v->zfast = c.semantics == TSDF_SEM_FUSIONPY;
+  v->identity_base = is_identity(c.base2world);
+  int rc = tsdf_invert_matrix(c.base2world, v->base2world_inv);  // src/tsdf.cu:74 (result checked here)
+  if (rc) return rc;
+  int ndev = 0;
+  rc = tsdf_device_count(&ndev);
+  if (rc) return rc;
+  REQUIRE(c.device >= 0 && c.device < ndev, "device ordinal out of range");
+  DeviceGuard g(c.device);
+  size_t bytes = (size_t)v->n_local * sizeof(float);
+  CU_CHECK(cudaMalloc(&v->d_tsdf, bytes));
+  CU_CHECK(cudaMalloc(&v->d_weight, bytes));
+  if (c.with_color) CU_CHECK(cudaMalloc(&v->d_color, bytes));
+  CU_CHECK(cudaMalloc(&v->d_written, sizeof(unsigned long long)));
+  CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocDefault));
+  *v->h_written = 0;
+  CU_CHECK(cudaStreamCreateWithFlags(&v->s_compute, cudaStreamNonBlocking));
+  CU_CHECK(cudaStreamCreateWithFlags(&v->s_copy, cudaStreamNonBlocking));
+  CU_CHECK(cudaEventCreate(&v->ev_k0));
+  CU_CHECK(cudaEventCreate(&v->ev_k1));
+  CU_CHECK(cudaEventCreate(&v->ev_u0));
+  CU_CHECK(cudaEventCreate(&v->ev_u1));
+  return tsdf_reset(v);
+}
+
+extern "C" int tsdf_create(const tsdf_config* cfg, tsdf_vol** out) {
+  REQUIRE(cfg && out, "null argument");
+  *out = nullptr;
+  tsdf_vol* v = new (std::nothrow) tsdf_vol();
+  if (!v) { tsdf_set_error("tsdf_create: host allocation failed"); return TSDF_E_NOMEM; }
+  int rc = create_impl(cfg, v);
+  if (rc) { free_vol(v); return rc; }
+  *out = v;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_destroy(tsdf_vol* v) {
+  free_vol(v);
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_reset(tsdf_vol* v) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  int rc = launch_fill(v->d_tsdf, 1.0f, v->n_local, v->s_compute);  // src/tsdf.cu:79-80
+  if (rc) return rc;
+  CU_CHECK(cudaMemsetAsync(v->d_weight, 0, (size_t)v->n_local * 4, v->s_compute));  // :81
+  if (v->d_color) CU_CHECK(cudaMemsetAsync(v->d_color, 0, (size_t)v->n_local * 4, v->s_compute));
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  v->frames = 0;
+  v->last_written = 0;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_get_config(const tsdf_vol* v, tsdf_config* cfg) {
+  REQUIRE(v && cfg, "null argument");
+  *cfg = v->cfg;
+  return TSDF_OK;
+}
+
+// ---- frame upload path (K2) ----------------------------------------------------------------
+// Pinned, multi-buffered staging; H2D + prep run on the copy stream and are chained to the
+// compute stream by events, so the upload of frame i+1 overlaps the integrate of frame i.
+// (The reference does two blocking cudaMemcpy from pageable memory per frame per object,
+// src/tsdf.cu:161-162.)
+static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
+  const size_t px = frame_pixels(v->cfg);
+  if (!s.d_raw) {
+    CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
+    CU_CHECK(cudaMalloc(&s.d_frame, px * 8));           // uint2 per pixel (float when no colour)
+    CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
+    CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
+  }
+  return TSDF_OK;
+}
+
+enum PtrKind { PTR_PAGEABLE, PTR_PINNED, PTR_DEVICE };
+static PtrKind ptr_kind(const void* p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return PTR_PAGEABLE; }
+  if (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged) return PTR_DEVICE;
+  if (a.type == cudaMemoryTypeHost) return PTR_PINNED;
+  return PTR_PAGEABLE;
+}
+
+// Moves `bytes` from src (any kind) to where the prep kernel can read it; returns the device
+// pointer to read from.  Pageable data goes through the slot's pinned buffer.
+static int to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
+                     const void** d_out) {
+  PtrKind k = ptr_kind(src);
+  if (k == PTR_DEVICE) { *d_out = src; return TSDF_OK; }
+  char* dst = reinterpret_cast<char*>(s.d_raw) + raw_off;
+  if (k == PTR_PAGEABLE) {
+    if (!s.h_pinned) CU_CHECK(cudaHostAlloc(&s.h_pinned, frame_pixels(v->cfg) * 7 + 64, cudaHostAllocDefault));
+    char* stage = reinterpret_cast<char*>(s.h_pinned) + raw_off;
+    memcpy(stage, src, bytes);
+    src = stage;
+  }
+  CU_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, v->s_copy));
+  *d_out = dst;
+  return TSDF_OK;
+}
+
+int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
+                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot) {
+  FrameSlot& s = v->slot[slot_index];
+  int rc = ensure_slot(v, s);
+  if (rc) return rc;
+  if (s.in_flight) {  // the kernel that last read this slot must be done before we overwrite it
+    CU_CHECK(cudaEventSynchronize(s.consumed));
+    s.in_flight = false;
+  }
+  const size_t px = frame_pixels(v->cfg);
+  const size_t dbytes = px * (depth_fmt == TSDF_DEPTH_U16 ? 2 : 4);
+  const void* d_depth = nullptr;
+  const void* d_rgb = nullptr;
+  rc = to_device(v, s, depth, dbytes, 0, &d_depth);
+  if (rc) return rc;
+  if (want_color && rgb) {
+    rc = to_device(v, s, rgb, px * 3, ((px * 4 + 63) / 64) * 64, &d_rgb);
+    if (rc) return rc;
+  }
+  rc = launch_frame_prep(d_depth, depth_fmt, depth_scale, sub_c, sub_r,
+                         reinterpret_cast<const uint8_t*>(d_rgb), nullptr, v->cfg.im_h, v->cfg.im_w,
+                         v->cfg.max_depth, want_color, s.d_frame, v->s_copy);
+  if (rc) return rc;
+  CU_CHECK(cudaEventRecord(s.uploaded, v->s_copy));
+  *out_slot = &s;
+  return TSDF_OK;
+}
+
+int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b) {
+  if (v->identity_base) memcpy(c2b, T_wc, 16 * sizeof(float));  // inv(I)*T == T exactly
+  else tsdf_multiply_matrix(v->base2world_inv, T_wc, c2b);       // src/tsdf.cu:142
+  return TSDF_OK;
+}
+
+int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
+                      const void* d_frame, FrameP* out) {
+  float c2b[16];
+  compose_cam2base(v, T_wc, c2b);
+  memcpy(out->c, c2b, 12 * sizeof(float));
+  const float* k = K ? K : v->cfg.K;
+  out->fx = k[0]; out->cx = k[2]; out->fy = k[4]; out->cy = k[5];
+  out->obs_weight = obs_weight;
+  out->pad_ = 0;
+  out->img = d_frame;
+  return TSDF_OK;
+}
+
+// Launches the integrate kernel for nf prepared frames and records stats/events.
+static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
+  for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
+  CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
+  CU_CHECK(cudaEventRecord(v->ev_k0, v->s_compute));
+  int rc = launch_integrate(v, fp, nf, color, v->s_compute);
+  if (rc) return rc;
+  CU_CHECK(cudaEventRecord(v->ev_k1, v->s_compute));
+  CU_CHECK(cudaMemcpyAsync(v->h_written, v->d_written, sizeof(unsigned long long),
+                           cudaMemcpyDeviceToHost, v->s_compute));
+  for (int i = 0; i < nf; ++i) {
+    CU_CHECK(cudaEventRecord(slots[i]->consumed, v->s_compute));
+    slots[i]->in_flight = true;
+  }
+  memcpy(v->last_frames, fp, sizeof(FrameP) * nf);
+  v->last_nf = nf;
+  v->last_color = color;
+  v->last_frames_in_launch = nf;
+  v->frames += nf;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int depth_fmt,
+                                        float depth_scale, int sub_c, int sub_r, const uint8_t* rgb,
+                                        const float* K, const float* T_wc, float obs_weight) {
+  REQUIRE(v && depth && T_wc, "null argument");
+  REQUIRE(depth_fmt == TSDF_DEPTH_F32 || depth_fmt == TSDF_DEPTH_U16, "bad depth format");
+  DeviceGuard g(v->cfg.device);
+  const bool color = v->d_color != nullptr && rgb != nullptr;
+  FrameSlot* s = nullptr;
+  CU_CHECK(cudaEventRecord(v->ev_u0, v->s_copy));
+  int rc = stage_frame(v, (int)(v->seq % 3), depth, depth_fmt, depth_scale, sub_c < 1 ? 1 : sub_c,
+                       sub_r < 1 ? 1 : sub_r, rgb, color, &s);
+  if (rc) return rc;
+  CU_CHECK(cudaEventRecord(v->ev_u1, v->s_copy));
+  ++v->seq;
+  FrameP fp;
+  make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
+  return submit(v, &s, &fp, 1, color);
+}
+
+extern "C" int tsdf_integrate_async(tsdf_vol* v, const float* depth, const uint8_t* rgb,
+                                    const float* K, const float* T_wc, float obs_weight) {
+  return tsdf_integrate_raw_async(v, depth, TSDF_DEPTH_F32, 1.0f, 1, 1, rgb, K, T_wc, obs_weight);
+}
+
+extern "C" int tsdf_integrate(tsdf_vol* v, const float* depth, const uint8_t* rgb, const float* K,
+                              const float* T_wc, float obs_weight) {
+  int rc = tsdf_integrate_async(v, depth, rgb, K, T_wc, obs_weight);
+  return rc ? rc : tsdf_sync(v);
+}
+
+extern "C" int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth, const uint8_t* rgb,
+                                          const float* K, const float* T_wc, float obs_weight) {
+  REQUIRE(v && depth && T_wc && k >= 1, "null argument or k < 1");
+  DeviceGuard g(v->cfg.device);
+  const bool color = v->d_color != nullptr && rgb != nullptr;
+  const size_t px = frame_pixels(v->cfg);
+  int done = 0;
+  while (done < k) {  // greedy split into fused launches of 8/4/2/1 frames, in frame order
+    int nf = (k - done >= 8) ? 8 : (k - done >= 4) ? 4 : (k - done >= 2) ? 2 : 1;
+    FrameSlot* slots[kMaxFusedFrames];
+    FrameP fp[kMaxFusedFrames];
+    const int group = (int)(v->mseq % 2);
+    for (int i = 0; i < nf; ++i) {
+      const int f = done + i;
+      int rc = stage_frame(v, 3 + group * kMaxFusedFrames + i, depth + (size_t)f * px, TSDF_DEPTH_F32,
+                           1.0f, 1, 1, rgb ? rgb + (size_t)f * px * 3 : nullptr, color, &slots[i]);
+      if (rc) return rc;
+      make_frame_params(v, K, T_wc + 16 * f, obs_weight, slots[i]->d_frame, &fp[i]);
+    }
+    ++v->mseq;
+    int rc = submit(v, slots, fp, nf, color);
+    if (rc) return rc;
+    done += nf;
+  }
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_sync(tsdf_vol* v) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  CU_CHECK(cudaStreamSynchronize(v->s_copy));
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  for (FrameSlot& s : v->slot) s.in_flight = false;
+  v->last_written = (int64_t)*v->h_written;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s) {
+  REQUIRE(v && s, "null argument");
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  memset(s, 0, sizeof(*s));
+  s->voxels_visited = v->n_local * v->last_frames_in_launch;
+  s->voxels_written = v->last_written;
+  s->frames = v->frames;
+  if (v->last_nf > 0) {
+    cudaEventElapsedTime(&s->last_kernel_ms, v->ev_k0, v->ev_k1);
+    if (cudaEventElapsedTime(&s->last_upload_ms, v->ev_u0, v->ev_u1) != cudaSuccess) {
+      cudaGetLastError();
+      s->last_upload_ms = 0;
+    }
+  }
+  const int64_t bvox = v->last_color ? 24 : 16;
+  const int64_t bpix = v->last_color ? 8 : 4;
+  s->bytes_algorithmic = bvox * v->last_written +
+                         bpix * (int64_t)frame_pixels(v->cfg) * v->last_frames_in_launch;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_set_variant(tsdf_vol* v, int variant) {
+  REQUIRE(v, "null handle");
+  v->variant = variant;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
+  REQUIRE(v && avg_ms && iters > 0, "bad argument");
+  REQUIRE(v->last_nf > 0, "no frame integrated yet");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
+  CU_CHECK(cudaEventRecord(v->ev_k0, v->s_compute));
+  for (int i = 0; i < iters; ++i) {
+    rc = launch_integrate(v, v->last_frames, v->last_nf, v->last_color, v->s_compute);
+    if (rc) return rc;
+  }
+  CU_CHECK(cudaEventRecord(v->ev_k1, v->s_compute));
+  CU_CHECK(cudaMemcpyAsync(v->h_written, v->d_written, sizeof(unsigned long long),
+                           cudaMemcpyDeviceToHost, v->s_compute));
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  float ms = 0;
+  CU_CHECK(cudaEventElapsedTime(&ms, v->ev_k0, v->ev_k1));
+  *avg_ms = ms / iters;
+  v->frames += (int64_t)iters * v->last_nf;
+  v->last_written = (int64_t)(*v->h_written / (unsigned long long)iters);
+  return TSDF_OK;
+}
+
+// ---- readback (K4, K5, K7) -------------------------------------------------------------------
+// Slab <-> host arrays in the semantics' reference order.  TSDFCU slab [zl][y][x] is one
+// contiguous range of the global array; FUSIONPY slab [x][y][zl] is a strided window of
+// the global [x][y][z] array (2-D copy with pitch Dz).
+static int copy_slab(tsdf_vol* v, float* host, float* dev, int global_layout, bool to_host) {
+  if (!host || !dev) return TSDF_OK;
+  const tsdf_config& c = v->cfg;
+  cudaMemcpyKind kind = to_host ? cudaMemcpyDeviceToHost : cudaMemcpyHostToDevice;
+  if (!global_layout || (v->dzl == c.dim_z)) {
+    if (to_host) CU_CHECK(cudaMemcpyAsync(host, dev, (size_t)v->n_local * 4, kind, v->s_compute));
+    else         CU_CHECK(cudaMemcpyAsync(dev, host, (size_t)v->n_local * 4, kind, v->s_compute));
+    return TSDF_OK;
+  }
+  if (!v->zfast) {
+    float* h = host + (size_t)c.z_begin * c.dim_y * c.dim_x;
+    if (to_host) CU_CHECK(cudaMemcpyAsync(h, dev, (size_t)v->n_local * 4, kind, v->s_compute));
+    else         CU_CHECK(cudaMemcpyAsync(dev, h, (size_t)v->n_local * 4, kind, v->s_compute));
+    return TSDF_OK;
+  }
+  float* h = host + c.z_begin;
+  const size_t rows = (size_t)c.dim_x * c.dim_y;
+  if (to_host)
+    CU_CHECK(cudaMemcpy2DAsync(h, (size_t)c.dim_z * 4, dev, (size_t)v->dzl * 4, (size_t)v->dzl * 4, rows, kind, v->s_compute));
+  else
+    CU_CHECK(cudaMemcpy2DAsync(dev, (size_t)v->dzl * 4, h, (size_t)c.dim_z * 4, (size_t)v->dzl * 4, rows, kind, v->s_compute));
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_download(tsdf_vol* v, float* tsdf, float* weight, float* color, int global_layout) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  REQUIRE(!color || v->d_color, "volume has no colour array");
+  if ((rc = copy_slab(v, tsdf, v->d_tsdf, global_layout, true))) return rc;
+  if ((rc = copy_slab(v, weight, v->d_weight, global_layout, true))) return rc;
+  if ((rc = copy_slab(v, color, v->d_color, global_layout, true))) return rc;
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, const float* color,
+                           int global_layout) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  REQUIRE(!color || v->d_color, "volume has no colour array");
+  if ((rc = copy_slab(v, const_cast<float*>(tsdf), v->d_tsdf, global_layout, false))) return rc;
+  if ((rc = copy_slab(v, const_cast<float*>(weight), v->d_weight, global_layout, false))) return rc;
+  if ((rc = copy_slab(v, const_cast<float*>(color), v->d_color, global_layout, false))) return rc;
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_extract_points_device(tsdf_vol* v, int predicate, float tsdf_thresh,
+                                          float weight_thresh, float* d_xyz, uint8_t* d_rgb,
+                                          int64_t* d_idx, int64_t cap, int64_t* count) {
+  REQUIRE(v && count, "null argument");
+  REQUIRE(predicate == TSDF_PRED_NONZERO || predicate == TSDF_PRED_ABS_LT, "bad predicate");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  return extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, cap, count);
+}
+
+extern "C" int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
+                                   float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap, int64_t* count) {
+  REQUIRE(v && count, "null argument");
+  REQUIRE(predicate == TSDF_PRED_NONZERO || predicate == TSDF_PRED_ABS_LT, "bad predicate");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  int64_t n = 0;
+  rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, nullptr, 0, &n);
+  if (rc) return rc;
+  *count = n;
+  if (!xyz && !rgb && !idx) return TSDF_OK;
+  if (cap < n) {
+    tsdf_set_error("tsdf_extract_points: capacity %lld < %lld points", (long long)cap, (long long)n);
+    return TSDF_E_CAPACITY;
+  }
+  if (n == 0) return TSDF_OK;
+  float* d_xyz = nullptr; uint8_t* d_rgb = nullptr; int64_t* d_idx = nullptr;
+  auto cleanup = [&]() { cudaFree(d_xyz); cudaFree(d_rgb); cudaFree(d_idx); };
+  cudaError_t e = cudaSuccess;
+  if (xyz) e = cudaMalloc(&d_xyz, (size_t)n * 12);
+  if (e == cudaSuccess && rgb) e = cudaMalloc(&d_rgb, (size_t)n * 3);
+  if (e == cudaSuccess && idx) e = cudaMalloc(&d_idx, (size_t)n * 8);
+  if (e != cudaSuccess) { cleanup(); tsdf_set_error("extract: output alloc: %s", cudaGetErrorString(e)); return TSDF_E_NOMEM; }
+  rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, n, &n);
+  if (!rc) {
+    if (xyz) e = cudaMemcpy(xyz, d_xyz, (size_t)n * 12, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && rgb) e = cudaMemcpy(rgb, d_rgb, (size_t)n * 3, cudaMemcpyDeviceToHost);
+    if (e == cudaSuccess && idx) e = cudaMemcpy(idx, d_idx, (size_t)n * 8, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { tsdf_set_error("extract: D2H: %s", cudaGetErrorString(e)); rc = TSDF_E_CUDA; }
+  }
+  cleanup();
+  return rc;
+}
+
+// PLY: header text of src/tsdf.cu:186-192, then float x,y,z per kept voxel.
+extern "C" int tsdf_save_ply(tsdf_vol* v, const char* path, int predicate, float tsdf_thresh,
+                             float weight_thresh) {
+  REQUIRE(v && path, "null argument");
+  REQUIRE(v->dzl == v->cfg.dim_z, "tsdf_save_ply needs a whole-grid handle");
+  int64_t n = 0;
+  int rc = tsdf_extract_points(v, predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, nullptr, 0, &n);
+  if (rc) return rc;
+  std::vector<float> xyz((size_t)(n ? n : 1) * 3);
+  if (n) {
+    rc = tsdf_extract_points(v, predicate, tsdf_thresh, weight_thresh, xyz.data(), nullptr, nullptr, n, &n);
+    if (rc) return rc;
+  }
+  FILE* fp = fopen(path, "w");
+  if (!fp) { tsdf_set_error("tsdf_save_ply: cannot open %s", path); return TSDF_E_IO; }
+  fprintf(fp, "ply\n");
+  fprintf(fp, "format binary_little_endian 1.0\n");
+  fprintf(fp, "element vertex %d\n", (int)n);
+  fprintf(fp, "property float x\n");
+  fprintf(fp, "property float y\n");
+  fprintf(fp, "property float z\n");
+  fprintf(fp, "end_header\n");
+  size_t wr = fwrite(xyz.data(), sizeof(float), (size_t)n * 3, fp);
+  fclose(fp);
+  if (wr != (size_t)n * 3) { tsdf_set_error("tsdf_save_ply: short write"); return TSDF_E_IO; }
+  return TSDF_OK;
+}
+
+// BIN: 8-float header (dims as floats, origin, voxel_size, trunc) + tsdf (src/tsdf.cu:116-132).
+extern "C" int tsdf_save_bin(tsdf_vol* v, const char* path) {
+  REQUIRE(v && path, "null argument");
+  REQUIRE(v->dzl == v->cfg.dim_z, "tsdf_save_bin needs a whole-grid handle");
+  std::vector<float> t((size_t)v->n_local);
+  int rc = tsdf_download(v, t.data(), nullptr, nullptr, 0);
+  if (rc) return rc;
+  FILE* fp = fopen(path, "wb");
+  if (!fp) { tsdf_set_error("tsdf_save_bin: cannot open %s", path); return TSDF_E_IO; }
+  const tsdf_config& c = v->cfg;
+  float h[8] = {(float)c.dim_x, (float)c.dim_y, (float)c.dim_z, c.origin[0], c.origin[1], c.origin[2],
+                c.voxel_size, c.trunc_margin};
+  size_t wr = fwrite(h, sizeof(float), 8, fp);
+  wr += fwrite(t.data(), sizeof(float), t.size(), fp);
+  fclose(fp);
+  if (wr != 8 + t.size()) { tsdf_set_error("tsdf_save_bin: short write"); return TSDF_E_IO; }
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_load_bin(tsdf_vol* v, const char* path) {
+  REQUIRE(v && path, "null argument");
+  REQUIRE(v->dzl == v->cfg.dim_z, "tsdf_load_bin needs a whole-grid handle");
+  FILE* fp = fopen(path, "rb");
+  if (!fp) { tsdf_set_error("tsdf_load_bin: cannot open %s", path); return TSDF_E_IO; }
+  float h[8];
+  const tsdf_config& c = v->cfg;
+  if (fread(h, sizeof(float), 8, fp) != 8 || (int)h[0] != c.dim_x || (int)h[1] != c.dim_y ||
+      (int)h[2] != c.dim_z) {
+    fclose(fp);
+    tsdf_set_error("tsdf_load_bin: header of %s does not match the volume dims", path);
+    return TSDF_E_IO;
+  }
+  std::vector<float> t((size_t)v->n_local);
+  size_t rd = fread(t.data(), sizeof(float), t.size(), fp);
+  fclose(fp);
+  if (rd != t.size()) { tsdf_set_error("tsdf_load_bin: short read"); return TSDF_E_IO; }
+  return tsdf_upload(v, t.data(), nullptr, nullptr, 0);
+}
+
+// ---- per-instance origin on the device (K9) -----------------------------------------------------
+extern "C" int tsdf_instance_origin(int device, const float* depth, const uint8_t* mask, int im_h,
+                                    int im_w, const float K[9], float origin_out[3]) {
+  REQUIRE(depth && K && origin_out && im_h > 0 && im_w > 0, "bad argument");
+  int ndev = 0;
+  int rc = tsdf_device_count(&ndev);
+  if (rc) return rc;
+  DeviceGuard g(device);
+  const size_t px = (size_t)im_h * im_w;
+  float* d_depth = nullptr; uint8_t* d_mask = nullptr; float* d_out = nullptr;
+  const float* dd = depth; const uint8_t* dm = mask;
+  auto cleanup = [&]() { cudaFree(d_depth); cudaFree(d_mask); cudaFree(d_out); };
+  cudaError_t e = cudaMalloc(&d_out, 12);
+  if (e == cudaSuccess && ptr_kind(depth) != PTR_DEVICE) {
+    e = cudaMalloc(&d_depth, px * 4);
+    if (e == cudaSuccess) e = cudaMemcpy(d_depth, depth, px * 4, cudaMemcpyHostToDevice);
+    dd = d_depth;
+  }
+  if (e == cudaSuccess && mask && ptr_kind(mask) != PTR_DEVICE) {
+    e = cudaMalloc(&d_mask, px);
+    if (e == cudaSuccess) e = cudaMemcpy(d_mask, mask, px, cudaMemcpyHostToDevice);
+    dm = d_mask;
+  }
+  if (e != cudaSuccess) { cleanup(); tsdf_set_error("tsdf_instance_origin: %s", cudaGetErrorString(e)); return TSDF_E_CUDA; }
+  rc = launch_instance_origin(dd, dm, im_h, im_w, K[0], K[2], K[4], K[5], d_out, 0);
+  if (!rc) {
+    e = cudaMemcpy(origin_out, d_out, 12, cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { tsdf_set_error("tsdf_instance_origin: %s", cudaGetErrorString(e)); rc = TSDF_E_CUDA; }
+  }
+  cleanup();
+  return rc;
+}
+
+// ---- memory helpers -------------------------------------------------------------------------------
+extern "C" int tsdf_host_alloc(void** p, size_t bytes) {
+  REQUIRE(p, "null argument");
+  CU_CHECK(cudaHostAlloc(p, bytes, cudaHostAllocDefault));
+  return TSDF_OK;
+}
+extern "C" int tsdf_host_free(void* p) {
+  if (p) CU_CHECK(cudaFreeHost(p));
+  return TSDF_OK;
+}
+extern "C" int tsdf_device_alloc(int device, void** p, size_t bytes) {
+  REQUIRE(p, "null argument");
+  DeviceGuard g(device);
+  CU_CHECK(cudaMalloc(p, bytes));
+  return TSDF_OK;
+}
+extern "C" int tsdf_device_free(int device, void* p) {
+  DeviceGuard g(device);
+  if (p) CU_CHECK(cudaFree(p));
+  return TSDF_OK;
+}
+extern "C" int tsdf_memcpy_h2d(int device, void* dst, const void* src, size_t bytes) {
+  DeviceGuard g(device);
+  CU_CHECK(cudaMemcpy(dst, src, bytes, cudaMemcpyHostToDevice));
+  return TSDF_OK;
+}
+extern "C" int tsdf_memcpy_d2h(int device, void* dst, const void* src, size_t bytes) {
+  DeviceGuard g(device);
+  CU_CHECK(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
+  return TSDF_OK;
+}
+
+// ---- helpers for comm.cu: frame staging split around the NCCL broadcast ------------------------
+// bcast_stage picks the next single-frame slot, moves the root's images to the device (or
+// takes them where they already are) and tells comm.cu what to broadcast into the slot's raw
+// buffer; bcast_finish preps the slot and launches the integrate.
+int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rgb, bool color,
+                FrameSlot** slot, void** d_depth, void** d_rgb, const void** send_depth,
+                const void** send_rgb) {
+  FrameSlot& s = v->slot[v->seq % 3];
+  int rc = ensure_slot(v, s);
+  if (rc) return rc;
+  if (s.in_flight) {
+    CU_CHECK(cudaEventSynchronize(s.consumed));
+    s.in_flight = false;
+  }
+  const size_t px = frame_pixels(v->cfg);
+  const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
+  *d_depth = s.d_raw;
+  *d_rgb = reinterpret_cast<char*>(s.d_raw) + rgb_off;
+  *send_depth = *d_depth;
+  *send_rgb = *d_rgb;
+  if (is_root) {
+    rc = to_device(v, s, depth, px * 4, 0, send_depth);   // device inputs are sent from where they are
+    if (rc) return rc;
+    if (color) {
+      rc = to_device(v, s, rgb, px * 3, rgb_off, send_rgb);
+      if (rc) return rc;
+    }
+  }
+  *slot = &s;
+  return TSDF_OK;
+}
+
+int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const float* T_wc,
+                 float obs_weight) {
+  const size_t px = frame_pixels(v->cfg);
+  const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
+  int rc = launch_frame_prep(s->d_raw, TSDF_DEPTH_F32, 1.0f, 1, 1,
+                             color ? reinterpret_cast<const uint8_t*>(s->d_raw) + rgb_off : nullptr,
+                             nullptr, v->cfg.im_h, v->cfg.im_w, v->cfg.max_depth, color, s->d_frame,
+                             v->s_copy);
+  if (rc) return rc;
+  CU_CHECK(cudaEventRecord(s->uploaded, v->s_copy));
+  ++v->seq;
+  FrameP fp;
+  make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
+  return submit(v, &s, &fp, 1, color);
+}

@@ -1,0 +1,204 @@
+// batch.cu — batched per-instance object volumes (BASELINE config 5).
+//
+// In the reference every Mask-RCNN instance owns a `TSDF*` (include/Object.hpp:216-218) and
+// Engine::Run would, per mask, build a full-frame masked depth image
+// (src/Engine.cpp:192-193) and call Object::Integrate -> TSDF::Integrate, i.e. one blocking
+// 1.2 MB upload and one <<<Dz,Dy>>> launch per instance per keyframe (src/tsdf.cu:161-167).
+// Here the frame is uploaded ONCE, the 8-bit masks of the active instances are uploaded as
+// one block, and ONE launch (blockIdx.z = instance) integrates all of them; the mask test
+// `depth * (mask/255)` is applied at gather time inside the kernel.
+#include <new>
+
+#include "common.cuh"
+
+struct tsdf_batch {
+  int n = 0;
+  std::vector<tsdf_vol*> vols;   // per-instance state (arrays, config, base pose); own streams unused
+  tsdf_vol* frame_owner = nullptr;  // vols[0]: its slots/streams carry the shared frame
+  BatchDesc* d_descs = nullptr;
+  BatchDesc* h_descs = nullptr;  // pinned
+  uint8_t* d_masks = nullptr;    // n * H*W
+  uint8_t* h_masks = nullptr;    // pinned staging, n * H*W
+  unsigned long long* d_written = nullptr;
+  unsigned long long* h_written = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, masks_free = nullptr;
+  bool masks_in_flight = false;
+  int last_active = 0;
+  int64_t last_visited = 0;
+  bool last_color = false;
+};
+
+extern "C" int tsdf_batch_destroy(tsdf_batch* b) {
+  if (!b) return TSDF_OK;
+  if (b->frame_owner) {
+    DeviceGuard g(b->frame_owner->cfg.device);
+    cudaStreamSynchronize(b->frame_owner->s_compute);
+    cudaStreamSynchronize(b->frame_owner->s_copy);
+    cudaFree(b->d_descs); cudaFree(b->d_masks); cudaFree(b->d_written);
+    if (b->h_descs) cudaFreeHost(b->h_descs);
+    if (b->h_masks) cudaFreeHost(b->h_masks);
+    if (b->h_written) cudaFreeHost(b->h_written);
+    for (cudaEvent_t e : {b->ev0, b->ev1, b->masks_free}) if (e) cudaEventDestroy(e);
+  }
+  for (tsdf_vol* v : b->vols) tsdf_destroy(v);
+  delete b;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_create(const tsdf_config* cfgs, int n, tsdf_batch** out) {
+  REQUIRE(cfgs && out && n >= 1, "bad argument");
+  *out = nullptr;
+  for (int i = 1; i < n; ++i) {
+    REQUIRE(cfgs[i].semantics == cfgs[0].semantics && cfgs[i].with_color == cfgs[0].with_color &&
+                cfgs[i].device == cfgs[0].device && cfgs[i].im_h == cfgs[0].im_h &&
+                cfgs[i].im_w == cfgs[0].im_w && cfgs[i].max_depth == cfgs[0].max_depth,
+            "instances of a batch must share semantics, colour mode, device, frame shape, max_depth");
+  }
+  tsdf_batch* b = new (std::nothrow) tsdf_batch();
+  if (!b) { tsdf_set_error("tsdf_batch_create: host allocation failed"); return TSDF_E_NOMEM; }
+  b->n = n;
+  for (int i = 0; i < n; ++i) {
+    tsdf_vol* v = nullptr;
+    int rc = tsdf_create(&cfgs[i], &v);
+    if (rc) { tsdf_batch_destroy(b); return rc; }
+    REQUIRE(v->dzl == v->cfg.dim_z, "batched instances must be whole grids");
+    b->vols.push_back(v);
+  }
+  b->frame_owner = b->vols[0];
+  DeviceGuard g(cfgs[0].device);
+  const size_t px = frame_pixels(cfgs[0]);
+  auto fail = [&](const char* what) { tsdf_set_error("tsdf_batch_create: %s failed", what); tsdf_batch_destroy(b); return TSDF_E_NOMEM; };
+  if (cudaMalloc(&b->d_descs, sizeof(BatchDesc) * (size_t)n)) return fail("cudaMalloc descs");
+  if (cudaHostAlloc(&b->h_descs, sizeof(BatchDesc) * (size_t)n, cudaHostAllocDefault)) return fail("cudaHostAlloc descs");
+  if (cudaMalloc(&b->d_masks, px * (size_t)n)) return fail("cudaMalloc masks");
+  if (cudaHostAlloc(&b->h_masks, px * (size_t)n, cudaHostAllocDefault)) return fail("cudaHostAlloc masks");
+  if (cudaMalloc(&b->d_written, 8)) return fail("cudaMalloc counter");
+  if (cudaHostAlloc(&b->h_written, 8, cudaHostAllocDefault)) return fail("cudaHostAlloc counter");
+  *b->h_written = 0;
+  cudaEventCreate(&b->ev0); cudaEventCreate(&b->ev1);
+  cudaEventCreateWithFlags(&b->masks_free, cudaEventDisableTiming);
+  *out = b;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_size(const tsdf_batch* b, int* n) {
+  REQUIRE(b && n, "null argument");
+  *n = b->n;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
+                                          const int32_t* active, int n_active, const uint8_t* masks,
+                                          const float* K, const float* T_wc, float obs_weight) {
+  REQUIRE(b && depth && T_wc && active && n_active >= 1 && n_active <= b->n, "bad argument");
+  tsdf_vol* fo = b->frame_owner;
+  DeviceGuard g(fo->cfg.device);
+  const size_t px = frame_pixels(fo->cfg);
+  const bool color = fo->d_color != nullptr && rgb != nullptr;
+  // the previous launch may still read descs/masks
+  if (b->masks_in_flight) { CU_CHECK(cudaEventSynchronize(b->masks_free)); b->masks_in_flight = false; }
+  // 1. shared frame: one upload + prep on the copy stream
+  FrameSlot* slot = nullptr;
+  int rc = stage_frame(fo, (int)(fo->seq % 3), depth, TSDF_DEPTH_F32, 1.0f, 1, 1, rgb, color, &slot);
+  if (rc) return rc;
+  ++fo->seq;
+  // 2. masks: one block copy (device masks are used in place)
+  const uint8_t* d_masks = nullptr;
+  if (masks) {
+    cudaPointerAttributes a;
+    bool on_dev = cudaPointerGetAttributes(&a, masks) == cudaSuccess &&
+                  (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged);
+    cudaGetLastError();
+    if (on_dev) d_masks = masks;
+    else {
+      const bool pinned = a.type == cudaMemoryTypeHost;
+      const void* src = masks;
+      if (!pinned) { memcpy(b->h_masks, masks, px * (size_t)n_active); src = b->h_masks; }
+      CU_CHECK(cudaMemcpyAsync(b->d_masks, src, px * (size_t)n_active, cudaMemcpyHostToDevice, fo->s_copy));
+      d_masks = b->d_masks;
+    }
+  }
+  // 3. descriptors
+  int max_fast = 0, max_rows = 0;
+  int64_t visited = 0;
+  bool vec4 = true;
+  for (int i = 0; i < n_active; ++i) {
+    REQUIRE(active[i] >= 0 && active[i] < b->n, "instance id out of range");
+    tsdf_vol* v = b->vols[active[i]];
+    const tsdf_config& c = v->cfg;
+    BatchDesc& d = b->h_descs[i];
+    d.g.n_fast = v->zfast ? v->dzl : c.dim_x;
+    d.g.n_mid = c.dim_y;
+    d.g.n_slow = v->zfast ? c.dim_x : v->dzl;
+    d.g.z0 = c.z_begin;
+    d.g.ox = c.origin[0]; d.g.oy = c.origin[1]; d.g.oz = c.origin[2];
+    d.g.vs = c.voxel_size; d.g.trunc = c.trunc_margin;
+    d.g.W = c.im_w; d.g.H = c.im_h;
+    d.g.tsdf = v->d_tsdf; d.g.weight = v->d_weight; d.g.color = color ? v->d_color : nullptr;
+    d.g.written = b->d_written;
+    make_frame_params(v, K, T_wc, obs_weight, slot->d_frame, &d.f);
+    d.mask = d_masks ? d_masks + px * (size_t)i : nullptr;
+    max_fast = d.g.n_fast > max_fast ? d.g.n_fast : max_fast;
+    int rows = d.g.n_mid * d.g.n_slow;
+    max_rows = rows > max_rows ? rows : max_rows;
+    vec4 = vec4 && (d.g.n_fast % 4 == 0);
+    visited += v->n_local;
+    v->frames += 1;
+  }
+  CU_CHECK(cudaMemcpyAsync(b->d_descs, b->h_descs, sizeof(BatchDesc) * (size_t)n_active,
+                           cudaMemcpyHostToDevice, fo->s_copy));
+  CU_CHECK(cudaEventRecord(slot->uploaded, fo->s_copy));  // covers frame, masks and descriptors
+  // 4. one launch for all active instances
+  CU_CHECK(cudaStreamWaitEvent(fo->s_compute, slot->uploaded, 0));
+  CU_CHECK(cudaMemsetAsync(b->d_written, 0, 8, fo->s_compute));
+  CU_CHECK(cudaEventRecord(b->ev0, fo->s_compute));
+  rc = launch_integrate_batch(b->d_descs, n_active, max_fast, max_rows, fo->zfast, color, vec4, fo->s_compute);
+  if (rc) return rc;
+  CU_CHECK(cudaEventRecord(b->ev1, fo->s_compute));
+  CU_CHECK(cudaMemcpyAsync(b->h_written, b->d_written, 8, cudaMemcpyDeviceToHost, fo->s_compute));
+  CU_CHECK(cudaEventRecord(slot->consumed, fo->s_compute));
+  CU_CHECK(cudaEventRecord(b->masks_free, fo->s_compute));
+  slot->in_flight = true;
+  b->masks_in_flight = true;
+  b->last_active = n_active;
+  b->last_visited = visited;
+  b->last_color = color;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_sync(tsdf_batch* b) {
+  REQUIRE(b, "null handle");
+  int rc = tsdf_sync(b->frame_owner);
+  b->masks_in_flight = false;
+  return rc;
+}
+
+extern "C" int tsdf_batch_get_stats(tsdf_batch* b, tsdf_stats* s) {
+  REQUIRE(b && s, "null argument");
+  int rc = tsdf_batch_sync(b);
+  if (rc) return rc;
+  memset(s, 0, sizeof(*s));
+  s->voxels_visited = b->last_visited;
+  s->voxels_written = (int64_t)*b->h_written;
+  s->frames = b->frame_owner->seq;
+  if (b->last_active > 0) cudaEventElapsedTime(&s->last_kernel_ms, b->ev0, b->ev1);
+  s->bytes_algorithmic = (b->last_color ? 24 : 16) * s->voxels_written +
+                         (int64_t)frame_pixels(b->frame_owner->cfg) * ((b->last_color ? 8 : 4) + b->last_active);
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_download(tsdf_batch* b, int instance, float* tsdf, float* weight, float* color) {
+  REQUIRE(b && instance >= 0 && instance < b->n, "bad argument");
+  int rc = tsdf_batch_sync(b);
+  if (rc) return rc;
+  return tsdf_download(b->vols[instance], tsdf, weight, color, 0);
+}
+
+extern "C" int tsdf_batch_extract_points(tsdf_batch* b, int instance, int predicate, float tsdf_thresh,
+                                         float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx,
+                                         int64_t cap, int64_t* count) {
+  REQUIRE(b && instance >= 0 && instance < b->n, "bad argument");
+  int rc = tsdf_batch_sync(b);
+  if (rc) return rc;
+  return tsdf_extract_points(b->vols[instance], predicate, tsdf_thresh, weight_thresh, xyz, rgb, idx, cap, count);
+}

@@ -1,0 +1,279 @@
+// comm.cu — multi-GPU plumbing for z-slab sharded volumes.
+//
+// The reference has no multi-GPU path at all; this is new design.  The voxel
+// update is embarrassingly parallel across voxels, so the only exchange steps are
+//   * per frame: the bulky image payload (depth fp32 + rgb u8) is broadcast from the rank
+//     that received it to all ranks over NVLink/NVSwitch with ncclBroadcast (one grouped
+//     launch), into each rank's raw frame slot, then every rank preps + integrates its slab;
+//     the 100-byte pose/intrinsics metadata travels on the host control plane (the caller
+//     passes it on every rank);
+//   * at readback: counts are all-gathered, point records are sent to the root with grouped
+//     ncclSend/ncclRecv and merged to ascending GLOBAL reference index.
+// NCCL is bound at run time with dlopen so that the core library has no link-time
+// dependency (a process that already loaded torch's libnccl.so.2 reuses that one).
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "common.cuh"
+
+namespace {
+
+struct NcclApi {
+  void* h = nullptr;
+  ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+  ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Send)(const void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Recv)(void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*GroupStart)() = nullptr;
+  ncclResult_t (*GroupEnd)() = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+};
+
+NcclApi g_nccl;
+
+int load_nccl() {
+  if (g_nccl.h) return TSDF_OK;
+  const char* names[] = {"libnccl.so.2", "libnccl.so"};
+  void* h = nullptr;
+  for (const char* n : names) {
+    h = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+    if (h) break;
+  }
+  if (!h) {
+    tsdf_set_error("NCCL not found: %s", dlerror());
+    return TSDF_E_NCCL;
+  }
+#define BIND(field, sym)                                              \
+  g_nccl.field = reinterpret_cast<decltype(g_nccl.field)>(dlsym(h, sym)); \
+  if (!g_nccl.field) { tsdf_set_error("NCCL symbol %s missing", sym); return TSDF_E_NCCL; }
+  BIND(GetUniqueId, "ncclGetUniqueId");
+  BIND(CommInitRank, "ncclCommInitRank");
+  BIND(CommDestroy, "ncclCommDestroy");
+  BIND(Broadcast, "ncclBroadcast");
+  BIND(AllGather, "ncclAllGather");
+  BIND(Send, "ncclSend");
+  BIND(Recv, "ncclRecv");
+  BIND(GroupStart, "ncclGroupStart");
+  BIND(GroupEnd, "ncclGroupEnd");
+  BIND(GetErrorString, "ncclGetErrorString");
+#undef BIND
+  g_nccl.h = h;
+  return TSDF_OK;
+}
+
+#define NCCL_CHECK(expr)                                                              \
+  do {                                                                                \
+    ncclResult_t r__ = (expr);                                                        \
+    if (r__ != ncclSuccess) {                                                         \
+      tsdf_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, g_nccl.GetErrorString(r__)); \
+      return TSDF_E_NCCL;                                                             \
+    }                                                                                 \
+  } while (0)
+
+}  // namespace
+
+struct tsdf_comm {
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0, device = 0;
+  int64_t* d_counts = nullptr;  // nranks entries
+};
+
+static_assert(sizeof(ncclUniqueId) == 128, "uid128 contract");
+
+extern "C" int tsdf_comm_unique_id(void* uid128) {
+  REQUIRE(uid128, "null argument");
+  int rc = load_nccl();
+  if (rc) return rc;
+  ncclUniqueId id;
+  NCCL_CHECK(g_nccl.GetUniqueId(&id));
+  memcpy(uid128, &id, 128);
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_comm_create(const void* uid128, int nranks, int rank, int device, tsdf_comm** out) {
+  REQUIRE(uid128 && out && nranks >= 1 && rank >= 0 && rank < nranks, "bad argument");
+  *out = nullptr;
+  int rc = load_nccl();
+  if (rc) return rc;
+  int ndev = 0;
+  if ((rc = tsdf_device_count(&ndev))) return rc;
+  REQUIRE(device >= 0 && device < ndev, "device ordinal out of range");
+  // ncclCommInitRank binds to the CURRENT device: leave it set for the lifetime of the call
+  DeviceGuard g(device);
+  tsdf_comm* c = new (std::nothrow) tsdf_comm();
+  if (!c) { tsdf_set_error("tsdf_comm_create: host allocation failed"); return TSDF_E_NOMEM; }
+  c->nranks = nranks; c->rank = rank; c->device = device;
+  ncclUniqueId id;
+  memcpy(&id, uid128, 128);
+  ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+  if (r != ncclSuccess) {
+    tsdf_set_error("ncclCommInitRank: %s", g_nccl.GetErrorString(r));
+    delete c;
+    return TSDF_E_NCCL;
+  }
+  if (cudaMalloc(&c->d_counts, sizeof(int64_t) * (size_t)nranks) != cudaSuccess) {
+    g_nccl.CommDestroy(c->comm);
+    delete c;
+    tsdf_set_error("tsdf_comm_create: device allocation failed");
+    return TSDF_E_NOMEM;
+  }
+  *out = c;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_comm_destroy(tsdf_comm* c) {
+  if (!c) return TSDF_OK;
+  DeviceGuard g(c->device);
+  cudaFree(c->d_counts);
+  if (c->comm) g_nccl.CommDestroy(c->comm);
+  delete c;
+  return TSDF_OK;
+}
+
+// defined in api.cu
+int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rgb, bool color,
+                FrameSlot** slot, void** d_depth, void** d_rgb, const void** send_depth,
+                const void** send_rgb);
+int bcast_finish(tsdf_vol* v, FrameSlot* slot, bool color, const float* K, const float* T_wc,
+                 float obs_weight);
+
+extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float* depth,
+                                          const uint8_t* rgb, const float* K, const float* T_wc,
+                                          float obs_weight) {
+  REQUIRE(v && c && T_wc, "null argument (pose metadata is required on every rank)");
+  REQUIRE(root >= 0 && root < c->nranks, "bad root");
+  REQUIRE(v->cfg.device == c->device, "volume and communicator live on different devices");
+  const bool is_root = c->rank == root;
+  const bool color = v->d_color != nullptr;  // every rank decides the same way
+  REQUIRE(!is_root || depth, "root needs a depth image");
+  REQUIRE(!is_root || !color || rgb, "root needs an rgb image for a colour volume");
+  DeviceGuard g(v->cfg.device);
+  FrameSlot* slot = nullptr;
+  void *d_depth = nullptr, *d_rgb = nullptr;
+  const void *s_depth = nullptr, *s_rgb = nullptr;
+  int rc = bcast_stage(v, is_root, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb);
+  if (rc) return rc;
+  const size_t px = frame_pixels(v->cfg);
+  if (c->nranks > 1) {
+    NCCL_CHECK(g_nccl.GroupStart());
+    NCCL_CHECK(g_nccl.Broadcast(s_depth, d_depth, px * 4, ncclUint8, root, c->comm, v->s_copy));
+    if (color) NCCL_CHECK(g_nccl.Broadcast(s_rgb, d_rgb, px * 3, ncclUint8, root, c->comm, v->s_copy));
+    NCCL_CHECK(g_nccl.GroupEnd());
+  } else {
+    if (s_depth != d_depth) CU_CHECK(cudaMemcpyAsync(d_depth, s_depth, px * 4, cudaMemcpyDeviceToDevice, v->s_copy));
+    if (color && s_rgb != d_rgb) CU_CHECK(cudaMemcpyAsync(d_rgb, s_rgb, px * 3, cudaMemcpyDeviceToDevice, v->s_copy));
+  }
+  return bcast_finish(v, slot, color, K, T_wc, obs_weight);
+}
+
+extern "C" int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predicate, float tsdf_thresh,
+                                  float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx,
+                                  int64_t cap, int64_t* count) {
+  REQUIRE(v && c && count, "null argument");
+  REQUIRE(root >= 0 && root < c->nranks, "bad root");
+  DeviceGuard g(v->cfg.device);
+  const bool is_root = c->rank == root;
+  const bool want_rgb = v->d_color != nullptr;
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  // 1. local extraction into device buffers (idx always: it is the merge key)
+  int64_t n_local = 0;
+  rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, nullptr, 0, &n_local);
+  if (rc) return rc;
+  float* d_xyz = nullptr; uint8_t* d_rgb = nullptr; int64_t* d_idx = nullptr;
+  float* r_xyz = nullptr; uint8_t* r_rgb = nullptr; int64_t* r_idx = nullptr;
+  auto cleanup = [&]() { cudaFree(d_xyz); cudaFree(d_rgb); cudaFree(d_idx); cudaFree(r_xyz); cudaFree(r_rgb); cudaFree(r_idx); };
+  const size_t nl = (size_t)std::max<int64_t>(n_local, 1);
+  if (cudaMalloc(&d_xyz, nl * 12) || cudaMalloc(&d_idx, nl * 8) || (want_rgb && cudaMalloc(&d_rgb, nl * 3))) {
+    cleanup(); tsdf_set_error("tsdf_gather_points: device allocation failed"); return TSDF_E_NOMEM;
+  }
+  if (n_local) {
+    rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, n_local, &n_local);
+    if (rc) { cleanup(); return rc; }
+  }
+  // 2. counts
+  cudaStream_t st = v->s_compute;
+  std::vector<int64_t> counts((size_t)c->nranks, 0);
+  if (c->nranks > 1) {
+    cudaMemcpyAsync(c->d_counts + c->rank, &n_local, 8, cudaMemcpyHostToDevice, st);
+    ncclResult_t r = g_nccl.AllGather(c->d_counts + c->rank, c->d_counts, 1, ncclInt64, c->comm, st);
+    if (r != ncclSuccess) { cleanup(); tsdf_set_error("ncclAllGather: %s", g_nccl.GetErrorString(r)); return TSDF_E_NCCL; }
+    cudaMemcpyAsync(counts.data(), c->d_counts, 8 * (size_t)c->nranks, cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess) { cleanup(); tsdf_set_error("gather: sync failed"); return TSDF_E_CUDA; }
+  } else {
+    counts[0] = n_local;
+  }
+  int64_t total = 0;
+  std::vector<int64_t> offs((size_t)c->nranks + 1, 0);
+  for (int r = 0; r < c->nranks; ++r) { offs[r] = total; total += counts[r]; }
+  offs[c->nranks] = total;
+  *count = is_root ? total : n_local;
+  // 3. records to the root (every rank takes part even if the root's buffers are too small:
+  //    the root then receives into scratch and reports TSDF_E_CAPACITY afterwards)
+  const size_t nt = (size_t)std::max<int64_t>(total, 1);
+  if (is_root) {
+    if (cudaMalloc(&r_xyz, nt * 12) || cudaMalloc(&r_idx, nt * 8) || (want_rgb && cudaMalloc(&r_rgb, nt * 3))) {
+      cleanup(); tsdf_set_error("tsdf_gather_points: root allocation failed"); return TSDF_E_NOMEM;
+    }
+  }
+  if (c->nranks > 1) {
+    g_nccl.GroupStart();
+    if (!is_root) {
+      if (n_local) {
+        g_nccl.Send(d_xyz, (size_t)n_local * 3, ncclFloat32, root, c->comm, st);
+        g_nccl.Send(d_idx, (size_t)n_local, ncclInt64, root, c->comm, st);
+        if (want_rgb) g_nccl.Send(d_rgb, (size_t)n_local * 3, ncclUint8, root, c->comm, st);
+      }
+    } else {
+      for (int r = 0; r < c->nranks; ++r) {
+        if (r == root || counts[r] == 0) continue;
+        g_nccl.Recv(r_xyz + offs[r] * 3, (size_t)counts[r] * 3, ncclFloat32, r, c->comm, st);
+        g_nccl.Recv(r_idx + offs[r], (size_t)counts[r], ncclInt64, r, c->comm, st);
+        if (want_rgb) g_nccl.Recv(r_rgb + offs[r] * 3, (size_t)counts[r] * 3, ncclUint8, r, c->comm, st);
+      }
+    }
+    ncclResult_t r = g_nccl.GroupEnd();
+    if (r != ncclSuccess) { cleanup(); tsdf_set_error("gather send/recv: %s", g_nccl.GetErrorString(r)); return TSDF_E_NCCL; }
+  }
+  if (is_root && n_local) {
+    cudaMemcpyAsync(r_xyz + offs[root] * 3, d_xyz, (size_t)n_local * 12, cudaMemcpyDeviceToDevice, st);
+    cudaMemcpyAsync(r_idx + offs[root], d_idx, (size_t)n_local * 8, cudaMemcpyDeviceToDevice, st);
+    if (want_rgb) cudaMemcpyAsync(r_rgb + offs[root] * 3, d_rgb, (size_t)n_local * 3, cudaMemcpyDeviceToDevice, st);
+  }
+  if (cudaStreamSynchronize(st) != cudaSuccess) { cleanup(); tsdf_set_error("gather: %s", cudaGetErrorString(cudaGetLastError())); return TSDF_E_CUDA; }
+  rc = TSDF_OK;
+  if (is_root && (xyz || rgb || idx)) {
+    if (cap < total) {
+      tsdf_set_error("tsdf_gather_points: capacity %lld < %lld points", (long long)cap, (long long)total);
+      rc = TSDF_E_CAPACITY;
+    } else if (total) {
+      // 4. D2H, then k-way merge by GLOBAL reference index.  x-fast slabs are contiguous index
+      //    ranges (concatenation is already sorted); z-fast slabs interleave per (x,y) row.
+      std::vector<float> hx(nt * 3); std::vector<int64_t> hi(nt); std::vector<uint8_t> hc(want_rgb ? nt * 3 : 0);
+      cudaMemcpy(hx.data(), r_xyz, (size_t)total * 12, cudaMemcpyDeviceToHost);
+      cudaMemcpy(hi.data(), r_idx, (size_t)total * 8, cudaMemcpyDeviceToHost);
+      if (want_rgb) cudaMemcpy(hc.data(), r_rgb, (size_t)total * 3, cudaMemcpyDeviceToHost);
+      std::vector<int64_t> cur(offs.begin(), offs.end() - 1);
+      for (int64_t o = 0; o < total; ++o) {
+        int best = -1; int64_t bi = 0;
+        for (int r = 0; r < c->nranks; ++r)
+          if (cur[r] < offs[r + 1] && (best < 0 || hi[cur[r]] < bi)) { best = r; bi = hi[cur[r]]; }
+        const int64_t s = cur[best]++;
+        if (xyz) { xyz[3 * o] = hx[3 * s]; xyz[3 * o + 1] = hx[3 * s + 1]; xyz[3 * o + 2] = hx[3 * s + 2]; }
+        if (idx) idx[o] = bi;
+        if (rgb) {
+          if (want_rgb) { rgb[3 * o] = hc[3 * s]; rgb[3 * o + 1] = hc[3 * s + 1]; rgb[3 * o + 2] = hc[3 * s + 2]; }
+          else { rgb[3 * o] = rgb[3 * o + 1] = rgb[3 * o + 2] = 0; }
+        }
+      }
+    }
+  }
+  cleanup();
+  return rc;
+}

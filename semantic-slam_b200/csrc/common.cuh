@@ -1,0 +1,144 @@
+// common.cuh — internal types shared by the translation units of libtsdf_b200.so.
+// Nothing here is part of the ABI; the ABI is include/tsdf_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/tsdf_b200.h"
+
+// ---- error plumbing -----------------------------------------------------------------
+void tsdf_set_error(const char* fmt, ...);  // thread-local, printf style
+#define CU_CHECK(expr)                                                                    \
+  do {                                                                                    \
+    cudaError_t e__ = (expr);                                                             \
+    if (e__ != cudaSuccess) {                                                             \
+      tsdf_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
+      return e__ == cudaErrorMemoryAllocation ? TSDF_E_NOMEM : TSDF_E_CUDA;               \
+    }                                                                                     \
+  } while (0)
+#define REQUIRE(cond, msg)                                  \
+  do {                                                      \
+    if (!(cond)) {                                          \
+      tsdf_set_error("%s: %s", __func__, msg);              \
+      return TSDF_E_INVALID;                                \
+    }                                                       \
+  } while (0)
+
+struct DeviceGuard {  // restores the caller's current device
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+// ---- kernel-side parameter blocks (passed by value => constant bank) ------------------
+constexpr int kMaxFusedFrames = 8;
+
+struct FrameP {       // one camera frame
+  float c[12];        // cam2base rows 0..2 (row-major 3x4), src/tsdf.cu:33-38
+  float fx, cx, fy, cy;  // K[0],K[2],K[4],K[5], src/tsdf.cu:41-42
+  float obs_weight;
+  int pad_;
+  const void* img;    // prepared frame: float depth[H*W]  or  uint2 {depth, packed colour}[H*W]
+};
+
+struct GridP {        // one volume slab
+  int n_fast;         // voxels along the fast (contiguous) axis of the slab
+  int n_mid;          // = dim_y
+  int n_slow;         // slow axis count of the slab
+  int z0;             // global z of local slice 0
+  float ox, oy, oz;   // origin (base frame)
+  float vs, trunc;
+  int W, H;
+  float* tsdf;
+  float* weight;
+  float* color;                  // may be null
+  unsigned long long* written;   // device counter (exact N_written)
+};
+
+struct BatchDesc {    // one active instance of a batched launch (lives in global memory)
+  GridP g;
+  FrameP f;
+  const uint8_t* mask;  // H*W 8-bit instance mask on the device, or null
+};
+
+// Prepared-frame pixel when colour is on: .x = depth bits (invalid canonicalised to 0.0f),
+// .y = packed colour as an exact small integer in fp32 bits (c2*65536+c1*256+c0).
+// Depth-only frames are a plain float image.
+
+// ---- host-side handle -------------------------------------------------------------------
+struct FrameSlot {
+  void* h_pinned = nullptr;   // staging for pageable inputs (depth + rgb)
+  void* d_raw = nullptr;      // raw upload target (depth fp32|u16 + rgb u8)
+  void* d_frame = nullptr;    // prepared frame consumed by the integrate kernel
+  cudaEvent_t uploaded = nullptr;  // recorded on the copy stream after prep
+  cudaEvent_t consumed = nullptr;  // recorded on the compute stream after integrate
+  bool in_flight = false;
+};
+
+struct tsdf_vol {
+  tsdf_config cfg;
+  int dzl = 0;                 // local slices
+  int64_t n_local = 0;         // voxels in this slab
+  bool zfast = false;          // FUSIONPY layout [x][y][zl]; else TSDFCU layout [zl][y][x]
+  bool identity_base = false;  // skip the host pose composition
+  float base2world_inv[16];
+  float* d_tsdf = nullptr;
+  float* d_weight = nullptr;
+  float* d_color = nullptr;
+  unsigned long long* d_written = nullptr;
+  unsigned long long* h_written = nullptr;  // pinned mirror
+  cudaStream_t s_compute = nullptr;
+  cudaStream_t s_copy = nullptr;
+  cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_u0 = nullptr, ev_u1 = nullptr;
+  // slots 0..2: single-frame ring; 3..3+2*kMaxFusedFrames: two groups for fused launches
+  FrameSlot slot[3 + kMaxFusedFrames * 2];
+  uint64_t seq = 0;            // single-frame submissions
+  uint64_t mseq = 0;           // fused submissions
+  int64_t frames = 0;
+  int64_t last_written = 0;
+  int64_t last_frames_in_launch = 1;
+  int variant = 0;
+  // state of the last launch, for tsdf_bench_kernel
+  FrameP last_frames[kMaxFusedFrames];
+  int last_nf = 0;
+  bool last_color = false;
+  // extraction scratch
+  void* d_scratch = nullptr;
+  size_t scratch_bytes = 0;
+};
+
+inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
+
+// ---- launchers implemented in the .cu files -----------------------------------------------
+// integrate.cu
+int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st);
+int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
+                           bool zfast, bool color, bool vec4, cudaStream_t st);
+// frame.cu
+int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
+                      const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
+                      bool with_color, void* d_frame, cudaStream_t st);
+int launch_fill(float* p, float val, int64_t n, cudaStream_t st);
+int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, int W, float fx,
+                           float cx, float fy, float cy, float* d_out3, cudaStream_t st);
+// extract.cu
+int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh, float* d_xyz,
+                   uint8_t* d_rgb, int64_t* d_idx, int64_t cap, int64_t* count);
+int ensure_scratch(tsdf_vol* v, size_t bytes);
+
+// api.cpp helpers used elsewhere
+int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);
+int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
+                      const void* d_frame, FrameP* out);
+int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
+                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot);

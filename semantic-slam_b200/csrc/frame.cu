@@ -1,0 +1,116 @@
+// frame.cu — frame upload companions: turns the raw upload (depth fp32|u16 + rgb u8x3)
+// into the "prepared frame" the integrate kernel gathers from, plus small utility kernels.
+//
+// Prepared frame:
+//   colour on : uint2 per pixel {depth bits, packed colour fp32 bits} -> ONE 64-bit gather
+//               per voxel instead of two 32-bit gathers
+//   colour off: float per pixel
+// Depth is canonicalised here: a sample failing the reference's validity test
+// `d <= 0 || d > max_depth` (src/tsdf.cu:46) is stored as 0.0f, so the hot loop needs a
+// single compare.  NaN fails neither test in the reference and is kept.
+// The packed colour is floor(c2*65536 + c1*256 + c0) (upstream fold); all values are
+// integers < 2^24, exact in fp32.
+// Optional per-instance mask: depth * (mask/255), i.e. depth kept where mask >= 128
+// (src/Engine.cpp:192-193; OpenCV 8-bit divide rounds to nearest).
+#include "common.cuh"
+
+namespace {
+
+__global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scale, int sub_c,
+                             int sub_r, const uint8_t* __restrict__ rgb,
+                             const uint8_t* __restrict__ mask, int H, int W, float max_depth,
+                             bool with_color, void* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= H * W) return;
+  float d;
+  if (fmt == TSDF_DEPTH_U16) d = (float)reinterpret_cast<const uint16_t*>(depth)[i] * scale;
+  else                       d = reinterpret_cast<const float*>(depth)[i] * scale;
+  if (sub_c > 1 || sub_r > 1) {  // examples/label_instance_rgbd.cpp:89-97
+    int r = i / W, c = i - r * W;
+    if ((c % sub_c) != 0 || (r % sub_r) != 0) d = 0.0f;
+  }
+  if (mask) d = d * (mask[i] >= 128 ? 1.0f : 0.0f);
+  if (d <= 0.0f || d > max_depth) d = 0.0f;
+  if (with_color) {
+    float pc = 0.0f;
+    if (rgb) pc = floorf((float)rgb[3 * i + 2] * 65536.0f + (float)rgb[3 * i + 1] * 256.0f +
+                         (float)rgb[3 * i + 0]);
+    reinterpret_cast<uint2*>(out)[i] = make_uint2(__float_as_uint(d), __float_as_uint(pc));
+  } else {
+    reinterpret_cast<float*>(out)[i] = d;
+  }
+}
+
+__global__ void k_fill(float* __restrict__ p, float val, int64_t n) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  // 128-bit body, scalar tail
+  int64_t n4 = n >> 2;
+  float4 v4 = make_float4(val, val, val, val);
+  for (int64_t k = i; k < n4; k += stride) reinterpret_cast<float4*>(p)[k] = v4;
+  for (int64_t k = (n4 << 2) + i; k < n; k += stride) p[k] = val;
+}
+
+// Per-instance origin (K9): min over valid masked pixels of the back-projected x, y, z.
+// src/Object.cpp:37-49.  fmin of floats is order independent, so a parallel reduction is
+// bit-identical to the reference's serial scan.
+__global__ void k_instance_origin(const float* __restrict__ depth, const uint8_t* __restrict__ mask,
+                                  int H, int W, float cx, float cy, float ifx, float ify,
+                                  float* __restrict__ out3) {
+  float mx = 1000.0f, my = 1000.0f, mz = 1000.0f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < H * W; i += gridDim.x * blockDim.x) {
+    float z = depth[i];
+    if (mask) z = z * (mask[i] >= 128 ? 1.0f : 0.0f);
+    if (z <= 0.0f) continue;
+    int r = i / W, c = i - r * W;
+    float x = ((float)c - cx) * z * ifx;
+    float y = ((float)r - cy) * z * ify;
+    mx = x < mx ? x : mx;
+    my = y < my ? y : my;
+    mz = z < mz ? z : mz;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mx = fminf(mx, __shfl_down_sync(0xffffffffu, mx, o));
+    my = fminf(my, __shfl_down_sync(0xffffffffu, my, o));
+    mz = fminf(mz, __shfl_down_sync(0xffffffffu, mz, o));
+  }
+  if ((threadIdx.x & 31) == 0) {
+    // positive-float ordering == signed-int ordering only for non-negative values; use the
+    // sign-aware trick: atomicMin on int for >=0, atomicMax on uint for <0
+    auto amin = [](float* addr, float v) {
+      if (v >= 0.0f) atomicMin(reinterpret_cast<int*>(addr), __float_as_int(v));
+      else atomicMax(reinterpret_cast<unsigned int*>(addr), __float_as_uint(v));
+    };
+    amin(out3 + 0, mx);
+    amin(out3 + 1, my);
+    amin(out3 + 2, mz);
+  }
+}
+
+}  // namespace
+
+int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
+                      const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
+                      bool with_color, void* d_frame, cudaStream_t st) {
+  int n = H * W;
+  k_frame_prep<<<(n + 255) / 256, 256, 0, st>>>(d_depth, depth_fmt, depth_scale, sub_c, sub_r, d_rgb,
+                                                d_mask, H, W, max_depth, with_color, d_frame);
+  CU_CHECK(cudaGetLastError());
+  return TSDF_OK;
+}
+
+int launch_fill(float* p, float val, int64_t n, cudaStream_t st) {
+  if (n <= 0) return TSDF_OK;
+  k_fill<<<148 * 8, 256, 0, st>>>(p, val, n);
+  CU_CHECK(cudaGetLastError());
+  return TSDF_OK;
+}
+
+int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, int W, float fx,
+                           float cx, float fy, float cy, float* d_out3, cudaStream_t st) {
+  const float init[3] = {1000.0f, 1000.0f, 1000.0f};
+  CU_CHECK(cudaMemcpyAsync(d_out3, init, sizeof(init), cudaMemcpyHostToDevice, st));
+  k_instance_origin<<<148, 256, 0, st>>>(d_depth, d_mask, H, W, cx, cy, 1.0f / fx, 1.0f / fy, d_out3);
+  CU_CHECK(cudaGetLastError());
+  return TSDF_OK;
+}

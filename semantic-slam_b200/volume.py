@@ -1,0 +1,302 @@
+"""Host-side mirror of the reference's operator surface for the TSDF hot path, over the C ABI.
+
+  Volume      thin RAII wrapper of a `tsdf_vol*` handle (one grid or one z-slab on one GPU)
+  TSDF        mirrors class TSDF (reference include/tsdf.hpp:22-98): TSDF(h, w, id,
+              base2world, origin), Integrate(depth, cam2world), host mirrors
+              voxel_grid_TSDF / voxel_grid_weight, and the destructor's .ply/.bin dump
+              (src/tsdf.cu:98-133) as close()
+  TSDFVolume  mirrors the plugin surface reached through class TSDFfusion
+              (src/TSDFfusion.py.in:21-53 -> fusion.TSDFVolume): TSDFVolume(vol_bnds,
+              voxel_size), integrate(color_im, depth_im, cam_intr, cam_pose, obs_weight),
+              get_volume(), get_point_cloud()
+
+All compute happens in libtsdf_b200.so on the GPU; nothing here computes a voxel.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import (Config, Stats, check, f32, ptr, SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO,
+                   PRED_ABS_LT, DEPTH_F32, DEPTH_U16)
+
+
+def default_config():
+    cfg = Config()
+    capi.load().tsdf_config_default(C.byref(cfg))
+    return cfg
+
+
+def config_from_bounds(vol_bnds, voxel_size):
+    cfg = Config()
+    b = (C.c_double * 6)(*np.asarray(vol_bnds, np.float64).reshape(6))
+    check(capi.load().tsdf_config_from_bounds(b, float(voxel_size), C.byref(cfg)))
+    return cfg
+
+
+def make_config(dims, voxel_size, origin, semantics=SEM_FUSIONPY, with_color=True, trunc=None,
+                im_hw=(480, 640), K=None, max_depth=None, base2world=None, device=0, z_range=None,
+                vol_id=0):
+    cfg = default_config()
+    cfg.dim_x, cfg.dim_y, cfg.dim_z = [int(d) for d in dims]
+    cfg.voxel_size = np.float32(voxel_size)
+    cfg.trunc_margin = np.float32(trunc) if trunc is not None else np.float32(np.float32(voxel_size) * np.float32(5))
+    cfg.origin[:] = [float(np.float32(o)) for o in origin]
+    cfg.im_h, cfg.im_w = int(im_hw[0]), int(im_hw[1])
+    if K is not None:
+        cfg.K[:] = [float(k) for k in np.asarray(K, np.float32).reshape(9)]
+    if max_depth is None:
+        max_depth = 6.0 if semantics == SEM_TSDFCU else np.inf
+    cfg.max_depth = np.float32(max_depth)
+    cfg.semantics = int(semantics)
+    cfg.with_color = int(bool(with_color))
+    if base2world is not None:
+        cfg.base2world[:] = [float(x) for x in np.asarray(base2world, np.float32).reshape(16)]
+    cfg.device = int(device)
+    if z_range is not None:
+        cfg.z_begin, cfg.z_end = int(z_range[0]), int(z_range[1])
+    cfg.id = int(vol_id)
+    return cfg
+
+
+def slab_range(dim_z, nranks, rank):
+    a, b = C.c_int(0), C.c_int(0)
+    capi.load().tsdf_slab_range(int(dim_z), int(nranks), int(rank), C.byref(a), C.byref(b))
+    return a.value, b.value
+
+
+def device_count():
+    n = C.c_int(0)
+    rc = capi.load().tsdf_device_count(C.byref(n))
+    return n.value if rc == capi.OK else 0
+
+
+class Volume:
+    """One `tsdf_vol*`.  Arrays returned by download() are in the semantics' reference order
+    (TSDFCU: [z][y][x]; FUSIONPY: [x][y][z]) restricted to this handle's z-slab."""
+
+    def __init__(self, cfg):
+        self.lib = capi.load()
+        self.h = C.c_void_p()
+        check(self.lib.tsdf_create(C.byref(cfg), C.byref(self.h)))
+        self.cfg = Config()
+        check(self.lib.tsdf_get_config(self.h, C.byref(self.cfg)))
+        self._keep = []  # keeps borrowed input arrays alive until sync()
+
+    # -- lifecycle --------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.tsdf_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def reset(self):
+        check(self.lib.tsdf_reset(self.h))
+
+    # -- shape helpers ------------------------------------------------------------------
+    @property
+    def dims(self):
+        return (self.cfg.dim_x, self.cfg.dim_y, self.cfg.dim_z)
+
+    @property
+    def dz_local(self):
+        return self.cfg.z_end - self.cfg.z_begin
+
+    @property
+    def n_local(self):
+        return self.cfg.dim_x * self.cfg.dim_y * self.dz_local
+
+    def local_shape(self):
+        if self.cfg.semantics == SEM_TSDFCU:
+            return (self.dz_local, self.cfg.dim_y, self.cfg.dim_x)
+        return (self.cfg.dim_x, self.cfg.dim_y, self.dz_local)
+
+    # -- integration -------------------------------------------------------------------
+    def _frame_args(self, depth, rgb, K, T_wc, dtype=np.float32):
+        H, W = self.cfg.im_h, self.cfg.im_w
+        if not isinstance(depth, (int, np.integer)):
+            depth = np.ascontiguousarray(depth, dtype)
+            assert depth.size == H * W, "depth shape mismatch"
+        if rgb is not None and not isinstance(rgb, (int, np.integer)):
+            rgb = np.ascontiguousarray(rgb, np.uint8)
+            assert rgb.size == H * W * 3, "rgb shape mismatch"
+        Kc = None if K is None else f32(K, 9)
+        T = f32(T_wc, 16)
+        self._keep.append((depth, rgb, Kc, T))
+        return depth, rgb, Kc, T
+
+    def integrate(self, depth, rgb, T_wc, K=None, obs_weight=1.0, sync=True):
+        depth, rgb, Kc, T = self._frame_args(depth, rgb, K, T_wc)
+        fn = self.lib.tsdf_integrate if sync else self.lib.tsdf_integrate_async
+        check(fn(self.h, ptr(depth), ptr(rgb), ptr(Kc), ptr(T), np.float32(obs_weight)))
+        if sync:
+            self._keep.clear()
+
+    def integrate_raw(self, depth_u16, depth_scale, rgb, T_wc, K=None, obs_weight=1.0, subsample=(1, 1)):
+        depth, rgb, Kc, T = self._frame_args(depth_u16, rgb, K, T_wc, dtype=np.uint16)
+        check(self.lib.tsdf_integrate_raw_async(self.h, ptr(depth), DEPTH_U16, np.float32(depth_scale),
+                                                int(subsample[0]), int(subsample[1]), ptr(rgb), ptr(Kc),
+                                                ptr(T), np.float32(obs_weight)))
+        self.sync()
+
+    def integrate_multi(self, depths, rgbs, T_wcs, K=None, obs_weight=1.0, sync=True):
+        k = len(T_wcs)
+        d = np.ascontiguousarray(np.stack([np.asarray(x, np.float32) for x in depths]))
+        c = None if rgbs is None else np.ascontiguousarray(np.stack([np.asarray(x, np.uint8) for x in rgbs]))
+        T = np.ascontiguousarray(np.stack([f32(t, 16) for t in T_wcs]))
+        Kc = None if K is None else f32(K, 9)
+        self._keep.append((d, c, T, Kc))
+        check(self.lib.tsdf_integrate_multi_async(self.h, k, ptr(d), ptr(c), ptr(Kc), ptr(T), np.float32(obs_weight)))
+        if sync:
+            self.sync()
+
+    def sync(self):
+        check(self.lib.tsdf_sync(self.h))
+        self._keep.clear()
+
+    def stats(self):
+        s = Stats()
+        check(self.lib.tsdf_get_stats(self.h, C.byref(s)))
+        self._keep.clear()
+        return s
+
+    def bench_kernel(self, iters):
+        ms = C.c_float(0)
+        check(self.lib.tsdf_bench_kernel(self.h, int(iters), C.byref(ms)))
+        return ms.value
+
+    def set_variant(self, variant):
+        check(self.lib.tsdf_set_variant(self.h, int(variant)))
+
+    # -- readback ------------------------------------------------------------------------
+    def download(self, want_color=None):
+        n = self.n_local
+        t = np.empty(n, np.float32)
+        w = np.empty(n, np.float32)
+        has_c = bool(self.cfg.with_color) if want_color is None else want_color
+        c = np.empty(n, np.float32) if has_c else None
+        check(self.lib.tsdf_download(self.h, ptr(t), ptr(w), ptr(c), 0))
+        return t, w, c
+
+    def download_into(self, tsdf, weight, color):
+        """Scatter this slab into GLOBAL host arrays (global_layout=1)."""
+        check(self.lib.tsdf_download(self.h, ptr(tsdf), ptr(weight), ptr(color), 1))
+
+    def upload(self, tsdf=None, weight=None, color=None, global_layout=False):
+        a = [None if x is None else f32(x) for x in (tsdf, weight, color)]
+        check(self.lib.tsdf_upload(self.h, ptr(a[0]), ptr(a[1]), ptr(a[2]), int(global_layout)))
+
+    def extract_count(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
+        n = C.c_int64(0)
+        check(self.lib.tsdf_extract_points(self.h, pred, np.float32(tsdf_thresh), np.float32(weight_thresh),
+                                           None, None, None, 0, C.byref(n)))
+        return n.value
+
+    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
+        n = self.extract_count(pred, tsdf_thresh, weight_thresh)
+        xyz = np.zeros((max(n, 1), 3), np.float32)
+        rgb = np.zeros((max(n, 1), 3), np.uint8)
+        idx = np.zeros(max(n, 1), np.int64)
+        cnt = C.c_int64(0)
+        check(self.lib.tsdf_extract_points(self.h, pred, np.float32(tsdf_thresh), np.float32(weight_thresh),
+                                           ptr(xyz), ptr(rgb), ptr(idx), n, C.byref(cnt)))
+        assert cnt.value == n
+        return xyz[:n], rgb[:n], idx[:n]
+
+    def save_ply(self, path, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
+        check(self.lib.tsdf_save_ply(self.h, path.encode(), pred, np.float32(tsdf_thresh), np.float32(weight_thresh)))
+
+    def save_bin(self, path):
+        check(self.lib.tsdf_save_bin(self.h, path.encode()))
+
+    def load_bin(self, path):
+        check(self.lib.tsdf_load_bin(self.h, path.encode()))
+
+
+class TSDF:
+    """Mirror of the reference's `class TSDF` (include/tsdf.hpp:22-98).
+
+    TSDF(h, w, id, base2world_vec, origin): 200^3 grid, 4 mm voxels, trunc = 5 voxels, TUM3
+    intrinsics (include/tsdf.hpp:63-67,96).  Integrate(depth_im, cam2world_vec) as
+    src/tsdf.cu:135-168.  The reference refreshes its public host mirrors only in the
+    destructor (src/tsdf.cu:101-104); here `refresh()` does it on demand and `close()`
+    reproduces the destructor: download, tsdf<id>.ply, tsdf<id>.bin (src/tsdf.cu:98-133)."""
+
+    def __init__(self, h, w, id, base2world_vec, origin, device=0, dims=(200, 200, 200),
+                 voxel_size=0.004):
+        cfg = make_config(dims, voxel_size, origin, semantics=SEM_TSDFCU, with_color=False,
+                          im_hw=(h, w), base2world=base2world_vec, device=device, vol_id=id)
+        self.vol = Volume(cfg)
+        self.mnId = int(id)
+        n = self.vol.n_local
+        self.voxel_grid_TSDF = np.ones(n, np.float32)    # src/tsdf.cu:79-80
+        self.voxel_grid_weight = np.zeros(n, np.float32)  # src/tsdf.cu:81
+
+    def Integrate(self, depth_im, cam2world_vec):
+        self.vol.integrate(depth_im, None, cam2world_vec, obs_weight=1.0, sync=False)
+
+    def refresh(self):
+        t, w, _ = self.vol.download(want_color=False)
+        self.voxel_grid_TSDF[:] = t
+        self.voxel_grid_weight[:] = w
+
+    def close(self, out_dir=None):
+        if self.vol is None:
+            return
+        self.refresh()
+        if out_dir is not None:
+            self.vol.save_ply(f"{out_dir}/tsdf{self.mnId}.ply", PRED_NONZERO, 1.2, 0.9)  # src/tsdf.cu:109-112
+            self.vol.save_bin(f"{out_dir}/tsdf{self.mnId}.bin")                           # src/tsdf.cu:116-132
+        self.vol.close()
+        self.vol = None
+
+
+class TSDFVolume:
+    """Mirror of the plugin surface (`fusion.TSDFVolume` as driven by src/TSDFfusion.py.in).
+
+    vol_bnds: 3x2 [[xmin,xmax],[ymin,ymax],[zmin,zmax]] in metres; dims = ceil(extent/voxel_size),
+    trunc = 5*voxel_size, origin = mins (src/TSDFfusion.py.in:23-29)."""
+
+    def __init__(self, vol_bnds, voxel_size, device=0, im_hw=(480, 640), z_range=None):
+        cfg = config_from_bounds(vol_bnds, voxel_size)
+        cfg.device = int(device)
+        cfg.im_h, cfg.im_w = int(im_hw[0]), int(im_hw[1])
+        if z_range is not None:
+            cfg.z_begin, cfg.z_end = int(z_range[0]), int(z_range[1])
+        self.vol = Volume(cfg)
+        self._vol_dim = np.array(self.vol.dims)
+        self._voxel_size = float(voxel_size)
+        self._trunc_margin = float(self.vol.cfg.trunc_margin)
+        self._vol_origin = np.array(self.vol.cfg.origin[:], np.float32)
+
+    def integrate(self, color_im, depth_im, cam_intr, cam_pose, obs_weight=1.0):
+        """src/TSDFfusion.py.in:43 — integrate(color HxWx3 u8, depth HxW m, K 3x3, T_wc 4x4)."""
+        self.vol.integrate(depth_im, color_im, cam_pose, K=cam_intr, obs_weight=obs_weight, sync=False)
+
+    def get_volume(self):
+        t, w, c = self.vol.download()
+        shp = self.vol.local_shape()
+        return t.reshape(shp), c.reshape(shp)
+
+    def get_weights(self):
+        return self.vol.download()[1].reshape(self.vol.local_shape())
+
+    def get_point_cloud(self, tsdf_thresh=1.2, weight_thresh=0.9, pred=PRED_NONZERO):
+        """Headless replacement of the mesh/viewer readback (src/TSDFfusion.py.in:48-53;
+        viewers are unavailable on this box): xyz + rgb of the kept voxels."""
+        xyz, rgb, _ = self.vol.extract_points(pred, tsdf_thresh, weight_thresh)
+        return xyz, rgb
+
+    def close(self):
+        self.vol.close()

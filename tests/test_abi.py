@@ -1,0 +1,117 @@
+"""CPU tests of the drop-in boundary: the library loads, exports every symbol declared in
+include/tsdf_b200.h, the host-only entry points behave, and compute entry points fail LOUDLY
+(no CPU fallback) when there is no device."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+from conftest import ROOT, bits
+
+
+def header_functions():
+    src = open(os.path.join(ROOT, "include", "tsdf_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(tsdf_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol(pkg):
+    lib = pkg.load()
+    names = header_functions()
+    assert len(names) >= 45
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in include/tsdf_b200.h but not exported"
+    assert set(names) == set(pkg.capi.SIGNATURES), "ctypes stub and header disagree"
+    assert lib.tsdf_version() == 100
+
+
+def test_config_struct_layout(pkg):
+    assert C.sizeof(pkg.capi.Config) == 4 * (3 + 2 + 3 + 16 + 2 + 9 + 1 + 3 + 2 + 1 + 7)
+    cfg = pkg.default_config()
+    assert (cfg.dim_x, cfg.dim_y, cfg.dim_z) == (200, 200, 200)          # include/tsdf.hpp:65-67
+    assert cfg.voxel_size == np.float32(0.004)                            # include/tsdf.hpp:63
+    assert cfg.trunc_margin == np.float32(0.004) * np.float32(5)          # include/tsdf.hpp:64
+    assert list(cfg.K)[:6] == [np.float32(v) for v in (535.4, 0, 320.1, 0, 539.2, 247.6)]
+    assert cfg.max_depth == 6.0 and (cfg.im_h, cfg.im_w) == (480, 640)
+
+
+def test_config_from_bounds_follows_fusion_rule(pkg):
+    cfg = pkg.config_from_bounds([[0, 10], [0, 10], [0, 10]], 0.02)       # src/TSDFfusion.py.in:23-29
+    assert (cfg.dim_x, cfg.dim_y, cfg.dim_z) == (500, 500, 500)
+    assert cfg.trunc_margin == np.float32(0.02 * 5) and cfg.semantics == pkg.SEM_FUSIONPY
+    cfg = pkg.config_from_bounds([[-1.03, 2.0], [0.5, 0.77], [3, 3.001]], 0.05)
+    ext = np.array([3.03, 0.27, 0.001])
+    assert [cfg.dim_x, cfg.dim_y, cfg.dim_z] == list(np.ceil(ext / 0.05).astype(int))
+    assert list(cfg.origin) == [np.float32(-1.03), np.float32(0.5), np.float32(3)]
+    with pytest.raises(pkg.TsdfError):
+        pkg.config_from_bounds([[0, 0], [0, 1], [0, 1]], 0.05)
+
+
+def test_host_matrix_helpers_match_oracle(pkg, oracle, synth):
+    lib = pkg.load()
+    rng = np.random.default_rng(2)
+    for i in range(500):
+        A = synth.pose(synth.rot_xyz(*rng.uniform(-3, 3, 3)), rng.uniform(-5, 5, 3)).reshape(16)
+        B = rng.normal(size=16).astype(np.float32)
+        out = np.zeros(16, np.float32)
+        lib.tsdf_multiply_matrix(A.ctypes.data, B.ctypes.data, out.ctypes.data)
+        assert np.array_equal(bits(out), bits(oracle.multiply(A, B)))
+        M = A if i % 2 else B
+        rc = lib.tsdf_invert_matrix(M.ctypes.data, out.ctypes.data)
+        ref = oracle.invert(M)
+        assert (rc != 0) == (ref is None)
+        if ref is not None:
+            assert np.array_equal(bits(out), bits(ref))
+    Z = np.zeros(16, np.float32)
+    assert lib.tsdf_invert_matrix(Z.ctypes.data, out.ctypes.data) == pkg.capi.E_SINGULAR
+
+
+def test_slab_ranges_partition_the_grid(pkg):
+    for dz in (1024, 256, 200, 130, 7):
+        for n in (1, 2, 3, 4, 8):
+            r = [pkg.slab_range(dz, n, k) for k in range(n)]
+            assert r[0][0] == 0 and r[-1][1] == dz
+            for a, b in zip(r, r[1:]):
+                assert a[1] == b[0]
+            assert all(z0 % 4 == 0 for z0, z1 in r if z1 > z0)
+    assert [pkg.slab_range(1024, 8, k) for k in range(8)] == [(128 * k, 128 * k + 128) for k in range(8)]
+
+
+def test_invalid_configs_are_rejected(pkg):
+    cfg = pkg.default_config()
+    cfg.dim_x = 0
+    with pytest.raises(pkg.TsdfError) as e:
+        pkg.Volume(cfg)
+    assert e.value.code in (pkg.capi.E_INVALID, pkg.capi.E_NODEVICE)
+
+
+def test_no_cpu_fallback(pkg):
+    """Without a device every compute entry point must fail loudly."""
+    if pkg.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(pkg.TsdfError) as e:
+        pkg.Volume(pkg.default_config())
+    assert e.value.code == pkg.capi.E_NODEVICE
+    out = np.zeros(3, np.float32)
+    d = np.ones((4, 4), np.float32)
+    K = pkg.synth.TUM3_K
+    rc = pkg.load().tsdf_instance_origin(0, d.ctypes.data, None, 4, 4, K.ctypes.data, out.ctypes.data)
+    assert rc == pkg.capi.E_NODEVICE
+
+
+def test_product_does_not_import_oracle():
+    """The product path must never route through oracle/ (test infrastructure)."""
+    pk = os.path.join(ROOT, "semantic-slam_b200")
+    for dirpath, _, files in os.walk(pk):
+        for f in files:
+            path = os.path.join(dirpath, f)
+            if f.endswith(".py"):
+                txt = open(path).read()
+                assert not re.search(r"^\s*(from|import)\s+oracle", txt, flags=re.M), f"{f} imports oracle"
+                assert "liboracle" not in txt and "_ref" not in txt, f"{f} loads oracle artefacts"
+            elif f.endswith((".cu", ".cuh", ".cpp", ".h", ".hpp")) or f == "Makefile":
+                txt = open(path, errors="replace").read()
+                assert not re.search(r"#include\s+[\"<][^\">]*oracle", txt), f"{f} includes oracle code"
+                assert "liboracle" not in txt and "libtsdf_ref" not in txt, f"{f} links oracle artefacts"

@@ -1,0 +1,114 @@
+"""CPU tests of the oracle: pinned against the golden vectors made from the reference's own
+source lines (tests/golden/make_golden.py), and against oracle/_ref itself when present."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import bits
+from oracle.oracle import Oracle, RefLift, ref_available, SEM_TSDFCU, SEM_FUSIONPY, PRED_ABS_LT
+
+
+def run_cu(o, g):
+    dims, vs, hw, K = tuple(g["dims"]), float(g["vs"]), tuple(g["hw"]), g["K"]
+    trunc = np.float32(vs) * np.float32(5)
+    p = o.params(dims, vs, trunc, g["origin"], hw, K, 6.0, SEM_TSDFCU)
+    t, w, _ = o.new_volume(p)
+    for d, T, c2b in zip(g["depth"], g["T_wc"], g["cam2base"]):
+        mine = o.compose(g["base2world"], T)
+        assert np.array_equal(bits(mine), bits(c2b)), "pose composition differs from the reference"
+        o.integrate(p, mine, d, None, 1.0, t, w, None)
+    return p, t, w
+
+
+def test_oracle_matches_reference_golden(oracle, golden_cu, tmp_path):
+    p, t, w = run_cu(oracle, golden_cu)
+    assert np.array_equal(w, golden_cu["weight"])
+    assert np.array_equal(bits(t), bits(golden_cu["tsdf"]))
+    path = str(tmp_path / "o.ply")
+    assert oracle.save_ply(path, p, t, w)
+    assert np.array_equal(np.frombuffer(open(path, "rb").read(), np.uint8), golden_cu["ply"])
+
+
+def test_oracle_fusionpy_regression(oracle, golden_cu, golden_py):
+    g = golden_cu
+    dims, vs, hw, K = tuple(g["dims"]), float(g["vs"]), tuple(g["hw"]), g["K"]
+    p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), g["origin"], hw, K, np.inf, SEM_FUSIONPY)
+    t, w, c = oracle.new_volume(p, True)
+    for d, rgb, T in zip(g["depth"], g["rgb"], g["T_wc"]):
+        oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb), float(golden_py["obs_weight"]), t, w, c)
+    assert np.array_equal(w, golden_py["weight"]) and np.array_equal(bits(t), bits(golden_py["tsdf"]))
+    assert np.array_equal(c, golden_py["color"])
+    xyz, rgb, idx = oracle.extract(p, t, w, c)
+    assert np.array_equal(idx, golden_py["idx"]) and np.array_equal(rgb, golden_py["rgb"])
+
+
+@pytest.mark.skipif(not ref_available(), reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_oracle_vs_reference_lift_random(oracle, synth):
+    r = RefLift()
+    rng = np.random.default_rng(7)
+    for i in range(300):
+        T = synth.pose(synth.rot_xyz(*rng.uniform(-3, 3, 3)), rng.uniform(-5, 5, 3))
+        if i % 3 == 0:
+            T = rng.normal(size=(4, 4)).astype(np.float32)
+        a, b = oracle.invert(T), r.invert(T)
+        assert (a is None and b is None) or np.array_equal(bits(a), bits(b))
+        T2 = rng.normal(size=(4, 4)).astype(np.float32)
+        assert np.array_equal(bits(oracle.multiply(T, T2)), bits(r.multiply(T, T2)))
+    dims, vs = (50, 44, 38), 0.03          # odd sizes on purpose
+    origin, frames = synth.s_real(dims, vs, n_frames=4, seed=11)
+    p = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, SEM_TSDFCU)
+    t, w, _ = oracle.new_volume(p)
+    t2, w2 = np.ones_like(t), np.zeros_like(w)
+    base = frames[1][2]
+    for d, _, T in frames:
+        c2b = oracle.compose(base, T)
+        oracle.integrate(p, c2b, d, None, 1.0, t, w, None)
+        r.integrate(synth.TUM3_K, c2b, d, dims, origin, vs, 5 * vs, t2, w2)
+    assert w.max() >= 2 and np.array_equal(w, w2) and np.array_equal(bits(t), bits(t2))
+
+
+def test_oracle_slabs_equal_whole(oracle, synth):
+    dims, vs = (32, 24, 40), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=3)
+    for sem in (SEM_TSDFCU, SEM_FUSIONPY):
+        p = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, sem)
+        t, w, c = oracle.new_volume(p, True)
+        for d, rgb, T in frames:
+            oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb), 1.0, t, w, c)
+        shape = (dims[2], dims[1], dims[0]) if sem == SEM_TSDFCU else dims
+        zax = 0 if sem == SEM_TSDFCU else 2
+        parts = []
+        for z0, z1 in ((0, 12), (12, 28), (28, 40)):
+            ps = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, sem, (z0, z1))
+            ts, ws, cs = oracle.new_volume(ps, True)
+            for d, rgb, T in frames:
+                oracle.integrate(ps, T.reshape(16), d, oracle.pack_color(rgb), 1.0, ts, ws, cs)
+            lshape = list(shape)
+            lshape[zax] = z1 - z0
+            parts.append(ws.reshape(lshape))
+        assert np.array_equal(np.concatenate(parts, axis=zax), w.reshape(shape))
+
+
+def test_oracle_extract_predicates_and_origin(oracle, synth):
+    dims, vs = (24, 24, 24), 0.05
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=5)
+    p = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, SEM_TSDFCU)
+    t, w, _ = oracle.new_volume(p)
+    for d, _, T in frames:
+        oracle.integrate(p, T.reshape(16), d, None, 1.0, t, w, None)
+    _, _, idx = oracle.extract(p, t, w, None)
+    assert np.array_equal(idx, np.flatnonzero((np.abs(t) != 0) & (w > np.float32(0.9))))
+    _, _, idx2 = oracle.extract(p, t, w, None, PRED_ABS_LT, 0.5, 0.9)
+    assert np.array_equal(idx2, np.flatnonzero((np.abs(t) < np.float32(0.5)) & (w > np.float32(0.9))))
+    d = frames[0][0]
+    mask = np.zeros(d.shape, np.uint8)
+    mask[100:200, 300:400] = 255
+    og = oracle.instance_origin(d, mask, synth.TUM3_K)
+    v, u = np.mgrid[0:d.shape[0], 0:d.shape[1]]
+    z = np.where(mask >= 128, d, 0).astype(np.float32)
+    ok = z > 0
+    K = synth.TUM3_K
+    x = ((u.astype(np.float32) - K[2]) * z * (np.float32(1) / K[0]))[ok]
+    y = ((v.astype(np.float32) - K[5]) * z * (np.float32(1) / K[4]))[ok]
+    assert np.allclose(og, [x.min(), y.min(), z[ok].min()], rtol=0, atol=0)

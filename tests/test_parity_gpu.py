@@ -1,0 +1,347 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against the CPU oracle on the same
+seeded inputs, against the committed golden vectors, and — at BASELINE sizes — through
+size-independent properties.  Bar (BASELINE.json north_star): weights and extracted index
+sets bit-exact; tsdf and colour within 1e-5 abs.  The implementation is in fact bit-exact on
+tsdf too, and the tests assert that (any non-zero diff is a bug signal)."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import bits
+from oracle.oracle import SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO, PRED_ABS_LT
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5  # north_star tolerance for tsdf / colour
+
+
+def oracle_run(oracle, dims, vs, origin, frames, sem, color, obs=1.0, base=None, K=None, hw=None,
+               max_depth=None, z_range=None, trunc=None):
+    K = K if K is not None else np.array([535.4, 0, 320.1, 0, 539.2, 247.6, 0, 0, 1], np.float32)
+    hw = hw or frames[0][0].shape
+    if max_depth is None:
+        max_depth = 6.0 if sem == SEM_TSDFCU else np.inf
+    trunc = trunc if trunc is not None else np.float32(vs) * np.float32(5)
+    p = oracle.params(dims, vs, trunc, origin, hw, K, max_depth, sem, z_range)
+    t, w, c = oracle.new_volume(p, color)
+    written = []
+    for d, rgb, T in frames:
+        c2b = T.reshape(16) if base is None else oracle.compose(base, T)
+        written.append(oracle.integrate(p, c2b, d, oracle.pack_color(rgb) if color else None, obs, t, w, c))
+    return p, t, w, c, written
+
+
+def assert_volume_equal(gt, gw, gc, t, w, c):
+    assert np.array_equal(gw, w), f"weights differ at {np.flatnonzero(gw != w)[:5]}"
+    assert np.max(np.abs(gt - t), initial=0) <= TOL
+    assert np.array_equal(bits(gt), bits(t)), "tsdf not bit-exact"
+    if c is not None:
+        assert np.max(np.abs(gc - c), initial=0) <= TOL, "colour differs"
+
+
+@pytest.mark.parametrize("sem,color", [(SEM_TSDFCU, False), (SEM_FUSIONPY, True), (SEM_FUSIONPY, False)])
+@pytest.mark.parametrize("dims", [(64, 48, 64), (50, 44, 38), (33, 17, 21), (128, 8, 260)])
+def test_integrate_matches_oracle(pkg, oracle, synth, sem, color, dims):
+    vs = 0.03
+    origin, frames = synth.s_real(dims, vs, n_frames=4, seed=21)
+    base = frames[1][2] if sem == SEM_TSDFCU else None
+    obs = 1.0 if sem == SEM_TSDFCU else 0.5
+    p, t, w, c, written = oracle_run(oracle, dims, vs, origin, frames, sem, color, obs, base)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, base2world=base)
+    with pkg.Volume(cfg) as vol:
+        for (d, rgb, T), ow in zip(frames, written):
+            vol.integrate(d, rgb if color else None, T, obs_weight=obs)
+            st = vol.stats()
+            assert st.voxels_written == ow and st.voxels_visited == vol.n_local
+        gt, gw, gc = vol.download()
+    assert sum(written) > 0
+    assert_volume_equal(gt, gw, gc, t, w, c)
+
+
+def test_golden_vectors_from_reference_lines(pkg, golden_cu, tmp_path):
+    """CUDA path vs outputs of the reference's own src/tsdf.cu lines (tests/golden)."""
+    g = golden_cu
+    dims, vs, hw = tuple(int(x) for x in g["dims"]), float(g["vs"]), tuple(int(x) for x in g["hw"])
+    cfg = pkg.make_config(dims, vs, g["origin"], semantics=SEM_TSDFCU, with_color=False, im_hw=hw,
+                          K=g["K"], base2world=g["base2world"], vol_id=7)
+    with pkg.Volume(cfg) as vol:
+        for d, T in zip(g["depth"], g["T_wc"]):
+            vol.integrate(d, None, T)
+        gt, gw, _ = vol.download()
+        ply, binf = str(tmp_path / "tsdf7.ply"), str(tmp_path / "tsdf7.bin")
+        vol.save_ply(ply, PRED_NONZERO, 1.2, 0.9)
+        vol.save_bin(binf)
+    assert np.array_equal(gw, g["weight"]) and np.array_equal(bits(gt), bits(g["tsdf"]))
+    assert np.array_equal(np.frombuffer(open(ply, "rb").read(), np.uint8), g["ply"])  # byte-compatible PLY
+    raw = np.fromfile(binf, np.float32)
+    assert list(raw[:3]) == list(map(float, dims)) and np.array_equal(bits(raw[8:]), bits(g["tsdf"]))
+    assert raw[6] == np.float32(vs) and raw[7] == np.float32(vs) * np.float32(5)
+
+
+def test_golden_fusionpy_regression(pkg, golden_cu, golden_py):
+    g = golden_cu
+    dims, vs, hw = tuple(int(x) for x in g["dims"]), float(g["vs"]), tuple(int(x) for x in g["hw"])
+    cfg = pkg.make_config(dims, vs, g["origin"], semantics=SEM_FUSIONPY, with_color=True, im_hw=hw, K=g["K"])
+    with pkg.Volume(cfg) as vol:
+        for d, rgb, T in zip(g["depth"], g["rgb"], g["T_wc"]):
+            vol.integrate(d, rgb, T, obs_weight=float(golden_py["obs_weight"]))
+        gt, gw, gc = vol.download()
+        xyz, rgb, idx = vol.extract_points()
+    assert_volume_equal(gt, gw, gc, golden_py["tsdf"], golden_py["weight"], golden_py["color"])
+    assert np.array_equal(idx, golden_py["idx"]) and np.array_equal(rgb, golden_py["rgb"])
+    assert np.array_equal(bits(xyz), bits(golden_py["xyz"]))
+
+
+@pytest.mark.parametrize("sem", [SEM_TSDFCU, SEM_FUSIONPY])
+def test_extraction_index_sets_bit_exact(pkg, oracle, synth, sem):
+    dims, vs = (72, 40, 56), 0.03
+    color = sem == SEM_FUSIONPY
+    origin, frames = synth.s_real(dims, vs, n_frames=5, seed=31)
+    p, t, w, c, _ = oracle_run(oracle, dims, vs, origin, frames, sem, color)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color)
+    with pkg.Volume(cfg) as vol:
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb if color else None, T, sync=False)
+        for pred, tt, wt in ((PRED_NONZERO, 1.2, 0.9), (PRED_ABS_LT, 0.4, 1.5), (PRED_ABS_LT, 0.0, 0.0)):
+            oxyz, orgb, oidx = oracle.extract(p, t, w, c, pred, tt, wt)
+            assert vol.extract_count(pred, tt, wt) == len(oidx)
+            xyz, rgb, idx = vol.extract_points(pred, tt, wt)
+            assert np.array_equal(idx, oidx)
+            assert np.array_equal(bits(xyz), bits(oxyz))
+            if color:
+                assert np.array_equal(rgb, orgb)
+        # capacity protocol
+        import ctypes as C
+        n = C.c_int64(0)
+        buf = np.zeros(3, np.float32)
+        rc = vol.lib.tsdf_extract_points(vol.h, PRED_NONZERO, np.float32(1.2), np.float32(0.9),
+                                         buf.ctypes.data, None, None, 1, C.byref(n))
+        assert rc == pkg.capi.E_CAPACITY and n.value == len(oracle.extract(p, t, w, c)[2])
+
+
+def test_empty_and_degenerate_frames(pkg, oracle, synth):
+    dims, vs = (32, 32, 32), 0.05
+    origin = np.array([-0.8, -0.8, 1.0], np.float32)
+    H, W = 480, 640
+    I = np.eye(4, dtype=np.float32)
+    zeros = np.zeros((H, W), np.float32)
+    far = np.full((H, W), 7.5, np.float32)            # > max_depth 6 (src/tsdf.cu:46)
+    neg = np.full((H, W), -1.0, np.float32)
+    behind = synth.pose(synth.rot_xyz(0, np.pi, 0), (0, 0, 0))  # volume behind the camera (:39)
+    wall = np.full((H, W), 2.0, np.float32)
+    wall[::7, ::5] = 0.0
+    nanny = wall.copy()
+    nanny[200:210, 300:310] = np.nan                    # NaN depth is integrated by the reference
+    rgb = np.zeros((H, W, 3), np.uint8)
+    for sem in (SEM_TSDFCU, SEM_FUSIONPY):
+        frames = [(zeros, rgb, I), (far, rgb, I), (neg, rgb, I), (wall, rgb, behind), (wall, rgb, I), (nanny, rgb, I)]
+        p, t, w, c, written = oracle_run(oracle, dims, vs, origin, frames, sem, False, max_depth=6.0)
+        assert written[0] == written[2] == written[3] == 0 and written[4] > 0
+        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=False, max_depth=6.0)
+        with pkg.Volume(cfg) as vol:
+            for (d, _, T), ow in zip(frames, written):
+                vol.integrate(d, None, T)
+                assert vol.stats().voxels_written == ow
+            gt, gw, _ = vol.download()
+        assert np.array_equal(gw, w)
+        assert np.array_equal(np.isnan(gt), np.isnan(t)) and np.isnan(t).any()
+        ok = ~np.isnan(t)
+        assert np.array_equal(bits(gt[ok]), bits(t[ok]))
+
+
+def test_reset_and_upload_roundtrip(pkg, synth):
+    dims, vs = (40, 40, 40), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=41)
+    cfg = pkg.make_config(dims, vs, origin)
+    with pkg.Volume(cfg) as vol:
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T)
+        a = vol.download()
+        vol.reset()
+        t0, w0, c0 = vol.download()
+        assert (t0 == 1).all() and (w0 == 0).all() and (c0 == 0).all()   # src/tsdf.cu:79-81
+        vol.upload(*a)
+        b = vol.download()
+        assert all(np.array_equal(bits(x), bits(y)) for x, y in zip(a, b))
+        vol.reset()
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T)
+        b = vol.download()
+        assert all(np.array_equal(bits(x), bits(y)) for x, y in zip(a, b)), "not deterministic"
+
+
+@pytest.mark.parametrize("sem", [SEM_TSDFCU, SEM_FUSIONPY])
+def test_fused_multi_frame_equals_sequential(pkg, oracle, synth, sem):
+    dims, vs = (48, 40, 64), 0.035
+    color = sem == SEM_FUSIONPY
+    origin, frames = synth.s_real(dims, vs, n_frames=11, seed=51)   # 8 + 2 + 1 fused launches
+    p, t, w, c, written = oracle_run(oracle, dims, vs, origin, frames, sem, color, 0.5 if color else 1.0)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color)
+    with pkg.Volume(cfg) as vol:
+        vol.integrate_multi([f[0] for f in frames], [f[1] for f in frames] if color else None,
+                            [f[2] for f in frames], obs_weight=0.5 if color else 1.0)
+        gt, gw, gc = vol.download()
+    assert_volume_equal(gt, gw, gc, t, w, c)
+
+
+@pytest.mark.parametrize("sem", [SEM_TSDFCU, SEM_FUSIONPY])
+def test_z_slabs_equal_whole_grid(pkg, oracle, synth, sem):
+    """Multi-GPU sharding emulated on one GPU: 3 slab handles == 1 whole-grid handle == oracle."""
+    dims, vs = (40, 32, 72), 0.04
+    color = sem == SEM_FUSIONPY
+    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=61)
+    p, t, w, c, _ = oracle_run(oracle, dims, vs, origin, frames, sem, color)
+    n = dims[0] * dims[1] * dims[2]
+    T_, W_, C_ = np.zeros(n, np.float32), np.zeros(n, np.float32), (np.zeros(n, np.float32) if color else None)
+    pts = []
+    for r in range(3):
+        zr = pkg.slab_range(dims[2], 3, r)
+        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, z_range=zr)
+        with pkg.Volume(cfg) as vol:
+            for d, rgb, T in frames:
+                vol.integrate(d, rgb if color else None, T)
+            vol.download_into(T_, W_, C_)
+            pts.append(vol.extract_points())
+    assert_volume_equal(T_, W_, C_, t, w, c)
+    oxyz, orgb, oidx = oracle.extract(p, t, w, c)
+    idx = np.concatenate([q[2] for q in pts])
+    xyz = np.concatenate([q[0] for q in pts])
+    order = np.argsort(idx, kind="stable")
+    assert np.array_equal(idx[order], oidx) and np.array_equal(bits(xyz[order]), bits(oxyz))
+
+
+def test_raw_u16_depth_and_subsampling(pkg, oracle, synth):
+    """Depth pre-processing fused into the upload (examples/label_instance_rgbd.cpp:89-100)."""
+    dims, vs = (48, 48, 48), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=71)
+    scale = np.float32(1.0) / np.float32(5000.0)
+    raw = [np.clip(np.round(f[0] * 5000.0), 0, 65535).astype(np.uint16) for f in frames]
+    sub = []
+    for r in raw:
+        d = r.astype(np.float32) * scale
+        m = np.zeros_like(d)
+        m[::4, ::3] = d[::4, ::3]
+        sub.append(m)
+    fr = [(s, f[1], f[2]) for s, f in zip(sub, frames)]
+    p, t, w, c, _ = oracle_run(oracle, dims, vs, origin, fr, SEM_FUSIONPY, True)
+    cfg = pkg.make_config(dims, vs, origin)
+    with pkg.Volume(cfg) as vol:
+        for r, f in zip(raw, frames):
+            vol.integrate_raw(r, scale, f[1], f[2], subsample=(3, 4))
+        gt, gw, gc = vol.download()
+    assert_volume_equal(gt, gw, gc, t, w, c)
+
+
+def test_instance_origin_on_device(pkg, oracle, synth):
+    import ctypes as C
+    _, frames = synth.s_real((32, 32, 32), 0.05, n_frames=1, seed=81)
+    d = frames[0][0]
+    masks, _ = synth.instance_masks(3)
+    for m in (None, masks[0], masks[2]):
+        out = np.zeros(3, np.float32)
+        rc = pkg.load().tsdf_instance_origin(0, d.ctypes.data, None if m is None else m.ctypes.data,
+                                             d.shape[0], d.shape[1], synth.TUM3_K.ctypes.data, out.ctypes.data)
+        assert rc == 0
+        assert np.array_equal(bits(out), bits(oracle.instance_origin(d, m, synth.TUM3_K)))
+
+
+def test_reference_class_mirrors(pkg, oracle, synth, tmp_path):
+    """TSDF(h,w,id,base2world,origin).Integrate(depth, cam2world) and
+    TSDFVolume(vol_bnds, voxel_size).integrate(color, depth, K, pose, obs_weight)."""
+    dims, vs = (200, 200, 200), 0.004      # the reference's hard-coded grid (include/tsdf.hpp:63-67)
+    L = 200 * vs
+    scene = synth.Scene().sphere((0, 0, 1.2), 0.25).plane((0, 0, 1), 1.6)
+    rng = np.random.default_rng(5)
+    poses = [synth.pose(synth.rot_xyz(0.01 * i, -0.02 * i, 0), (0.01 * i, 0, 0)) for i in range(3)]
+    frames = [synth.render(scene, synth.TUM3_K, synth.TUM3_HW, T, rng) + (T,) for T in poses]
+    origin = np.array([-L / 2, -L / 2, 0.8], np.float32)
+    base = poses[0]
+    p, t, w, _, _ = oracle_run(oracle, dims, vs, origin, frames, SEM_TSDFCU, False, base=base)
+    obj = pkg.TSDF(480, 640, 3, base.reshape(16), origin)
+    for d, _, T in frames:
+        obj.Integrate(d, T.reshape(16))
+    assert (obj.voxel_grid_weight == 0).all()          # mirrors are stale until readback (src/tsdf.cu:101-104)
+    obj.close(str(tmp_path))
+    assert np.array_equal(obj.voxel_grid_weight, w) and np.array_equal(bits(obj.voxel_grid_TSDF), bits(t))
+    assert oracle.save_ply(str(tmp_path / "o.ply"), p, t, w)
+    assert open(tmp_path / "o.ply", "rb").read() == open(tmp_path / "tsdf3.ply", "rb").read()
+    assert oracle.save_bin(str(tmp_path / "o.bin"), p, t)
+    assert open(tmp_path / "o.bin", "rb").read() == open(tmp_path / "tsdf3.bin", "rb").read()
+
+    bnds = np.array([[-0.6, 0.6], [-0.5, 0.5], [0.8, 1.8]])
+    tv = pkg.TSDFVolume(bnds, 0.01)
+    d3 = tuple(tv._vol_dim)
+    assert d3 == tuple(np.ceil((bnds[:, 1] - bnds[:, 0]) / 0.01).astype(int))
+    for d, rgb, T in frames:
+        tv.integrate(rgb, d, synth.TUM3_K.reshape(3, 3), T, obs_weight=1.0)
+    tsdf_vol, color_vol = tv.get_volume()
+    p2, t2, w2, c2, _ = oracle_run(oracle, d3, 0.01, bnds[:, 0], frames, SEM_FUSIONPY, True,
+                                   trunc=np.float32(0.01 * 5))
+    assert np.array_equal(bits(tsdf_vol.reshape(-1)), bits(t2)) and np.array_equal(color_vol.reshape(-1), c2)
+    xyz, rgb = tv.get_point_cloud()
+    oxyz, orgb, _ = oracle.extract(p2, t2, w2, c2)
+    assert np.array_equal(bits(xyz), bits(oxyz)) and np.array_equal(rgb, orgb)
+    tv.close()
+
+
+def test_batched_instances_match_per_instance_oracle(pkg, oracle, synth):
+    """Config 5 in small: N instance volumes, one launch per frame, masked depth semantics of
+    src/Engine.cpp:192-193 and per-instance base/origin of src/Object.cpp:23-49."""
+    import ctypes as C
+    n_inst, dims, vs = 6, (32, 32, 32), 0.02
+    _, frames = synth.s_real((64, 64, 64), 0.08, n_frames=3, seed=91)
+    masks, _ = synth.instance_masks(n_inst, seed=92)
+    base = frames[0][2]
+    d0 = frames[0][0]
+    cfgs = (pkg.capi.Config * n_inst)()
+    origins = []
+    for i in range(n_inst):
+        og = oracle.instance_origin(d0, masks[i], synth.TUM3_K)
+        origins.append(og)
+        cfgs[i] = pkg.make_config(dims, vs, og, semantics=SEM_TSDFCU, with_color=False, base2world=base,
+                                  max_depth=30.0, vol_id=i)
+    lib = pkg.load()
+    hb = C.c_void_p()
+    pkg.capi.check(lib.tsdf_batch_create(cfgs, n_inst, C.byref(hb)))
+    try:
+        active_sets = [list(range(n_inst)), [0, 2, 5], [4, 1]]
+        for (d, rgb, T), act in zip(frames, active_sets):
+            a = np.array(act, np.int32)
+            m = np.ascontiguousarray(masks[act])
+            Tc = np.ascontiguousarray(T, np.float32)
+            pkg.capi.check(lib.tsdf_batch_integrate_async(hb, d.ctypes.data, None, a.ctypes.data, len(act),
+                                                          m.ctypes.data, None, Tc.ctypes.data, np.float32(1.0)))
+            pkg.capi.check(lib.tsdf_batch_sync(hb))
+        for i in range(n_inst):
+            p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), origins[i], synth.TUM3_HW, synth.TUM3_K,
+                              30.0, SEM_TSDFCU)
+            t, w, _ = oracle.new_volume(p)
+            for (d, rgb, T), act in zip(frames, active_sets):
+                if i in act:
+                    md = d * (masks[i] >= 128)
+                    oracle.integrate(p, oracle.compose(base, T), md.astype(np.float32), None, 1.0, t, w, None)
+            gt, gw = np.zeros_like(t), np.zeros_like(w)
+            pkg.capi.check(lib.tsdf_batch_download(hb, i, gt.ctypes.data, gw.ctypes.data, None))
+            assert np.array_equal(gw, w) and np.array_equal(bits(gt), bits(t)), f"instance {i}"
+    finally:
+        lib.tsdf_batch_destroy(hb)
+
+
+def test_full_size_properties_c1(pkg, synth):
+    """BASELINE config 1 size (256^3, 2 cm) through size-independent properties: S-full writes
+    every voxel every frame (weights == frame count everywhere, N_written == N_vox), weights
+    are linear in obs_weight, and extraction returns a strictly ascending index list."""
+    dims, vs = (256, 256, 256), 0.02
+    origin, frames = synth.s_full(dims, vs, n_frames=3)
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+    with pkg.Volume(cfg) as vol:
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T, obs_weight=0.5)
+            assert vol.stats().voxels_written == vol.n_local
+        t, w, c = vol.download()
+        assert (w == 1.5).all() and np.isfinite(t).all() and (np.abs(t) <= 1).all()
+        assert (c >= 0).all() and (c < 2 ** 24).all() and (c == np.floor(c)).all()
+        xyz, rgb, idx = vol.extract_points(PRED_ABS_LT, 0.999, 1.0)
+        assert len(idx) > 0 and (np.diff(idx) > 0).all()
+        sel = (np.abs(t) < np.float32(0.999)) & (w > 1.0)
+        assert np.array_equal(idx, np.flatnonzero(sel))
