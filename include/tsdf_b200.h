@@ -226,7 +226,8 @@ int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float*
                                float obs_weight);
 /* Collective: every rank extracts its slab; the root receives all points,
  * merged to ascending GLOBAL reference index.  Non-root ranks pass NULL/0
- * buffers and get their LOCAL count in *count; the root gets the total.     */
+ * buffers and get their LOCAL count in *count; the root gets the total.
+ * cap < 0 on EVERY rank = count-only (sizing) call: no records are moved.    */
 int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predicate, float tsdf_thresh,
                        float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap,
                        int64_t* count);
@@ -250,6 +251,16 @@ int tsdf_invert_matrix(const float m[16], float out[16]); /* src/tsdf.cu:276-403
 int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms);
 /* Selects a kernel variant for A/B evidence (0 = default).                  */
 int tsdf_set_variant(tsdf_vol* v, int variant);
+/* Device-side stopwatch on the handle's compute stream (CUDA events): start
+ * records now; stop records after everything enqueued so far, waits for it
+ * and returns the elapsed ms.  bench.py brackets its timed region with it.  */
+int tsdf_timer_start(tsdf_vol* v);
+int tsdf_timer_stop(tsdf_vol* v, float* ms);
+/* Per-launch timing of the integrate kernel: when enabled every launch is
+ * bracketed by its own CUDA event pair on the launching stream; read returns
+ * the summed kernel ms and the number of launches since the last reset.     */
+int tsdf_kernel_timing(tsdf_vol* v, int enable);
+int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset);
 
 #ifdef __cplusplus
 }

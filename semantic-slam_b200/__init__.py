@@ -4,7 +4,7 @@ in include/tsdf_b200.h; this package is the thin host-side mirror of the referen
 TSDF / TSDFfusion surface over that ABI.  Import with
 `importlib.import_module("semantic-slam_b200")` (the directory name has a hyphen).
 """
-from . import capi, synth, volume  # noqa: F401
+from . import capi, synth, volume, dist  # noqa: F401
 from .capi import (SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO, PRED_ABS_LT, TsdfError, load)  # noqa: F401
 from .volume import (Volume, TSDF, TSDFVolume, make_config, config_from_bounds, default_config,
                      slab_range, device_count)  # noqa: F401

@@ -94,6 +94,10 @@ SIGNATURES = {
     "tsdf_invert_matrix": (_I, [_VP, _VP]),
     "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
     "tsdf_set_variant": (_I, [_VP, _I]),
+    "tsdf_timer_start": (_I, [_VP]),
+    "tsdf_timer_stop": (_I, [_VP, C.POINTER(_F)]),
+    "tsdf_kernel_timing": (_I, [_VP, _I]),
+    "tsdf_kernel_timing_read": (_I, [_VP, C.POINTER(C.c_double), C.POINTER(_I64), _I]),
 }
 
 _lib = None

@@ -168,7 +168,8 @@ static void free_vol(tsdf_vol* v) {
   cudaFree(v->d_tsdf); cudaFree(v->d_weight); cudaFree(v->d_color);
   cudaFree(v->d_written); cudaFree(v->d_scratch);
   if (v->h_written) cudaFreeHost(v->h_written);
-  for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1, v->ev_t0, v->ev_t1}) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : v->kev) cudaEventDestroy(e);
   if (v->s_compute) cudaStreamDestroy(v->s_compute);
   if (v->s_copy) cudaStreamDestroy(v->s_copy);
   delete v;
@@ -207,6 +208,8 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaEventCreate(&v->ev_k1));
   CU_CHECK(cudaEventCreate(&v->ev_u0));
   CU_CHECK(cudaEventCreate(&v->ev_u1));
+  CU_CHECK(cudaEventCreate(&v->ev_t0));
+  CU_CHECK(cudaEventCreate(&v->ev_t1));
   return tsdf_reset(v);
 }
 
@@ -339,10 +342,23 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
 static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
   CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
-  CU_CHECK(cudaEventRecord(v->ev_k0, v->s_compute));
+  cudaEvent_t k0 = v->ev_k0, k1 = v->ev_k1;
+  if (v->ktiming) {  // a private event pair per launch
+    if (v->kev_used + 2 > v->kev.size()) {
+      for (int i = 0; i < 2; ++i) {
+        cudaEvent_t e;
+        CU_CHECK(cudaEventCreate(&e));
+        v->kev.push_back(e);
+      }
+    }
+    k0 = v->kev[v->kev_used];
+    k1 = v->kev[v->kev_used + 1];
+    v->kev_used += 2;
+  }
+  CU_CHECK(cudaEventRecord(k0, v->s_compute));
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;
-  CU_CHECK(cudaEventRecord(v->ev_k1, v->s_compute));
+  CU_CHECK(cudaEventRecord(k1, v->s_compute));
   CU_CHECK(cudaMemcpyAsync(v->h_written, v->d_written, sizeof(unsigned long long),
                            cudaMemcpyDeviceToHost, v->s_compute));
   for (int i = 0; i < nf; ++i) {
@@ -433,7 +449,8 @@ extern "C" int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s) {
   s->voxels_written = v->last_written;
   s->frames = v->frames;
   if (v->last_nf > 0) {
-    cudaEventElapsedTime(&s->last_kernel_ms, v->ev_k0, v->ev_k1);
+    if (v->ktiming && v->kev_used >= 2) cudaEventElapsedTime(&s->last_kernel_ms, v->kev[v->kev_used - 2], v->kev[v->kev_used - 1]);
+    else if (cudaEventElapsedTime(&s->last_kernel_ms, v->ev_k0, v->ev_k1) != cudaSuccess) { cudaGetLastError(); s->last_kernel_ms = 0; }
     if (cudaEventElapsedTime(&s->last_upload_ms, v->ev_u0, v->ev_u1) != cudaSuccess) {
       cudaGetLastError();
       s->last_upload_ms = 0;
@@ -755,4 +772,48 @@ int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const fl
   FrameP fp;
   make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
   return submit(v, &s, &fp, 1, color);
+}
+
+// ---- measurement hooks ---------------------------------------------------------------------------
+extern "C" int tsdf_timer_start(tsdf_vol* v) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  CU_CHECK(cudaEventRecord(v->ev_t0, v->s_compute));
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_timer_stop(tsdf_vol* v, float* ms) {
+  REQUIRE(v && ms, "null argument");
+  DeviceGuard g(v->cfg.device);
+  CU_CHECK(cudaStreamSynchronize(v->s_copy));   // everything staged so far is enqueued/finished
+  CU_CHECK(cudaEventRecord(v->ev_t1, v->s_compute));
+  CU_CHECK(cudaEventSynchronize(v->ev_t1));
+  CU_CHECK(cudaEventElapsedTime(ms, v->ev_t0, v->ev_t1));
+  return tsdf_sync(v);
+}
+
+extern "C" int tsdf_kernel_timing(tsdf_vol* v, int enable) {
+  REQUIRE(v, "null handle");
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  v->ktiming = enable != 0;
+  v->kev_used = 0;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset) {
+  REQUIRE(v && sum_ms && launches, "null argument");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  double s = 0;
+  for (size_t i = 0; i + 1 < v->kev_used; i += 2) {
+    float ms = 0;
+    CU_CHECK(cudaEventElapsedTime(&ms, v->kev[i], v->kev[i + 1]));
+    s += ms;
+  }
+  *sum_ms = s;
+  *launches = (int64_t)(v->kev_used / 2);
+  if (reset) v->kev_used = 0;
+  return TSDF_OK;
 }

@@ -214,6 +214,7 @@ extern "C" int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predi
   for (int r = 0; r < c->nranks; ++r) { offs[r] = total; total += counts[r]; }
   offs[c->nranks] = total;
   *count = is_root ? total : n_local;
+  if (cap < 0) { cleanup(); return TSDF_OK; }  // collective count-only call (every rank passes cap < 0)
   // 3. records to the root (every rank takes part even if the root's buffers are too small:
   //    the root then receives into scratch and reports TSDF_E_CAPACITY afterwards)
   const size_t nt = (size_t)std::max<int64_t>(total, 1);

@@ -112,6 +112,11 @@ struct tsdf_vol {
   FrameP last_frames[kMaxFusedFrames];
   int last_nf = 0;
   bool last_color = false;
+  // measurement
+  cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+  bool ktiming = false;
+  std::vector<cudaEvent_t> kev;   // pairs
+  size_t kev_used = 0;            // events recorded since reset (2 per launch)
   // extraction scratch
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;

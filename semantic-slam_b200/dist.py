@@ -1,0 +1,110 @@
+"""One-process-per-GPU plumbing for z-slab sharded volumes.
+
+torch.distributed is used ONLY as the control plane (rendezvous, shipping the 128-byte NCCL
+unique id and the per-frame pose metadata); the data plane — frame broadcast and point
+gather — is NCCL inside libtsdf_b200.so (csrc/comm.cu).  Host-side logic here is covered by
+world_size-2 gloo tests on CPU (tests/test_dist_cpu.py).
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import capi
+from .capi import check, ptr, f32
+from .volume import Volume, make_config, slab_range
+
+
+def exchange_uid(make_uid, rank, dist_mod, device=None):
+    """Rank 0 calls make_uid() -> 128 bytes; everyone receives them via torch.distributed."""
+    import torch
+    buf = torch.zeros(128, dtype=torch.uint8)
+    if rank == 0:
+        uid = make_uid()
+        assert len(uid) == 128
+        buf = torch.frombuffer(bytearray(uid), dtype=torch.uint8).clone()
+    if device is not None:
+        buf = buf.to(device)
+    dist_mod.broadcast(buf, src=0)
+    return bytes(buf.cpu().numpy().tobytes())
+
+
+def broadcast_array(arr, rank, dist_mod, device=None):
+    """Control-plane broadcast of a small float32 array (poses, intrinsics) from rank 0."""
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(arr, np.float32).copy())
+    if device is not None:
+        t = t.to(device)
+    dist_mod.broadcast(t, src=0)
+    return t.cpu().numpy()
+
+
+def plan_slabs(dim_z, world):
+    """[(z_begin, z_end)] per rank; contiguous, 4-slice aligned, covering [0, dim_z)."""
+    return [slab_range(dim_z, world, r) for r in range(world)]
+
+
+def merge_by_index(parts):
+    """parts: list of (xyz, rgb, idx) with each idx ascending -> merged ascending by idx.
+    Host-side mirror of the k-way merge the library does at the root (test helper)."""
+    xyz = np.concatenate([p[0] for p in parts])
+    rgb = np.concatenate([p[1] for p in parts])
+    idx = np.concatenate([p[2] for p in parts])
+    order = np.argsort(idx, kind="stable")
+    return xyz[order], rgb[order], idx[order]
+
+
+def make_nccl_uid():
+    uid = (C.c_uint8 * 128)()
+    check(capi.load().tsdf_comm_unique_id(uid))
+    return bytes(uid)
+
+
+class ShardedVolume:
+    """This rank's z-slab of a grid + its NCCL communicator."""
+
+    def __init__(self, cfg, rank, world, device, uid):
+        self.rank, self.world = rank, world
+        zr = slab_range(cfg.dim_z, world, rank)
+        cfg.z_begin, cfg.z_end = zr
+        cfg.device = device
+        self.vol = Volume(cfg)
+        self.lib = capi.load()
+        self.comm = C.c_void_p()
+        ub = (C.c_uint8 * 128).from_buffer_copy(uid)
+        check(self.lib.tsdf_comm_create(ub, world, rank, device, C.byref(self.comm)))
+        self._keep = []
+
+    def integrate_bcast(self, depth, rgb, T_wc, K=None, obs_weight=1.0, root=0):
+        T = f32(T_wc, 16)
+        Kc = None if K is None else f32(K, 9)
+        self._keep.append((depth, rgb, T, Kc))
+        check(self.lib.tsdf_integrate_bcast_async(self.vol.h, self.comm, root, ptr(depth), ptr(rgb),
+                                                  ptr(Kc), ptr(T), np.float32(obs_weight)))
+
+    def sync(self):
+        self.vol.sync()
+        self._keep.clear()
+
+    def gather_points(self, pred=capi.PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, root=0, cap=None):
+        n = C.c_int64(0)
+        if cap is None:  # collective sizing call first
+            check(self.lib.tsdf_gather_points(self.vol.h, self.comm, root, pred, np.float32(tsdf_thresh),
+                                              np.float32(weight_thresh), None, None, None, -1, C.byref(n)))
+            cap = n.value
+        if self.rank != root:
+            check(self.lib.tsdf_gather_points(self.vol.h, self.comm, root, pred, np.float32(tsdf_thresh),
+                                              np.float32(weight_thresh), None, None, None, 0, C.byref(n)))
+            return None, None, None, n.value
+        cap = int(cap)
+        xyz = np.zeros((max(cap, 1), 3), np.float32)
+        rgb = np.zeros((max(cap, 1), 3), np.uint8)
+        idx = np.zeros(max(cap, 1), np.int64)
+        check(self.lib.tsdf_gather_points(self.vol.h, self.comm, root, pred, np.float32(tsdf_thresh),
+                                          np.float32(weight_thresh), ptr(xyz), ptr(rgb), ptr(idx), cap, C.byref(n)))
+        return xyz[:n.value], rgb[:n.value], idx[:n.value], n.value
+
+    def close(self):
+        if self.comm:
+            self.lib.tsdf_comm_destroy(self.comm)
+            self.comm = None
+        self.vol.close()

@@ -176,6 +176,23 @@ class Volume:
         check(self.lib.tsdf_bench_kernel(self.h, int(iters), C.byref(ms)))
         return ms.value
 
+    def timer_start(self):
+        check(self.lib.tsdf_timer_start(self.h))
+
+    def timer_stop(self):
+        ms = C.c_float(0)
+        check(self.lib.tsdf_timer_stop(self.h, C.byref(ms)))
+        self._keep.clear()
+        return ms.value
+
+    def kernel_timing(self, enable=True):
+        check(self.lib.tsdf_kernel_timing(self.h, int(enable)))
+
+    def kernel_timing_read(self, reset=True):
+        s, n = C.c_double(0), C.c_int64(0)
+        check(self.lib.tsdf_kernel_timing_read(self.h, C.byref(s), C.byref(n), int(reset)))
+        return s.value, n.value
+
     def set_variant(self, variant):
         check(self.lib.tsdf_set_variant(self.h, int(variant)))
 

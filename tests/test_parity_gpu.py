@@ -131,7 +131,7 @@ def test_empty_and_degenerate_frames(pkg, oracle, synth):
     wall = np.full((H, W), 2.0, np.float32)
     wall[::7, ::5] = 0.0
     nanny = wall.copy()
-    nanny[200:210, 300:310] = np.nan                    # NaN depth is integrated by the reference
+    nanny[150:330, 220:420] = np.nan                    # NaN depth is integrated by the reference
     rgb = np.zeros((H, W, 3), np.uint8)
     for sem in (SEM_TSDFCU, SEM_FUSIONPY):
         frames = [(zeros, rgb, I), (far, rgb, I), (neg, rgb, I), (wall, rgb, behind), (wall, rgb, I), (nanny, rgb, I)]
