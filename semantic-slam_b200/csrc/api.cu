@@ -239,6 +239,8 @@ extern "C" int tsdf_reset(tsdf_vol* v) {
   CU_CHECK(cudaStreamSynchronize(v->s_compute));
   v->frames = 0;
   v->last_written = 0;
+  v->intw = true;
+  v->w_bound = 0;
   return TSDF_OK;
 }
 
@@ -257,7 +259,7 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   const size_t px = frame_pixels(v->cfg);
   if (!s.d_raw) {
     CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
-    CU_CHECK(cudaMalloc(&s.d_frame, px * 8));           // uint2 per pixel (float when no colour)
+    CU_CHECK(cudaMalloc(&s.d_frame, px * 16));          // float4 per pixel (float when no colour)
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
   }
@@ -338,6 +340,16 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
   return TSDF_OK;
 }
 
+// Integer-weight bookkeeping (see blend_intw in integrate.cu).  Must be called once per
+// launch, before it: returns whether the launch may use the integer-weight colour path.
+bool account_weights(tsdf_vol* v, const FrameP* fp, int nf) {
+  bool all_one = true;
+  for (int i = 0; i < nf; ++i) all_one = all_one && fp[i].obs_weight == 1.0f;
+  if (!all_one) v->intw = false;
+  v->w_bound += nf;  // only meaningful while intw holds
+  return v->intw && v->w_bound <= 4094;
+}
+
 // Launches the integrate kernel for nf prepared frames and records stats/events.
 static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
@@ -355,6 +367,7 @@ static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool
     k1 = v->kev[v->kev_used + 1];
     v->kev_used += 2;
   }
+  v->wmode_ok = account_weights(v, fp, nf);
   CU_CHECK(cudaEventRecord(k0, v->s_compute));
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;
@@ -378,6 +391,7 @@ extern "C" int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int dept
                                         const float* K, const float* T_wc, float obs_weight) {
   REQUIRE(v && depth && T_wc, "null argument");
   REQUIRE(depth_fmt == TSDF_DEPTH_F32 || depth_fmt == TSDF_DEPTH_U16, "bad depth format");
+  REQUIRE(obs_weight >= 1e-6f && obs_weight <= 1e6f, "obs_weight must be in [1e-6, 1e6]");
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   FrameSlot* s = nullptr;
@@ -478,6 +492,7 @@ extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
   CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
   CU_CHECK(cudaEventRecord(v->ev_k0, v->s_compute));
   for (int i = 0; i < iters; ++i) {
+    v->wmode_ok = account_weights(v, v->last_frames, v->last_nf);
     rc = launch_integrate(v, v->last_frames, v->last_nf, v->last_color, v->s_compute);
     if (rc) return rc;
   }
@@ -541,6 +556,7 @@ extern "C" int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, 
   int rc = tsdf_sync(v);
   if (rc) return rc;
   REQUIRE(!color || v->d_color, "volume has no colour array");
+  if (weight) v->intw = false;  // arbitrary weights: the integer-weight fast path is off until reset
   if ((rc = copy_slab(v, const_cast<float*>(tsdf), v->d_tsdf, global_layout, false))) return rc;
   if ((rc = copy_slab(v, const_cast<float*>(weight), v->d_weight, global_layout, false))) return rc;
   if ((rc = copy_slab(v, const_cast<float*>(color), v->d_color, global_layout, false))) return rc;

@@ -122,21 +122,17 @@ extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, con
   int max_fast = 0, max_rows = 0;
   int64_t visited = 0;
   bool vec4 = true;
+  bool wmode = true;
   for (int i = 0; i < n_active; ++i) {
     REQUIRE(active[i] >= 0 && active[i] < b->n, "instance id out of range");
     tsdf_vol* v = b->vols[active[i]];
     const tsdf_config& c = v->cfg;
     BatchDesc& d = b->h_descs[i];
-    d.g.n_fast = v->zfast ? v->dzl : c.dim_x;
-    d.g.n_mid = c.dim_y;
-    d.g.n_slow = v->zfast ? c.dim_x : v->dzl;
-    d.g.z0 = c.z_begin;
-    d.g.ox = c.origin[0]; d.g.oy = c.origin[1]; d.g.oz = c.origin[2];
-    d.g.vs = c.voxel_size; d.g.trunc = c.trunc_margin;
-    d.g.W = c.im_w; d.g.H = c.im_h;
-    d.g.tsdf = v->d_tsdf; d.g.weight = v->d_weight; d.g.color = color ? v->d_color : nullptr;
+    (void)c;
+    fill_grid_params(v, color, &d.g);
     d.g.written = b->d_written;
     make_frame_params(v, K, T_wc, obs_weight, slot->d_frame, &d.f);
+    wmode = account_weights(v, &d.f, 1) && wmode;
     d.mask = d_masks ? d_masks + px * (size_t)i : nullptr;
     max_fast = d.g.n_fast > max_fast ? d.g.n_fast : max_fast;
     int rows = d.g.n_mid * d.g.n_slow;
@@ -152,7 +148,7 @@ extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, con
   CU_CHECK(cudaStreamWaitEvent(fo->s_compute, slot->uploaded, 0));
   CU_CHECK(cudaMemsetAsync(b->d_written, 0, 8, fo->s_compute));
   CU_CHECK(cudaEventRecord(b->ev0, fo->s_compute));
-  rc = launch_integrate_batch(b->d_descs, n_active, max_fast, max_rows, fo->zfast, color, vec4, fo->s_compute);
+  rc = launch_integrate_batch(b->d_descs, n_active, max_fast, max_rows, fo->zfast, color, vec4, (color && wmode) ? 1 : 0, fo->s_compute);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(b->ev1, fo->s_compute));
   CU_CHECK(cudaMemcpyAsync(b->h_written, b->d_written, 8, cudaMemcpyDeviceToHost, fo->s_compute));

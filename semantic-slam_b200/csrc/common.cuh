@@ -48,7 +48,7 @@ struct FrameP {       // one camera frame
   float fx, cx, fy, cy;  // K[0],K[2],K[4],K[5], src/tsdf.cu:41-42
   float obs_weight;
   int pad_;
-  const void* img;    // prepared frame: float depth[H*W]  or  uint2 {depth, packed colour}[H*W]
+  const void* img;    // prepared frame: float depth[H*W]  or  float4 {depth, c0, c1, c2}[H*W]
 };
 
 struct GridP {        // one volume slab
@@ -58,6 +58,8 @@ struct GridP {        // one volume slab
   int z0;             // global z of local slice 0
   float ox, oy, oz;   // origin (base frame)
   float vs, trunc;
+  float inv_trunc;    // RN(1/trunc), host IEEE division
+  float w_lim, h_lim; // W-0.5, H-0.5: (int)roundf(u) in [0,W) <=> -0.5 < u < W-0.5
   int W, H;
   float* tsdf;
   float* weight;
@@ -71,8 +73,8 @@ struct BatchDesc {    // one active instance of a batched launch (lives in globa
   const uint8_t* mask;  // H*W 8-bit instance mask on the device, or null
 };
 
-// Prepared-frame pixel when colour is on: .x = depth bits (invalid canonicalised to 0.0f),
-// .y = packed colour as an exact small integer in fp32 bits (c2*65536+c1*256+c0).
+// Prepared-frame pixel when colour is on: float4 {depth (invalid canonicalised to 0.0f),
+// c0, c1, c2 as exact floats}.
 // Depth-only frames are a plain float image.
 
 // ---- host-side handle -------------------------------------------------------------------
@@ -108,6 +110,11 @@ struct tsdf_vol {
   int64_t last_written = 0;
   int64_t last_frames_in_launch = 1;
   int variant = 0;
+  // integer-weight bookkeeping: true while every stored weight is provably an integer
+  // (only obs_weight == 1 integrations since the last reset); w_bound >= max stored weight
+  bool intw = true;
+  int64_t w_bound = 0;
+  bool wmode_ok = false;       // decided per launch by submit()
   // state of the last launch, for tsdf_bench_kernel
   FrameP last_frames[kMaxFusedFrames];
   int last_nf = 0;
@@ -128,7 +135,9 @@ inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_
 // integrate.cu
 int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st);
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
-                           bool zfast, bool color, bool vec4, cudaStream_t st);
+                           bool zfast, bool color, bool vec4, int wmode, cudaStream_t st);
+void fill_grid_params(const tsdf_vol* v, bool color, GridP* g);
+bool account_weights(tsdf_vol* v, const FrameP* fp, int nf);  // updates intw/w_bound, returns wmode_ok
 // frame.cu
 int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
                       const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,

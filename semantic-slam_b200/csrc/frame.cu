@@ -2,14 +2,14 @@
 // into the "prepared frame" the integrate kernel gathers from, plus small utility kernels.
 //
 // Prepared frame:
-//   colour on : uint2 per pixel {depth bits, packed colour fp32 bits} -> ONE 64-bit gather
-//               per voxel instead of two 32-bit gathers
+//   colour on : float4 per pixel {depth, c0, c1, c2} -> ONE 128-bit gather per voxel, and
+//               the colour channels arrive as exact floats (no per-voxel unpacking)
 //   colour off: float per pixel
 // Depth is canonicalised here: a sample failing the reference's validity test
 // `d <= 0 || d > max_depth` (src/tsdf.cu:46) is stored as 0.0f, so the hot loop needs a
 // single compare.  NaN fails neither test in the reference and is kept.
-// The packed colour is floor(c2*65536 + c1*256 + c0) (upstream fold); all values are
-// integers < 2^24, exact in fp32.
+// The upstream fold floor(c2*65536 + c1*256 + c0) followed by its floor/divide unfold returns
+// c2, c1, c0 unchanged (each < 256), so the channels are stored directly.
 // Optional per-instance mask: depth * (mask/255), i.e. depth kept where mask >= 128
 // (src/Engine.cpp:192-193; OpenCV 8-bit divide rounds to nearest).
 #include "common.cuh"
@@ -32,10 +32,10 @@ __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scal
   if (mask) d = d * (mask[i] >= 128 ? 1.0f : 0.0f);
   if (d <= 0.0f || d > max_depth) d = 0.0f;
   if (with_color) {
-    float pc = 0.0f;
-    if (rgb) pc = floorf((float)rgb[3 * i + 2] * 65536.0f + (float)rgb[3 * i + 1] * 256.0f +
-                         (float)rgb[3 * i + 0]);
-    reinterpret_cast<uint2*>(out)[i] = make_uint2(__float_as_uint(d), __float_as_uint(pc));
+    // channels of the folded colour floor(c2*65536 + c1*256 + c0) as exact floats
+    float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+    if (rgb) { c0 = (float)rgb[3 * i + 0]; c1 = (float)rgb[3 * i + 1]; c2 = (float)rgb[3 * i + 2]; }
+    reinterpret_cast<float4*>(out)[i] = make_float4(d, c0, c1, c2);
   } else {
     reinterpret_cast<float*>(out)[i] = d;
   }

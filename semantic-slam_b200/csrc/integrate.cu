@@ -18,6 +18,7 @@
 // single IEEE round-to-nearest op in the reference's source order,
 // so results are bit-identical to oracle/tsdf_oracle.c.
 #include "common.cuh"
+#include "exactmath.cuh"
 
 namespace {
 
@@ -52,59 +53,163 @@ __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
   }
 }
 
-// One voxel, one frame: decides validity and produces the truncated distance and the
-// pixel's packed colour.  Mirrors src/tsdf.cu:39-53.
+// ---------------------------------------------------------------------------------------
+// Per-voxel arithmetic.  Two spellings with identical results:
+//   MATH_EXACT   (default) the reference's source-order IEEE operations evaluated with the
+//                shared-reciprocal / Markstein / round-down-magic forms of exactmath.cuh
+//   MATH_LITERAL the literal C spelling (`/`, roundf, floorf) — kept as the A/B baseline
+//                (tsdf_set_variant(v, 1)) and as the fallback for out-of-range operands
+// ---------------------------------------------------------------------------------------
+constexpr int MATH_EXACT = 0, MATH_LITERAL = 1;
+
+struct Hit {          // result of probing one voxel against one frame
+  bool ok;
+  float dist;         // fmin(1, diff/trunc)                                   :53
+  float c0, c1, c2;   // pixel colour channels as exact floats (colour mode)
+};
+
+template <bool COLOR, bool MASK>
+__device__ __forceinline__ float fetch(const FrameP& f, const uint8_t* mask, int pix, Hit& h) {  // h: caller's registers
+  float d;
+  if constexpr (COLOR) {
+    float4 p = __ldg(reinterpret_cast<const float4*>(f.img) + pix);  // :45 + colour, one gather
+    d = p.x; h.c0 = p.y; h.c1 = p.z; h.c2 = p.w;
+  } else {
+    d = __ldg(reinterpret_cast<const float*>(f.img) + pix);
+    h.c0 = h.c1 = h.c2 = 0.0f;
+  }
+  // per-instance mask: masked depth = depth * (mask/255) (reference src/Engine.cpp:192-193)
+  if constexpr (MASK) d = __ldg(mask + pix) >= 128 ? d : 0.0f;
+  return d;
+}
+
+// Literal spelling of src/tsdf.cu:39-53.
 template <bool COLOR, bool LE_TRUNC, bool MASK>
-__device__ __forceinline__ bool probe(const FrameP& f, const GridP& g, const uint8_t* mask, float camx,
-                                      float camy, float camz, float& dist, float& ncol) {
+__device__ __forceinline__ Hit probe_literal_body(const FrameP& f, const GridP& g, const uint8_t* mask,
+                                                  float camx, float camy, float camz) {
+  Hit h;
   bool ok = camz > 0.0f;                                  // :39
   float u = f.fx * (camx / camz) + f.cx;                  // :41
   float v = f.fy * (camy / camz) + f.cy;                  // :42
   float ru = roundf(u), rv = roundf(v);
   ok = ok && ru >= 0.0f && ru < (float)g.W && rv >= 0.0f && rv < (float)g.H;  // :43
   int pix = ok ? (int)rv * g.W + (int)ru : 0;
-  float d;
-  if constexpr (COLOR) {
-    uint2 p = __ldg(reinterpret_cast<const uint2*>(f.img) + pix);  // :45 (+ colour)
-    d = __uint_as_float(p.x);
-    ncol = __uint_as_float(p.y);
-  } else {
-    d = __ldg(reinterpret_cast<const float*>(f.img) + pix);
-    ncol = 0.0f;
-  }
-  // per-instance mask: masked depth = depth * (mask/255) (reference src/Engine.cpp:192-193),
-  // i.e. the sample is invalid (0) where the 8-bit mask rounds to 0
-  if constexpr (MASK) d = __ldg(mask + pix) >= 128 ? d : 0.0f;
+  float d = fetch<COLOR, MASK>(f, mask, pix, h);
   ok = ok && !(d <= 0.0f);                                // :46 (d > max_depth folded into prep)
   float diff = d - camz;                                  // :48
   if constexpr (LE_TRUNC) ok = ok && !(diff <= -g.trunc); // :49
   else                    ok = ok && !(diff < -g.trunc);
-  dist = fminf(1.0f, diff / g.trunc);                     // :53
-  return ok;
+  h.dist = fminf(1.0f, diff / g.trunc);                   // :53
+  h.ok = ok;
+  return h;
+}
+// out-of-line copy used as the rare fallback of the exact path (keeps the hot loop small)
+template <bool COLOR, bool LE_TRUNC, bool MASK>
+__device__ __noinline__ Hit probe_literal_cold(const void* img, float fx, float cx, float fy, float cy,
+                                               float trunc, int W, int H, const uint8_t* mask,
+                                               float camx, float camy, float camz) {
+  FrameP f; f.img = img; f.fx = fx; f.cx = cx; f.fy = fy; f.cy = cy;
+  GridP g; g.trunc = trunc; g.W = W; g.H = H;
+  return probe_literal_body<COLOR, LE_TRUNC, MASK>(f, g, mask, camx, camy, camz);
 }
 
-// Colour running average on the float-packed value (upstream algorithm).
-__device__ __forceinline__ float blend_color(float oc, float nc, float w0, float w1) {
+// Same decisions and the same bits with the exactmath forms.  Operands outside the safe
+// exponent window (never seen on real data) take the literal path.
+template <bool COLOR, bool LE_TRUNC, bool MASK>
+__device__ __forceinline__ Hit probe_exact(const FrameP& f, const GridP& g, const uint8_t* mask,
+                                           float camx, float camy, float camz) {
+  const bool inr = em::in_safe_range(camz);               // implies camz > 0            :39
+  if (__builtin_expect(!inr && camz > 0.0f, 0))
+    return probe_literal_cold<COLOR, LE_TRUNC, MASK>(f.img, f.fx, f.cx, f.fy, f.cy, g.trunc, g.W, g.H, mask,
+                                                     camx, camy, camz);
+  Hit h;
+  const float yz = em::rcp_rn(camz);
+  const float u = f.fx * em::div_rn(camx, camz, yz) + f.cx;   // :41
+  const float v = f.fy * em::div_rn(camy, camz, yz) + f.cy;   // :42
+  // (int)roundf(u) in [0,W)  <=>  -0.5 < u < W-0.5   (roundf is half-away-from-zero)   :43
+  bool ok = inr && u > -0.5f && u < g.w_lim && v > -0.5f && v < g.h_lim;
+  const int px = em::round_half_away_nonneg_int(u);
+  const int py = em::round_half_away_nonneg_int(v);
+  const int pix = ok ? py * g.W + px : 0;
+  const float d = fetch<COLOR, MASK>(f, mask, pix, h);
+  ok = ok && !(d <= 0.0f);                                // :46
+  const float diff = d - camz;                            // :48
+  if constexpr (LE_TRUNC) ok = ok && !(diff <= -g.trunc); // :49
+  else                    ok = ok && !(diff < -g.trunc);
+  h.dist = fminf(1.0f, em::div_rn(diff, g.trunc, g.inv_trunc));  // :53
+  h.ok = ok;
+  return h;
+}
+
+// Colour running average (upstream algorithm) on the float-packed value
+// B*65536 + G*256 + R.  Literal spelling:
+__device__ __forceinline__ float blend_literal(float oc, float nc0, float nc1, float nc2, float w0, float w1) {
   float ob = floorf(oc / 65536.0f);
   float og = floorf((oc - ob * 65536.0f) / 256.0f);
   float orr = oc - ob * 65536.0f - og * 256.0f;
-  float nb = floorf(nc / 65536.0f);
-  float ng = floorf((nc - nb * 65536.0f) / 256.0f);
-  float nr = nc - nb * 65536.0f - ng * 256.0f;
-  nb = fminf(roundf((ob * w0 + nb) / w1), 255.0f);
-  ng = fminf(roundf((og * w0 + ng) / w1), 255.0f);
-  nr = fminf(roundf((orr * w0 + nr) / w1), 255.0f);
+  float nb = fminf(roundf((ob * w0 + nc2) / w1), 255.0f);
+  float ng = fminf(roundf((og * w0 + nc1) / w1), 255.0f);
+  float nr = fminf(roundf((orr * w0 + nc0) / w1), 255.0f);
   return nb * 65536.0f + ng * 256.0f + nr;
+}
+
+// Exact forms: the packed values are integers < 2^24, so the channel split is integer byte
+// extraction (identical to the floor/divide chain), the quotients share 1/w1, and
+// min(roundf(q),255) == roundf(min(q,255)) for q >= 0.
+__device__ __forceinline__ float blend_exact(float oc, float nc0, float nc1, float nc2, float w0,
+                                             float w1, float yw) {
+  const unsigned oci = (unsigned)oc;
+  const float ob = em::byte_to_float<2>(oci), og = em::byte_to_float<1>(oci), orr = em::byte_to_float<0>(oci);
+  const int vb = em::round_half_away_nonneg_int(fminf(em::div_rn(ob * w0 + nc2, w1, yw), 255.0f));
+  const int vg = em::round_half_away_nonneg_int(fminf(em::div_rn(og * w0 + nc1, w1, yw), 255.0f));
+  const int vr = em::round_half_away_nonneg_int(fminf(em::div_rn(orr * w0 + nc0, w1, yw), 255.0f));
+  return (float)((vb << 16) | (vg << 8) | vr);
+}
+
+// Integer-weight fast path (host guarantees: every stored weight is an integer <= 4094 and
+// obs_weight == 1, i.e. the volume has only ever been integrated with obs_weight 1 for fewer
+// than 4095 frames).  Then num = o*w0 + n is an exact integer, num/w1 is either an exact
+// half-integer tie or at least 1/(2*w1) >= 1.2e-4 away from one, while the error of
+// num * yp (yp = 1/w1 inflated by 2..4 ulp, so ties land on the upper side) is < 6.2e-5:
+// floor(num*yp + 0.5) == (int)roundf(RN(num/w1)), and the quotient never exceeds 255.
+__device__ __forceinline__ float blend_intw(float oc, float nc0, float nc1, float nc2, float w0, float yw) {
+  const unsigned oci = (unsigned)oc;
+  const float ob = em::byte_to_float<2>(oci), og = em::byte_to_float<1>(oci), orr = em::byte_to_float<0>(oci);
+  const float yp = __fmaf_rn(yw, 1.78813934e-7f /* 3*2^-24 */, yw);
+  const int vb = em::floor_prod_plus_half_int(__fmaf_rn(ob, w0, nc2), yp);
+  const int vg = em::floor_prod_plus_half_int(__fmaf_rn(og, w0, nc1), yp);
+  const int vr = em::floor_prod_plus_half_int(__fmaf_rn(orr, w0, nc0), yp);
+  return (float)((vb << 16) | (vg << 8) | vr);
+}
+
+// One voxel update, src/tsdf.cu:54-57 (+ colour).  WMODE: 0 general, 1 integer weights.
+template <bool COLOR, int MATH, int WMODE>
+__device__ __forceinline__ void update_voxel(float& t, float& w, float& col, const Hit& h, float obs) {
+  const float w0 = w;                                   // :54
+  const float w1 = w0 + obs;                            // :55
+  w = w1;                                               // :56
+  if constexpr (MATH == MATH_LITERAL) {
+    t = (t * w0 + h.dist) / w1;                         // :57
+    if constexpr (COLOR) col = blend_literal(col, h.c0, h.c1, h.c2, w0, w1);
+  } else {
+    const float yw = em::rcp_rn(w1);
+    t = em::div_rn(t * w0 + h.dist, w1, yw);            // :57
+    if constexpr (COLOR) {
+      if constexpr (WMODE == 1) col = blend_intw(col, h.c0, h.c1, h.c2, w0, yw);
+      else                      col = blend_exact(col, h.c0, h.c1, h.c2, w0, w1, yw);
+    }
+  }
 }
 
 // ZFAST : slab layout [x][y][zl]  (row = x*Dy + y, fast = zl)   — plugin surface
 // !ZFAST: slab layout [zl][y][x]  (row = zl*Dy + y, fast = x)   — class TSDF, src/tsdf.cu:52
-// Row table entry per frame: ZFAST  {A0,A1,A2}            A_k = c[k]*t0 + c[4+k]*t1
-//                            !ZFAST {Y0,Y1,Y2,Z0,Z1,Z2}   Y_k = c[4+k]*t1, Z_k = c[8+k]*t2
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, bool MASK>
-__device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8_t* mask, float* tab,
+// Row table entry per frame (padded to 128-bit loads):
+//   ZFAST  {A0,A1,A2,-}                A_k = c[k]*t0 + c[4+k]*t1
+//   !ZFAST {Y0,Y1,Y2,-, Z0,Z1,Z2,-}    Y_k = c[4+k]*t1, Z_k = c[8+k]*t2
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, bool MASK, int MATH, int WMODE>
+__device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8_t* mask, float4* tab,
                                                int tpr_log2, int rows_per_block) {
-  constexpr int NT = ZFAST ? 3 : 6;
+  constexpr int NT = ZFAST ? 1 : 2;  // float4 per row per frame
   const GridP& g = P.g;
   const int n_rows = g.n_mid * g.n_slow;
   const int row0 = blockIdx.x * rows_per_block;
@@ -120,18 +225,16 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       for (int f = 0; f < NF; ++f) {
         const float* c = P.f[f].c;
         float t1 = by - c[7];                                      // :34
-        float* e = tab + (lr * NF + f) * NT;
+        float4* e = tab + (lr * NF + f) * NT;
         if constexpr (ZFAST) {
           float bx = g.ox + (float)slow * g.vs;                    // :27
           float t0 = bx - c[3];                                    // :33
-          e[0] = c[0] * t0 + c[4] * t1;
-          e[1] = c[1] * t0 + c[5] * t1;
-          e[2] = c[2] * t0 + c[6] * t1;
+          e[0] = make_float4(c[0] * t0 + c[4] * t1, c[1] * t0 + c[5] * t1, c[2] * t0 + c[6] * t1, 0.0f);
         } else {
           float bz = g.oz + (float)(g.z0 + slow) * g.vs;           // :29 (global z)
           float t2 = bz - c[11];                                   // :35
-          e[0] = c[4] * t1; e[1] = c[5] * t1; e[2] = c[6] * t1;
-          e[3] = c[8] * t2; e[4] = c[9] * t2; e[5] = c[10] * t2;
+          e[0] = make_float4(c[4] * t1, c[5] * t1, c[6] * t1, 0.0f);
+          e[1] = make_float4(c[8] * t2, c[9] * t2, c[10] * t2, 0.0f);
         }
       }
     }
@@ -146,41 +249,55 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   const int f0 = (blockIdx.y * tpr + tf) * VEC;
   if (f0 >= g.n_fast) return;
 
-  float bf[VEC];  // base-frame coordinate of each voxel of the run along the fast axis
+  // per-run terms: the products of the fast-axis coordinate (registers, frame 0 only when
+  // several frames are fused: the others are recomputed per row to bound register use)
+  float bf[VEC];
+  float q0[VEC], q1[VEC], q2[VEC];
 #pragma unroll
   for (int j = 0; j < VEC; ++j) {
     if constexpr (ZFAST) bf[j] = g.oz + (float)(g.z0 + f0 + j) * g.vs;   // :29
     else                 bf[j] = g.ox + (float)(f0 + j) * g.vs;           // :27
+    const float* c = P.f[0].c;
+    const float tt = bf[j] - (ZFAST ? c[11] : c[3]);                      // :35 / :33
+    q0[j] = (ZFAST ? c[8] : c[0]) * tt;
+    q1[j] = (ZFAST ? c[9] : c[1]) * tt;
+    q2[j] = (ZFAST ? c[10] : c[2]) * tt;
   }
 
   unsigned int n_written = 0;
   for (int lr = tr; lr < rows_per_block; lr += rp) {
     const int r = row0 + lr;
     if (r >= n_rows) break;
-    bool okf[NF][VEC];
-    float distf[NF][VEC];
-    float ncolf[NF][VEC];
+    Hit hit[NF][VEC];
     bool any = false;
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
       const float* c = P.f[f].c;
-      const float* e = tab + (lr * NF + f) * NT;
+      const float4* e = tab + (lr * NF + f) * NT;
+      const float4 ea = e[0];
+      float4 eb = ea;
+      if constexpr (!ZFAST) eb = e[1];
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
+        float p0, p1, p2;
+        if (f == 0) { p0 = q0[j]; p1 = q1[j]; p2 = q2[j]; }
+        else {
+          const float tt = bf[j] - (ZFAST ? c[11] : c[3]);
+          p0 = (ZFAST ? c[8] : c[0]) * tt; p1 = (ZFAST ? c[9] : c[1]) * tt; p2 = (ZFAST ? c[10] : c[2]) * tt;
+        }
         float camx, camy, camz;
         if constexpr (ZFAST) {
-          float t2 = bf[j] - c[11];                 // :35
-          camx = e[0] + c[8] * t2;                  // :36
-          camy = e[1] + c[9] * t2;                  // :37
-          camz = e[2] + c[10] * t2;                 // :38
+          camx = ea.x + p0;                         // :36
+          camy = ea.y + p1;                         // :37
+          camz = ea.z + p2;                         // :38
         } else {
-          float t0 = bf[j] - c[3];                  // :33
-          camx = (c[0] * t0 + e[0]) + e[3];
-          camy = (c[1] * t0 + e[1]) + e[4];
-          camz = (c[2] * t0 + e[2]) + e[5];
+          camx = (p0 + ea.x) + eb.x;
+          camy = (p1 + ea.y) + eb.y;
+          camz = (p2 + ea.z) + eb.z;
         }
-        okf[f][j] = probe<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, camx, camy, camz, distf[f][j], ncolf[f][j]);
-        any = any || okf[f][j];
+        if constexpr (MATH == MATH_LITERAL) hit[f][j] = probe_literal_body<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, camx, camy, camz);
+        else                                hit[f][j] = probe_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, camx, camy, camz);
+        any = any || hit[f][j].ok;
       }
     }
     if (!any) continue;  // no volume traffic for a run with no update
@@ -190,17 +307,17 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     load_vec<VEC>(g.tsdf + base, t);
     load_vec<VEC>(g.weight + base, w);
     if constexpr (COLOR) load_vec<VEC>(g.color + base, col);
+    else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) col[j] = 0.0f;
+    }
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
       const float obs = P.f[f].obs_weight;
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        if (okf[f][j]) {
-          float w0 = w[j];                          // :54
-          float w1 = w0 + obs;                      // :55
-          w[j] = w1;                                // :56
-          t[j] = (t[j] * w0 + distf[f][j]) / w1;    // :57
-          if constexpr (COLOR) col[j] = blend_color(col[j], ncolf[f][j], w0, w1);
+        if (hit[f][j].ok) {
+          update_voxel<COLOR, MATH, WMODE>(t[j], w[j], col[j], hit[f][j], obs);
           ++n_written;
         }
       }
@@ -215,105 +332,133 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   if ((threadIdx.x & 31) == 0 && n_written) atomicAdd(g.written, (unsigned long long)n_written);
 }
 
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC>
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
 __global__ void __launch_bounds__(kThreads)
 k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_block) {
-  __shared__ float tab[kMaxRowsPerBlock * NF * (ZFAST ? 3 : 6)];
-  integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false>(P, nullptr, tab, tpr_log2, rows_per_block);
+  __shared__ float4 tab[kMaxRowsPerBlock * NF * (ZFAST ? 1 : 2)];
+  integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block);
 }
 
 // Batched per-instance volumes (config 5): blockIdx.z selects a descriptor {grid, pose, mask}
 // from global memory; one launch covers every active instance.
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int VEC>
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int VEC, int WMODE>
 __global__ void __launch_bounds__(kThreads)
 k_integrate_batch(const BatchDesc* __restrict__ descs, int tpr_log2, int rows_per_block) {
-  __shared__ float tab[kMaxRowsPerBlock * (ZFAST ? 3 : 6)];
+  __shared__ float4 tab[kMaxRowsPerBlock * (ZFAST ? 1 : 2)];
   __shared__ LaunchP<1> P;
   __shared__ const uint8_t* mask;
   const BatchDesc& d = descs[blockIdx.z];
   if (threadIdx.x == 0) { P.g = d.g; P.f[0] = d.f; mask = d.mask; }
   __syncthreads();
-  if (mask) integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, true>(P, mask, tab, tpr_log2, rows_per_block);
-  else      integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, false>(P, nullptr, tab, tpr_log2, rows_per_block);
+  if (mask) integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, true, MATH_EXACT, WMODE>(P, mask, tab, tpr_log2, rows_per_block);
+  else      integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, false, MATH_EXACT, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block);
 }
 
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC>
-int launch_t(const tsdf_vol* v, const GridP& g, const FrameP* frames, cudaStream_t st) {
+struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
+
+Geometry plan(int n_fast, int n_rows, int vec, int nz) {
+  Geometry q;
+  int vec_per_row = (n_fast + vec - 1) / vec;
+  q.tpr_log2 = 0;
+  while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < kThreads) ++q.tpr_log2;
+  int tpr = 1 << q.tpr_log2;
+  int rp = kThreads / tpr;
+  q.rows_per_block = rp * 16;
+  if (q.rows_per_block > kMaxRowsPerBlock) q.rows_per_block = kMaxRowsPerBlock;
+  if (q.rows_per_block < rp) q.rows_per_block = rp;
+  q.grid = dim3((n_rows + q.rows_per_block - 1) / q.rows_per_block, (vec_per_row + tpr - 1) / tpr, nz);
+  return q;
+}
+
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
+int launch_t(const GridP& g, const FrameP* frames, cudaStream_t st) {
   LaunchP<NF> P;
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
-  int vec_per_row = (g.n_fast + VEC - 1) / VEC;
-  int tpr_log2 = 0;
-  while ((1 << tpr_log2) < vec_per_row && (1 << tpr_log2) < kThreads) ++tpr_log2;
-  int tpr = 1 << tpr_log2;
-  int rp = kThreads / tpr;
-  int rows_per_block = rp * 16;
-  if (rows_per_block > kMaxRowsPerBlock) rows_per_block = kMaxRowsPerBlock;
-  if (rows_per_block < rp) rows_per_block = rp;
-  int n_rows = g.n_mid * g.n_slow;
-  dim3 grid((n_rows + rows_per_block - 1) / rows_per_block, (vec_per_row + tpr - 1) / tpr, 1);
-  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC><<<grid, kThreads, 0, st>>>(P, tpr_log2, rows_per_block);
+  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1);
+  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }
 
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int VEC>
-int launch_nf(const tsdf_vol* v, const GridP& g, const FrameP* frames, int nf, cudaStream_t st) {
-  switch (nf) {
-    case 1: return launch_t<ZFAST, COLOR, LE_TRUNC, 1, VEC>(v, g, frames, st);
-    case 2: return launch_t<ZFAST, COLOR, LE_TRUNC, 2, VEC>(v, g, frames, st);
-    case 4: return launch_t<ZFAST, COLOR, LE_TRUNC, 4, VEC>(v, g, frames, st);
-    case 8: return launch_t<ZFAST, COLOR, LE_TRUNC, 8, VEC>(v, g, frames, st);
+// layout (and with it the truncation compare) x colour x integer-weight mode, for one NF/VEC/MATH
+template <int NF, int VEC, int MATH>
+int launch_sem(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, cudaStream_t st) {
+  if (zfast) {
+    if (color) {
+      if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<true, true, false, NF, VEC, MATH, 1>(g, fr, st); }
+      return launch_t<true, true, false, NF, VEC, MATH, 0>(g, fr, st);
+    }
+    return launch_t<true, false, false, NF, VEC, MATH, 0>(g, fr, st);
   }
-  tsdf_set_error("launch_integrate: unsupported fused frame count %d", nf);
-  return TSDF_E_INVALID;
+  if (color) {
+    if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<false, true, true, NF, VEC, MATH, 1>(g, fr, st); }
+    return launch_t<false, true, true, NF, VEC, MATH, 0>(g, fr, st);
+  }
+  return launch_t<false, false, true, NF, VEC, MATH, 0>(g, fr, st);
 }
 
 }  // namespace
 
-// nf in {1,2,4,8}.  The semantics of the handle pick layout and truncation compare.
-int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st) {
-  GridP g;
+void fill_grid_params(const tsdf_vol* v, bool color, GridP* g) {
   const tsdf_config& c = v->cfg;
-  g.n_fast = v->zfast ? v->dzl : c.dim_x;
-  g.n_mid = c.dim_y;
-  g.n_slow = v->zfast ? c.dim_x : v->dzl;
-  g.z0 = c.z_begin;
-  g.ox = c.origin[0]; g.oy = c.origin[1]; g.oz = c.origin[2];
-  g.vs = c.voxel_size; g.trunc = c.trunc_margin;
-  g.W = c.im_w; g.H = c.im_h;
-  g.tsdf = v->d_tsdf; g.weight = v->d_weight; g.color = color ? v->d_color : nullptr;
-  g.written = v->d_written;
-  const bool vec4 = (g.n_fast % 4) == 0;
-  const bool le = c.semantics == TSDF_SEM_TSDFCU;
-#define DISPATCH(ZF, CO, LE)                                                     \
-  (vec4 ? launch_nf<ZF, CO, LE, 4>(v, g, frames, nf, st) : launch_nf<ZF, CO, LE, 1>(v, g, frames, nf, st))
-  // layout and truncation compare are both fixed by the semantics (tsdf_create)
-  (void)le;
-  if (v->zfast) return color ? DISPATCH(true, true, false) : DISPATCH(true, false, false);
-  return color ? DISPATCH(false, true, true) : DISPATCH(false, false, true);
-#undef DISPATCH
+  g->n_fast = v->zfast ? v->dzl : c.dim_x;
+  g->n_mid = c.dim_y;
+  g->n_slow = v->zfast ? c.dim_x : v->dzl;
+  g->z0 = c.z_begin;
+  g->ox = c.origin[0]; g->oy = c.origin[1]; g->oz = c.origin[2];
+  g->vs = c.voxel_size; g->trunc = c.trunc_margin;
+  g->inv_trunc = 1.0f / c.trunc_margin;   // host IEEE division: correctly rounded reciprocal
+  g->w_lim = (float)c.im_w - 0.5f;        // exact for W < 2^23
+  g->h_lim = (float)c.im_h - 0.5f;
+  g->W = c.im_w; g->H = c.im_h;
+  g->tsdf = v->d_tsdf; g->weight = v->d_weight; g->color = color ? v->d_color : nullptr;
+  g->written = v->d_written;
 }
 
-// All instances of a batch share semantics, colour mode and grid dims class (VEC); the grid
-// is sized for the largest instance.  descs: n_active device descriptors.
+// nf frames fused into one pass (nf in {1,2,4,8}; other counts and the literal variant fall
+// back to a sequence of launches, which is bit-identical).  wmode 1 = the host guarantees
+// integer weights <= 4094 and obs_weight == 1 for every frame (see blend_intw).
+int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st) {
+  GridP g;
+  fill_grid_params(v, color, &g);
+  const bool vec4 = (g.n_fast % 4) == 0;
+  const bool literal = v->variant == 1;
+  const int wmode = (color && v->wmode_ok) ? 1 : 0;
+  if (literal || !vec4 || !(nf == 1 || nf == 2 || nf == 4 || nf == 8)) {
+    for (int i = 0; i < nf; ++i) {
+      int rc;
+      if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, st)
+                             : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, st);
+      else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, st)
+                             : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, st);
+      if (rc) return rc;
+    }
+    return TSDF_OK;
+  }
+  switch (nf) {
+    case 1: return launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
+    case 2: return launch_sem<2, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
+    case 4: return launch_sem<4, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
+    default: return launch_sem<8, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
+  }
+}
+
+// All instances of a batch share semantics and colour mode; the grid is sized for the
+// largest instance.  descs: n_active device descriptors.
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
-                           bool zfast, bool color, bool vec4, cudaStream_t st) {
-  const int VECv = vec4 ? 4 : 1;
-  int vec_per_row = (max_fast + VECv - 1) / VECv;
-  int tpr_log2 = 0;
-  while ((1 << tpr_log2) < vec_per_row && (1 << tpr_log2) < kThreads) ++tpr_log2;
-  int tpr = 1 << tpr_log2;
-  int rp = kThreads / tpr;
-  int rows_per_block = rp * 16;
-  if (rows_per_block > kMaxRowsPerBlock) rows_per_block = kMaxRowsPerBlock;
-  if (rows_per_block < rp) rows_per_block = rp;
-  dim3 grid((max_rows + rows_per_block - 1) / rows_per_block, (vec_per_row + tpr - 1) / tpr, n_active);
-#define LB(ZF, CO, LE, V) k_integrate_batch<ZF, CO, LE, V><<<grid, kThreads, 0, st>>>(d_descs, tpr_log2, rows_per_block)
-  if (zfast) { if (color) { if (vec4) LB(true, true, false, 4); else LB(true, true, false, 1); }
-               else       { if (vec4) LB(true, false, false, 4); else LB(true, false, false, 1); } }
-  else       { if (color) { if (vec4) LB(false, true, true, 4); else LB(false, true, true, 1); }
-               else       { if (vec4) LB(false, false, true, 4); else LB(false, false, true, 1); } }
+                           bool zfast, bool color, bool vec4, int wmode, cudaStream_t st) {
+  Geometry q = plan(max_fast, max_rows, vec4 ? 4 : 1, n_active);
+#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block)
+  if (zfast) {
+    if (color) { if (wmode == 1) { if (vec4) LB(true, true, false, 4, 1); else LB(true, true, false, 1, 1); }
+                 else            { if (vec4) LB(true, true, false, 4, 0); else LB(true, true, false, 1, 0); } }
+    else       { if (vec4) LB(true, false, false, 4, 0); else LB(true, false, false, 1, 0); }
+  } else {
+    if (color) { if (wmode == 1) { if (vec4) LB(false, true, true, 4, 1); else LB(false, true, true, 1, 1); }
+                 else            { if (vec4) LB(false, true, true, 4, 0); else LB(false, true, true, 1, 0); } }
+    else       { if (vec4) LB(false, false, true, 4, 0); else LB(false, false, true, 1, 0); }
+  }
 #undef LB
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
