@@ -262,6 +262,12 @@ int tsdf_timer_stop(tsdf_vol* v, float* ms);
 int tsdf_kernel_timing(tsdf_vol* v, int enable);
 int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset);
 
+/* Validation hook: brute-forces the exact-arithmetic forms of the hot loop (shared
+ * reciprocal + Markstein division, round-down magic rounding, colour blends) against the
+ * IEEE operators on the device.  fails[0..4] = mismatches of {reciprocal, quotient, rounding,
+ * general colour blend, integer-weight colour blend (exhaustive)}; all must be 0.  */
+int tsdf_selftest_exactmath(int device, int64_t iters_per_thread, uint64_t seed, int64_t fails[5]);
+
 #ifdef __cplusplus
 }
 #endif

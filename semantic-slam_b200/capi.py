@@ -98,6 +98,7 @@ SIGNATURES = {
     "tsdf_timer_stop": (_I, [_VP, C.POINTER(_F)]),
     "tsdf_kernel_timing": (_I, [_VP, _I]),
     "tsdf_kernel_timing_read": (_I, [_VP, C.POINTER(C.c_double), C.POINTER(_I64), _I]),
+    "tsdf_selftest_exactmath": (_I, [_I, _I64, C.c_uint64, C.POINTER(_I64)]),
 }
 
 _lib = None

@@ -35,6 +35,11 @@ template <int VEC> struct VecT;
 template <> struct VecT<4> { using type = float4; };
 template <> struct VecT<1> { using type = float; };
 
+__device__ __forceinline__ void prefetch_line(const float* p, int mode) {
+  if (mode == 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  else           asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+
 template <int VEC>
 __device__ __forceinline__ void load_vec(const float* p, float (&v)[VEC]) {
   if constexpr (VEC == 4) {
@@ -141,47 +146,6 @@ __device__ __forceinline__ Hit probe_exact(const FrameP& f, const GridP& g, cons
   return h;
 }
 
-// Colour running average (upstream algorithm) on the float-packed value
-// B*65536 + G*256 + R.  Literal spelling:
-__device__ __forceinline__ float blend_literal(float oc, float nc0, float nc1, float nc2, float w0, float w1) {
-  float ob = floorf(oc / 65536.0f);
-  float og = floorf((oc - ob * 65536.0f) / 256.0f);
-  float orr = oc - ob * 65536.0f - og * 256.0f;
-  float nb = fminf(roundf((ob * w0 + nc2) / w1), 255.0f);
-  float ng = fminf(roundf((og * w0 + nc1) / w1), 255.0f);
-  float nr = fminf(roundf((orr * w0 + nc0) / w1), 255.0f);
-  return nb * 65536.0f + ng * 256.0f + nr;
-}
-
-// Exact forms: the packed values are integers < 2^24, so the channel split is integer byte
-// extraction (identical to the floor/divide chain), the quotients share 1/w1, and
-// min(roundf(q),255) == roundf(min(q,255)) for q >= 0.
-__device__ __forceinline__ float blend_exact(float oc, float nc0, float nc1, float nc2, float w0,
-                                             float w1, float yw) {
-  const unsigned oci = (unsigned)oc;
-  const float ob = em::byte_to_float<2>(oci), og = em::byte_to_float<1>(oci), orr = em::byte_to_float<0>(oci);
-  const int vb = em::round_half_away_nonneg_int(fminf(em::div_rn(ob * w0 + nc2, w1, yw), 255.0f));
-  const int vg = em::round_half_away_nonneg_int(fminf(em::div_rn(og * w0 + nc1, w1, yw), 255.0f));
-  const int vr = em::round_half_away_nonneg_int(fminf(em::div_rn(orr * w0 + nc0, w1, yw), 255.0f));
-  return (float)((vb << 16) | (vg << 8) | vr);
-}
-
-// Integer-weight fast path (host guarantees: every stored weight is an integer <= 4094 and
-// obs_weight == 1, i.e. the volume has only ever been integrated with obs_weight 1 for fewer
-// than 4095 frames).  Then num = o*w0 + n is an exact integer, num/w1 is either an exact
-// half-integer tie or at least 1/(2*w1) >= 1.2e-4 away from one, while the error of
-// num * yp (yp = 1/w1 inflated by 2..4 ulp, so ties land on the upper side) is < 6.2e-5:
-// floor(num*yp + 0.5) == (int)roundf(RN(num/w1)), and the quotient never exceeds 255.
-__device__ __forceinline__ float blend_intw(float oc, float nc0, float nc1, float nc2, float w0, float yw) {
-  const unsigned oci = (unsigned)oc;
-  const float ob = em::byte_to_float<2>(oci), og = em::byte_to_float<1>(oci), orr = em::byte_to_float<0>(oci);
-  const float yp = __fmaf_rn(yw, 1.78813934e-7f /* 3*2^-24 */, yw);
-  const int vb = em::floor_prod_plus_half_int(__fmaf_rn(ob, w0, nc2), yp);
-  const int vg = em::floor_prod_plus_half_int(__fmaf_rn(og, w0, nc1), yp);
-  const int vr = em::floor_prod_plus_half_int(__fmaf_rn(orr, w0, nc0), yp);
-  return (float)((vb << 16) | (vg << 8) | vr);
-}
-
 // One voxel update, src/tsdf.cu:54-57 (+ colour).  WMODE: 0 general, 1 integer weights.
 template <bool COLOR, int MATH, int WMODE>
 __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, const Hit& h, float obs) {
@@ -190,13 +154,13 @@ __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, con
   w = w1;                                               // :56
   if constexpr (MATH == MATH_LITERAL) {
     t = (t * w0 + h.dist) / w1;                         // :57
-    if constexpr (COLOR) col = blend_literal(col, h.c0, h.c1, h.c2, w0, w1);
+    if constexpr (COLOR) col = em::blend_literal(col, h.c0, h.c1, h.c2, w0, w1);
   } else {
     const float yw = em::rcp_rn(w1);
     t = em::div_rn(t * w0 + h.dist, w1, yw);            // :57
     if constexpr (COLOR) {
-      if constexpr (WMODE == 1) col = blend_intw(col, h.c0, h.c1, h.c2, w0, yw);
-      else                      col = blend_exact(col, h.c0, h.c1, h.c2, w0, w1, yw);
+      if constexpr (WMODE == 1) col = em::blend_intw(col, h.c0, h.c1, h.c2, w0, yw);
+      else                      col = em::blend_exact(col, h.c0, h.c1, h.c2, w0, w1, yw);
     }
   }
 }
@@ -208,7 +172,7 @@ __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, con
 //   !ZFAST {Y0,Y1,Y2,-, Z0,Z1,Z2,-}    Y_k = c[4+k]*t1, Z_k = c[8+k]*t2
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, bool MASK, int MATH, int WMODE>
 __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8_t* mask, float4* tab,
-                                               int tpr_log2, int rows_per_block) {
+                                               int tpr_log2, int rows_per_block, int pf) {
   constexpr int NT = ZFAST ? 1 : 2;  // float4 per row per frame
   const GridP& g = P.g;
   const int n_rows = g.n_mid * g.n_slow;
@@ -265,9 +229,29 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   }
 
   unsigned int n_written = 0;
+  // Software prefetch of the NEXT row's three 128-bit runs: the volume loads can only be
+  // issued after the depth gather has decided validity, so without it every row exposes a
+  // full DRAM latency (profiles/r1_v2: 45 % of stall samples on the first use of the loaded
+  // weight).  A row is prefetched when the row before it was updated (coherent frames), and
+  // the first row of a block unconditionally.
+  bool any_prev = true;
   for (int lr = tr; lr < rows_per_block; lr += rp) {
     const int r = row0 + lr;
     if (r >= n_rows) break;
+    if (pf) {
+      if (lr == tr) {
+        const int64_t pb = (int64_t)r * g.n_fast + f0;
+        prefetch_line(g.tsdf + pb, pf);
+        prefetch_line(g.weight + pb, pf);
+        if constexpr (COLOR) prefetch_line(g.color + pb, pf);
+      }
+      if (any_prev && lr + rp < rows_per_block && r + rp < n_rows) {
+        const int64_t pb = (int64_t)(r + rp) * g.n_fast + f0;
+        prefetch_line(g.tsdf + pb, pf);
+        prefetch_line(g.weight + pb, pf);
+        if constexpr (COLOR) prefetch_line(g.color + pb, pf);
+      }
+    }
     Hit hit[NF][VEC];
     bool any = false;
 #pragma unroll
@@ -300,6 +284,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
         any = any || hit[f][j].ok;
       }
     }
+    any_prev = any;
     if (!any) continue;  // no volume traffic for a run with no update
 
     const int64_t base = (int64_t)r * g.n_fast + f0;
@@ -334,25 +319,28 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
 
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
 __global__ void __launch_bounds__(kThreads)
-k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_block) {
+k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_block, int pf) {
   __shared__ float4 tab[kMaxRowsPerBlock * NF * (ZFAST ? 1 : 2)];
-  integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block);
+  integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block, pf);
 }
 
 // Batched per-instance volumes (config 5): blockIdx.z selects a descriptor {grid, pose, mask}
 // from global memory; one launch covers every active instance.
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int VEC, int WMODE>
 __global__ void __launch_bounds__(kThreads)
-k_integrate_batch(const BatchDesc* __restrict__ descs, int tpr_log2, int rows_per_block) {
+k_integrate_batch(const BatchDesc* __restrict__ descs, int tpr_log2, int rows_per_block, int pf) {
   __shared__ float4 tab[kMaxRowsPerBlock * (ZFAST ? 1 : 2)];
   __shared__ LaunchP<1> P;
   __shared__ const uint8_t* mask;
   const BatchDesc& d = descs[blockIdx.z];
   if (threadIdx.x == 0) { P.g = d.g; P.f[0] = d.f; mask = d.mask; }
   __syncthreads();
-  if (mask) integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, true, MATH_EXACT, WMODE>(P, mask, tab, tpr_log2, rows_per_block);
-  else      integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, false, MATH_EXACT, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block);
+  if (mask) integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, true, MATH_EXACT, WMODE>(P, mask, tab, tpr_log2, rows_per_block, pf);
+  else      integrate_body<ZFAST, COLOR, LE_TRUNC, 1, VEC, false, MATH_EXACT, WMODE>(P, nullptr, tab, tpr_log2, rows_per_block, pf);
 }
+
+int g_prefetch_mode = 1;  // 0 off, 1 L2, 2 L1 (set per launch from the handle's variant bits)
+int g_rows_mult = 16;
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
 
@@ -363,7 +351,7 @@ Geometry plan(int n_fast, int n_rows, int vec, int nz) {
   while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < kThreads) ++q.tpr_log2;
   int tpr = 1 << q.tpr_log2;
   int rp = kThreads / tpr;
-  q.rows_per_block = rp * 16;
+  q.rows_per_block = rp * g_rows_mult;
   if (q.rows_per_block > kMaxRowsPerBlock) q.rows_per_block = kMaxRowsPerBlock;
   if (q.rows_per_block < rp) q.rows_per_block = rp;
   q.grid = dim3((n_rows + q.rows_per_block - 1) / q.rows_per_block, (vec_per_row + tpr - 1) / tpr, nz);
@@ -372,11 +360,12 @@ Geometry plan(int n_fast, int n_rows, int vec, int nz) {
 
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
 int launch_t(const GridP& g, const FrameP* frames, cudaStream_t st) {
+  const int pf = g_prefetch_mode;
   LaunchP<NF> P;
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
   Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1);
-  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block);
+  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }
@@ -423,7 +412,11 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   GridP g;
   fill_grid_params(v, color, &g);
   const bool vec4 = (g.n_fast % 4) == 0;
-  const bool literal = v->variant == 1;
+  const bool literal = (v->variant & 1) != 0;
+  // A/B knobs (tsdf_set_variant): bit0 literal math; bits1-2 prefetch 1=L2 2=L1 (default L2);
+  // bit5 prefetch off; bits3-4 rows per block x64 / x32 (default x16)
+  g_prefetch_mode = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
+  g_rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : 16);
   const int wmode = (color && v->wmode_ok) ? 1 : 0;
   if (literal || !vec4 || !(nf == 1 || nf == 2 || nf == 4 || nf == 8)) {
     for (int i = 0; i < nf; ++i) {
@@ -449,7 +442,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st) {
   Geometry q = plan(max_fast, max_rows, vec4 ? 4 : 1, n_active);
-#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block)
+#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, g_prefetch_mode)
   if (zfast) {
     if (color) { if (wmode == 1) { if (vec4) LB(true, true, false, 4, 1); else LB(true, true, false, 1, 1); }
                  else            { if (vec4) LB(true, true, false, 4, 0); else LB(true, true, false, 1, 0); } }
