@@ -1,0 +1,68 @@
+"""Worker for the multi-GPU parity test: launched by torchrun with N ranks, one GPU each.
+Every rank integrates its z-slab from frames broadcast by rank 0 over NCCL, checks the slab
+against the oracle's slab, and the root checks the gathered point cloud against the oracle's
+whole-grid extraction.  Exits non-zero on any mismatch."""
+import importlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    import torch
+    import torch.distributed as dist
+    from oracle.oracle import Oracle, SEM_TSDFCU, SEM_FUSIONPY
+    pkg = importlib.import_module("semantic-slam_b200")
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    o = Oracle()
+    synth = pkg.synth
+    dims, vs = (48, 40, 72), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=4, seed=77)   # same seed => same data on all ranks
+    for sem, color in ((SEM_FUSIONPY, True), (SEM_TSDFCU, False)):
+        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color)
+        uid = pkg.dist.exchange_uid(pkg.dist.make_nccl_uid, rank, dist, dev)
+        sv = pkg.dist.ShardedVolume(cfg, rank, world, local, uid)
+        zr = (sv.vol.cfg.z_begin, sv.vol.cfg.z_end)
+        assert zr == pkg.slab_range(dims[2], world, rank)
+        for d, rgb, T in frames:
+            if rank == 0:   # only the root holds the images; poses are control-plane metadata
+                sv.integrate_bcast(d, rgb if color else None, T)
+            else:
+                sv.integrate_bcast(None, None, T)
+        sv.sync()
+        gt, gw, gc = sv.vol.download()
+        p = o.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, sem, zr)
+        t, w, c = o.new_volume(p, color)
+        for d, rgb, T in frames:
+            o.integrate(p, T.reshape(16), d, o.pack_color(rgb) if color else None, 1.0, t, w, c)
+        assert np.array_equal(gw, w), f"rank {rank}: weights differ"
+        assert np.array_equal(gt.view(np.uint32), t.view(np.uint32)), f"rank {rank}: tsdf differs"
+        if color:
+            assert np.array_equal(gc, c), f"rank {rank}: colour differs"
+        xyz, rgbp, idx, n = sv.gather_points()
+        if rank == 0:
+            pw = o.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, sem)
+            tw, ww, cw = o.new_volume(pw, color)
+            for d, rgb, T in frames:
+                o.integrate(pw, T.reshape(16), d, o.pack_color(rgb) if color else None, 1.0, tw, ww, cw)
+            oxyz, orgb, oidx = o.extract(pw, tw, ww, cw)
+            assert n == len(oidx) and np.array_equal(idx, oidx), "gathered index set differs"
+            assert np.array_equal(xyz.view(np.uint32), oxyz.view(np.uint32))
+            if color:
+                assert np.array_equal(rgbp, orgb)
+        sv.close()
+        dist.barrier()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("dist_worker ok", world)
+
+
+if __name__ == "__main__":
+    main()
