@@ -1,0 +1,131 @@
+// TSDFfusion.hpp — header-only C++ shim with the reference's `class TSDFfusion` surface
+// (reference include/TSDFfusion.hpp:25-65, src/TSDFfusion.cpp:25-105) over the C ABI.
+//
+// The reference class embeds a CPython interpreter and forwards to a module-global
+// fusion.TSDFVolume(vol_bnds=[0,10]^3, voxel_size=0.02) with hard-coded TUM3 intrinsics
+// (src/TSDFfusion.py.in:21-29).  This shim keeps that contract — default constructor builds
+// the same 500^3 volume, Integrate(imRGB, imD) fuses one frame — without any interpreter
+// ("Host code stays C++", north_star).  The three defects that stop the shipped wiring from
+// running are documented, not reproduced:
+//   * the C++ side passes 2 arguments to a 3-parameter Python function (pose missing)
+//     -> Integrate takes the pose explicitly; the 2-argument overload uses the last pose set
+//        with SetPose() (identity by default);
+//   * both cv::Mat are exposed with the RGB image's element type (src/TSDFfusion.cpp:89-100)
+//     -> depth is taken as CV_32F metres, colour as CV_8UC3;
+//   * the Python side references an undefined n_imgs (src/TSDFfusion.py.in:45).
+//
+// cv::Mat overloads are compiled only with -DTSDF_B200_WITH_OPENCV (OpenCV headers are not
+// present in the build container); the raw-pointer overloads are always available.
+#ifndef TSDF_B200_TSDFFUSION_HPP
+#define TSDF_B200_TSDFFUSION_HPP
+
+#include <cstdint>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "tsdf_b200.h"
+
+#ifdef TSDF_B200_WITH_OPENCV
+#include <opencv2/core.hpp>
+#endif
+
+class TSDFfusion {
+ public:
+  /// Default constructor: vol_bnds [0,10]^3, voxel_size 0.02 (src/TSDFfusion.py.in:23-29).
+  TSDFfusion() : TSDFfusion(default_bounds(), 0.02) {}
+
+  /// fusion.TSDFVolume(vol_bnds, voxel_size): dims = ceil(extent / voxel_size), trunc = 5 voxels.
+  TSDFfusion(const std::vector<double>& vol_bnds /* xmin,xmax,ymin,ymax,zmin,zmax */, double voxel_size,
+             int im_h = 480, int im_w = 640, int device = 0)
+      : vol_(nullptr) {
+    if (vol_bnds.size() != 6) throw std::invalid_argument("TSDFfusion: vol_bnds needs 6 values");
+    tsdf_config cfg;
+    check(tsdf_config_from_bounds(vol_bnds.data(), voxel_size, &cfg), "tsdf_config_from_bounds");
+    cfg.im_h = im_h;
+    cfg.im_w = im_w;
+    cfg.device = device;
+    check(tsdf_create(&cfg, &vol_), "tsdf_create");
+    cfg_ = cfg;
+    for (int i = 0; i < 16; ++i) pose_[i] = (i % 5 == 0) ? 1.0f : 0.0f;
+    const float K[9] = {535.4f, 0, 320.1f, 0, 539.2f, 247.6f, 0, 0, 1};  // src/TSDFfusion.py.in:21
+    for (int i = 0; i < 9; ++i) K_[i] = K[i];
+  }
+
+  ~TSDFfusion() {
+    if (vol_) tsdf_destroy(vol_);
+  }
+  TSDFfusion(const TSDFfusion&) = delete;
+  TSDFfusion& operator=(const TSDFfusion&) = delete;
+
+  void SetPose(const float cam_pose[16]) { for (int i = 0; i < 16; ++i) pose_[i] = cam_pose[i]; }
+  void SetIntrinsics(const float K[9]) { for (int i = 0; i < 9; ++i) K_[i] = K[i]; }
+
+  /// tsdf_vol.integrate(color_image, depth_im, cam_intr, cam_pose, obs_weight=1.) —
+  /// src/TSDFfusion.py.in:43.  rgb: H*W*3 u8, depth: H*W fp32 metres, cam_pose: row-major Twc.
+  void Integrate(const uint8_t* rgb, const float* depth, const float cam_pose[16], float obs_weight = 1.0f) {
+    check(tsdf_integrate(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate");
+  }
+  /// Non-blocking variant; inputs are borrowed until Sync().
+  void IntegrateAsync(const uint8_t* rgb, const float* depth, const float cam_pose[16], float obs_weight = 1.0f) {
+    check(tsdf_integrate_async(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate_async");
+  }
+  void Sync() { check(tsdf_sync(vol_), "tsdf_sync"); }
+
+#ifdef TSDF_B200_WITH_OPENCV
+  /// The reference's signature (include/TSDFfusion.hpp:49); pose = last SetPose().
+  void Integrate(cv::Mat imRGB, cv::Mat imD) { Integrate(imRGB, imD, cv::Mat()); }
+  void Integrate(cv::Mat imRGB, cv::Mat imD, cv::Mat cam_pose) {
+    if (imRGB.type() != CV_8UC3 || imD.type() != CV_32FC1 || !imRGB.isContinuous() || !imD.isContinuous())
+      throw std::runtime_error("TSDFfusion::Integrate: need continuous CV_8UC3 colour and CV_32FC1 depth");
+    if (imD.rows != cfg_.im_h || imD.cols != cfg_.im_w || imRGB.rows != imD.rows || imRGB.cols != imD.cols)
+      throw std::runtime_error("TSDFfusion::Integrate: frame shape differs from the volume's");
+    float T[16];
+    if (!cam_pose.empty()) {
+      cv::Mat P;
+      cam_pose.convertTo(P, CV_32F);
+      for (int r = 0; r < 4; ++r) for (int c = 0; c < 4; ++c) T[r * 4 + c] = P.at<float>(r, c);
+    } else {
+      for (int i = 0; i < 16; ++i) T[i] = pose_[i];
+    }
+    Integrate(imRGB.data, reinterpret_cast<const float*>(imD.data), T, 1.0f);
+  }
+#endif
+
+  /// Headless replacement of SaveMesh (src/TSDFfusion.py.in:48-53; viewers and skimage are
+  /// unavailable on this box): surface voxels as xyz (+rgb) — returns the point count.
+  int64_t GetPointCloud(std::vector<float>& xyz, std::vector<uint8_t>& rgb, float tsdf_thresh = 1.2f,
+                        float weight_thresh = 0.9f, int predicate = TSDF_PRED_NONZERO) {
+    int64_t n = 0;
+    check(tsdf_extract_points(vol_, predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, nullptr, 0, &n), "count");
+    xyz.resize((size_t)n * 3);
+    rgb.resize((size_t)n * 3);
+    if (n) check(tsdf_extract_points(vol_, predicate, tsdf_thresh, weight_thresh, xyz.data(), rgb.data(), nullptr, n, &n), "extract");
+    return n;
+  }
+  void SavePointCloud(const std::string& file_name, float tsdf_thresh = 1.2f, float weight_thresh = 0.9f) {
+    check(tsdf_save_ply(vol_, file_name.c_str(), TSDF_PRED_NONZERO, tsdf_thresh, weight_thresh), "tsdf_save_ply");
+  }
+  /// get_volume(): tsdf and colour arrays in numpy C order of [Dx,Dy,Dz].
+  void GetVolume(std::vector<float>& tsdf, std::vector<float>& color) {
+    size_t n = (size_t)cfg_.dim_x * cfg_.dim_y * cfg_.dim_z;
+    tsdf.resize(n);
+    color.resize(n);
+    check(tsdf_download(vol_, tsdf.data(), nullptr, color.data(), 0), "tsdf_download");
+  }
+  const tsdf_config& config() const { return cfg_; }
+  tsdf_vol* handle() { return vol_; }
+
+ private:
+  static std::vector<double> default_bounds() { return {0, 10, 0, 10, 0, 10}; }
+  static void check(int rc, const char* what) {
+    // the reference throws std::runtime_error on import/lookup failure (src/TSDFfusion.cpp:62-68,79-85)
+    if (rc != TSDF_OK) throw std::runtime_error(std::string("TSDFfusion: ") + what + ": " + tsdf_last_error());
+  }
+  tsdf_vol* vol_;
+  tsdf_config cfg_;
+  float pose_[16];
+  float K_[9];
+};
+
+#endif  // TSDF_B200_TSDFFUSION_HPP
