@@ -87,6 +87,17 @@ class ClockSampler(threading.Thread):
                 "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
+def measured_traffic(world):
+    """dram bytes per launch of the integrate kernel from the committed ncu capture (only valid
+    for the 1-GPU C4 workload it was taken on)."""
+    if world != 1 or DIM != 1024:
+        return None
+    try:
+        return int(json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_integrate"]["dram_bytes_per_launch"])
+    except Exception:
+        return None
+
+
 def visible_index(local_rank):
     cvd = os.environ.get("CUDA_VISIBLE_DEVICES")
     if cvd:
@@ -368,9 +379,9 @@ def run_b200(args, rank, world, local_rank):
                         "includes": "pinned-host frame H2D (+NCCL broadcast) + prep + integrate per step, "
                                     "8 B N_written readback per step, one extraction pass at the end",
                         "extracted_points": n_pts},
-                "gpu_launches": int(args.steps * 2),
+                "gpu_launches": int(args.steps * 3),  # k_frame_prep + k_integrate + k_publish per step
                 "roofline": {"bound": "hbm", "kernel": "k_integrate<ZFAST,COLOR,NF=1,VEC=4>", "achieved": achieved,
-                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                             "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(world),
                              "peak_source": peak_src, "kernel_ms": k_ms, "launches_timed": kn,
                              "algorithmic_bytes_per_launch": alg_bytes,
                              "note": "24 B x N_written + 8 B x H*W per launch on rank 0's slab"}}

@@ -10,7 +10,8 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtsdf_b200.so")
+# TSDF_B200_LIB: A/B tooling only (tools/variants.py against an older build of the same ABI)
+LIB_PATH = os.environ.get("TSDF_B200_LIB") or os.path.join(HERE, "libtsdf_b200.so")
 
 OK, E_INVALID, E_CUDA, E_NOMEM, E_CAPACITY, E_IO, E_NCCL, E_SINGULAR, E_NODEVICE = range(9)
 SEM_TSDFCU, SEM_FUSIONPY = 0, 1

@@ -200,7 +200,9 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaMalloc(&v->d_weight, bytes));
   if (c.with_color) CU_CHECK(cudaMalloc(&v->d_color, bytes));
   CU_CHECK(cudaMalloc(&v->d_written, sizeof(unsigned long long)));
-  CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocDefault));
+  CU_CHECK(cudaMemset(v->d_written, 0, sizeof(unsigned long long)));
+  CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
+  CU_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&v->hd_written), v->h_written, 0));
   *v->h_written = 0;
   CU_CHECK(cudaStreamCreateWithFlags(&v->s_compute, cudaStreamNonBlocking));
   CU_CHECK(cudaStreamCreateWithFlags(&v->s_copy, cudaStreamNonBlocking));
@@ -259,7 +261,7 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   const size_t px = frame_pixels(v->cfg);
   if (!s.d_raw) {
     CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
-    CU_CHECK(cudaMalloc(&s.d_frame, px * 16));          // float4 per pixel (float when no colour)
+    CU_CHECK(cudaMalloc(&s.d_frame, frame_alloc_bytes(px)));  // float4 per pixel (float when no colour) + tail
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
   }
@@ -337,6 +339,7 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
   out->obs_weight = obs_weight;
   out->pad_ = 0;
   out->img = d_frame;
+  out->dmax = frame_dmax_ptr(d_frame, frame_pixels(v->cfg));
   return TSDF_OK;
 }
 
@@ -353,7 +356,6 @@ bool account_weights(tsdf_vol* v, const FrameP* fp, int nf) {
 // Launches the integrate kernel for nf prepared frames and records stats/events.
 static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
-  CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
   cudaEvent_t k0 = v->ev_k0, k1 = v->ev_k1;
   if (v->ktiming) {  // a private event pair per launch
     if (v->kev_used + 2 > v->kev.size()) {
@@ -372,8 +374,8 @@ static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(k1, v->s_compute));
-  CU_CHECK(cudaMemcpyAsync(v->h_written, v->d_written, sizeof(unsigned long long),
-                           cudaMemcpyDeviceToHost, v->s_compute));
+  rc = launch_publish(v, false, v->s_compute);
+  if (rc) return rc;
   for (int i = 0; i < nf; ++i) {
     CU_CHECK(cudaEventRecord(slots[i]->consumed, v->s_compute));
     slots[i]->in_flight = true;
@@ -489,7 +491,6 @@ extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
   DeviceGuard g(v->cfg.device);
   int rc = tsdf_sync(v);
   if (rc) return rc;
-  CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long), v->s_compute));
   CU_CHECK(cudaEventRecord(v->ev_k0, v->s_compute));
   for (int i = 0; i < iters; ++i) {
     v->wmode_ok = account_weights(v, v->last_frames, v->last_nf);
@@ -497,14 +498,15 @@ extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
     if (rc) return rc;
   }
   CU_CHECK(cudaEventRecord(v->ev_k1, v->s_compute));
-  CU_CHECK(cudaMemcpyAsync(v->h_written, v->d_written, sizeof(unsigned long long),
-                           cudaMemcpyDeviceToHost, v->s_compute));
+  rc = launch_publish(v, false, v->s_compute);
+  if (rc) return rc;
   CU_CHECK(cudaStreamSynchronize(v->s_compute));
   float ms = 0;
   CU_CHECK(cudaEventElapsedTime(&ms, v->ev_k0, v->ev_k1));
   *avg_ms = ms / iters;
   v->frames += (int64_t)iters * v->last_nf;
-  v->last_written = (int64_t)(*v->h_written / (unsigned long long)iters);
+  *v->h_written /= (unsigned long long)iters;  // per-launch average (tsdf_sync re-reads the mirror)
+  v->last_written = (int64_t)*v->h_written;
   return TSDF_OK;
 }
 

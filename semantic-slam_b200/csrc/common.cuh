@@ -49,6 +49,7 @@ struct FrameP {       // one camera frame
   float obs_weight;
   int pad_;
   const void* img;    // prepared frame: float depth[H*W]  or  float4 {depth, c0, c1, c2}[H*W]
+  const float* dmax;  // largest depth of the prepared frame (+inf when it holds a NaN)
 };
 
 struct GridP {        // one volume slab
@@ -56,6 +57,7 @@ struct GridP {        // one volume slab
   int n_mid;          // = dim_y
   int n_slow;         // slow axis count of the slab
   int z0;             // global z of local slice 0
+  int nx_, nz_;       // dim_x and local slices (host-side use)
   float ox, oy, oz;   // origin (base frame)
   float vs, trunc;
   float inv_trunc;    // RN(1/trunc), host IEEE division
@@ -98,7 +100,8 @@ struct tsdf_vol {
   float* d_weight = nullptr;
   float* d_color = nullptr;
   unsigned long long* d_written = nullptr;
-  unsigned long long* h_written = nullptr;  // pinned mirror
+  unsigned long long* h_written = nullptr;  // pinned mirror (mapped: the kernel writes it)
+  unsigned long long* hd_written = nullptr; // its device address
   cudaStream_t s_compute = nullptr;
   cudaStream_t s_copy = nullptr;
   cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_u0 = nullptr, ev_u1 = nullptr;
@@ -130,10 +133,18 @@ struct tsdf_vol {
 };
 
 inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
+// A prepared frame is px*16 bytes of pixels followed by a 64-byte tail whose first word is the
+// frame's largest depth (written by k_frame_prep).
+constexpr size_t kFrameTailBytes = 64;
+inline size_t frame_alloc_bytes(size_t px) { return px * 16 + kFrameTailBytes; }
+inline float* frame_dmax_ptr(const void* d_frame, size_t px) {
+  return reinterpret_cast<float*>(reinterpret_cast<char*>(const_cast<void*>(d_frame)) + px * 16);
+}
 
 // ---- launchers implemented in the .cu files -----------------------------------------------
 // integrate.cu
 int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st);
+int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st);  // N_written -> pinned mirror, counter = 0
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st);
 void fill_grid_params(const tsdf_vol* v, bool color, GridP* g);

@@ -19,25 +19,38 @@ namespace {
 __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scale, int sub_c,
                              int sub_r, const uint8_t* __restrict__ rgb,
                              const uint8_t* __restrict__ mask, int H, int W, float max_depth,
-                             bool with_color, void* __restrict__ out) {
+                             bool with_color, void* __restrict__ out, int* __restrict__ dmax_bits) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= H * W) return;
-  float d;
-  if (fmt == TSDF_DEPTH_U16) d = (float)reinterpret_cast<const uint16_t*>(depth)[i] * scale;
-  else                       d = reinterpret_cast<const float*>(depth)[i] * scale;
-  if (sub_c > 1 || sub_r > 1) {  // examples/label_instance_rgbd.cpp:89-97
-    int r = i / W, c = i - r * W;
-    if ((c % sub_c) != 0 || (r % sub_r) != 0) d = 0.0f;
+  float d = 0.0f;
+  if (i < H * W) {
+    if (fmt == TSDF_DEPTH_U16) d = (float)reinterpret_cast<const uint16_t*>(depth)[i] * scale;
+    else                       d = reinterpret_cast<const float*>(depth)[i] * scale;
+    if (sub_c > 1 || sub_r > 1) {  // examples/label_instance_rgbd.cpp:89-97
+      int r = i / W, c = i - r * W;
+      if ((c % sub_c) != 0 || (r % sub_r) != 0) d = 0.0f;
+    }
+    if (mask) d = d * (mask[i] >= 128 ? 1.0f : 0.0f);
+    if (d <= 0.0f || d > max_depth) d = 0.0f;
+    if (with_color) {
+      // channels of the folded colour floor(c2*65536 + c1*256 + c0) as exact floats
+      float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
+      if (rgb) { c0 = (float)rgb[3 * i + 0]; c1 = (float)rgb[3 * i + 1]; c2 = (float)rgb[3 * i + 2]; }
+      reinterpret_cast<float4*>(out)[i] = make_float4(d, c0, c1, c2);
+    } else {
+      reinterpret_cast<float*>(out)[i] = d;
+    }
   }
-  if (mask) d = d * (mask[i] >= 128 ? 1.0f : 0.0f);
-  if (d <= 0.0f || d > max_depth) d = 0.0f;
-  if (with_color) {
-    // channels of the folded colour floor(c2*65536 + c1*256 + c0) as exact floats
-    float c0 = 0.0f, c1 = 0.0f, c2 = 0.0f;
-    if (rgb) { c0 = (float)rgb[3 * i + 0]; c1 = (float)rgb[3 * i + 1]; c2 = (float)rgb[3 * i + 2]; }
-    reinterpret_cast<float4*>(out)[i] = make_float4(d, c0, c1, c2);
-  } else {
-    reinterpret_cast<float*>(out)[i] = d;
+  // Largest depth of the prepared frame, for the integrate kernel's conservative "beyond every
+  // surface" cull.  Stored depths are >= +0 or NaN; a NaN (which the reference integrates)
+  // counts as +inf so that it disables the cull.  Non-negative floats order like their bits.
+  int b = (d != d) ? 0x7f800000 : __float_as_int(d);
+  b = __reduce_max_sync(0xffffffffu, b);
+  __shared__ int wmax[8];
+  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = b;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int k = 1; k < 8; ++k) b = max(b, wmax[k]);
+    if (b > 0) atomicMax(dmax_bits, b);
   }
 }
 
@@ -93,8 +106,10 @@ int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int
                       const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
                       bool with_color, void* d_frame, cudaStream_t st) {
   int n = H * W;
+  int* d_dmax = reinterpret_cast<int*>(frame_dmax_ptr(d_frame, (size_t)n));
+  CU_CHECK(cudaMemsetAsync(d_dmax, 0, sizeof(int), st));
   k_frame_prep<<<(n + 255) / 256, 256, 0, st>>>(d_depth, depth_fmt, depth_scale, sub_c, sub_r, d_rgb,
-                                                d_mask, H, W, max_depth, with_color, d_frame);
+                                                d_mask, H, W, max_depth, with_color, d_frame, d_dmax);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }

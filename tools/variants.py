@@ -1,24 +1,49 @@
-"""A/B timing of kernel variants on the S-full workload (evidence for DESIGN.md choices).
-usage: python tools/variants.py [dim] [variant ...]   (variant bits: 1 literal math, 2/4 prefetch L2/L1,
-8/16 rows-per-block x64/x32)"""
+"""A/B timing of kernel variants (evidence for DESIGN.md choices).
+usage: python tools/variants.py <scene> <dim> [variant ...]
+  scene: full  = S-full (every voxel written; the roofline workload)
+         real  = S-real with fr3_office keyframe poses (C2-like, ~7 % coverage)
+         kitti = S-kitti 1241x376 into (dim, dim/4, dim) at 102.4 m / dim voxels (C3-like)
+  variant bits: 1 literal math, 2/4 prefetch L2/L1, 8/16 rows-per-block x64/x32, 32 prefetch off,
+                64 segment cull off, 128 cull + staged probe
+Variants are timed round-robin (R rounds of 5 launches each per frame) so that clock / power
+drift hits all of them alike; the report is the median and the minimum over rounds."""
 import importlib, sys, os, json
+import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pkg = importlib.import_module("semantic-slam_b200")
-dim = int(sys.argv[1]) if len(sys.argv) > 1 else 1024
-variants = [int(v) for v in sys.argv[2:]] or [0, 2, 4]
-vs = 2.048 / dim
-origin, frames = pkg.synth.s_full((dim,) * 3, vs, n_frames=2)
-cfg = pkg.make_config((dim,) * 3, vs, origin)
-out = {}
+synth = pkg.synth
+scene = sys.argv[1] if len(sys.argv) > 1 else "full"
+dim = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
+variants = [int(v) for v in sys.argv[3:]] or [0, 64]
+R = int(os.environ.get("AB_ROUNDS", "7"))
+kw = {}
+if scene == "full":
+    dims, vs = (dim,) * 3, 2.048 / dim
+    origin, frames = synth.s_full(dims, vs, n_frames=2)
+elif scene == "real":
+    dims, vs = (dim,) * 3, 5.12 / dim
+    origin, frames = synth.s_real(dims, vs, n_frames=4, poses=synth.load_pose_fixture()[::48])
+else:
+    dims, vs = (dim, dim // 4, dim), 102.4 / dim
+    origin, frames = synth.s_kitti(n_frames=4, voxel_size=vs, dims=dims)
+    kw = dict(K=synth.KITTI_K, im_hw=synth.KITTI_HW, max_depth=50.0)
+cfg = pkg.make_config(dims, vs, origin, **kw)
+times = {v: [] for v in variants}
+cover = 0.0
 with pkg.Volume(cfg) as vol:
-    for var in variants:
-        vol.reset()
-        vol.set_variant(var)
-        d, c, T = frames[0]
-        vol.integrate(d, c, T)
-        vol.bench_kernel(3)
-        ms = min(vol.bench_kernel(10) for _ in range(3))
-        gb = (24 * vol.n_local + 16 * d.size) / 1e9
-        out[var] = {"ms": round(ms, 4), "GBps": round(gb / ms * 1e3, 1), "written": vol.stats().voxels_written}
-        print(var, out[var], flush=True)
-print(json.dumps(out))
+    for rnd in range(R + 1):               # round 0 = warm-up, dropped
+        for var in variants:
+            tot = 0.0
+            for d, c, T in frames:
+                vol.set_variant(var)
+                vol.integrate(d, c, T)      # uploads this frame; bench_kernel re-launches on it
+                tot += vol.bench_kernel(5)
+                cover = vol.stats().voxels_written / vol.n_local
+            if rnd:
+                times[var].append(tot / len(frames))
+out = {}
+for var in variants:
+    t = np.array(times[var])
+    out[var] = {"median_ms": round(float(np.median(t)), 4), "min_ms": round(float(t.min()), 4),
+                "Gvox_visited_per_s": round(vol.n_local / float(np.median(t)) / 1e6, 1)}
+print(json.dumps({"scene": scene, "dim": dim, "coverage_last": round(cover, 4), "rounds": R, "variants": out}))
