@@ -204,8 +204,14 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
   CU_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&v->hd_written), v->h_written, 0));
   *v->h_written = 0;
-  CU_CHECK(cudaStreamCreateWithFlags(&v->s_compute, cudaStreamNonBlocking));
-  CU_CHECK(cudaStreamCreateWithFlags(&v->s_copy, cudaStreamNonBlocking));
+  // The copy stream (H2D, NCCL broadcast, frame prep) gets the highest priority: its few small
+  // CTAs must be dispatched ahead of the tens of thousands of integrate blocks still queued on
+  // the compute stream, otherwise frame i+1 only arrives in the tail of integrate i and every
+  // step pays the broadcast latency.
+  int prio_least = 0, prio_greatest = 0;
+  CU_CHECK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+  CU_CHECK(cudaStreamCreateWithPriority(&v->s_compute, cudaStreamNonBlocking, prio_least));
+  CU_CHECK(cudaStreamCreateWithPriority(&v->s_copy, cudaStreamNonBlocking, prio_greatest));
   CU_CHECK(cudaEventCreate(&v->ev_k0));
   CU_CHECK(cudaEventCreate(&v->ev_k1));
   CU_CHECK(cudaEventCreate(&v->ev_u0));

@@ -14,6 +14,8 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <stdlib.h>
+
 #include <algorithm>
 #include <vector>
 
@@ -25,6 +27,7 @@ struct NcclApi {
   void* h = nullptr;
   ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+  ncclResult_t (*CommInitRankConfig)(ncclComm_t*, int, ncclUniqueId, int, ncclConfig_t*) = nullptr;  // optional
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
@@ -54,6 +57,7 @@ int load_nccl() {
   if (!g_nccl.field) { tsdf_set_error("NCCL symbol %s missing", sym); return TSDF_E_NCCL; }
   BIND(GetUniqueId, "ncclGetUniqueId");
   BIND(CommInitRank, "ncclCommInitRank");
+  g_nccl.CommInitRankConfig = reinterpret_cast<decltype(g_nccl.CommInitRankConfig)>(dlsym(h, "ncclCommInitRankConfig"));
   BIND(CommDestroy, "ncclCommDestroy");
   BIND(Broadcast, "ncclBroadcast");
   BIND(AllGather, "ncclAllGather");
@@ -111,7 +115,20 @@ extern "C" int tsdf_comm_create(const void* uid128, int nranks, int rank, int de
   c->nranks = nranks; c->rank = rank; c->device = device;
   ncclUniqueId id;
   memcpy(&id, uid128, 128);
-  ncclResult_t r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+  // The per-frame payload is ~2 MB: a couple of channels saturate nothing but are plenty, while
+  // every extra NCCL CTA spins on an SM the integrate kernel wants (measured: kernel time under
+  // the overlapped broadcast).  TSDF_B200_NCCL_MAX_CTAS overrides (0 = NCCL's default).
+  int max_ctas = 4;
+  if (const char* e = getenv("TSDF_B200_NCCL_MAX_CTAS")) max_ctas = atoi(e);
+  ncclResult_t r;
+  if (g_nccl.CommInitRankConfig && max_ctas > 0) {
+    ncclConfig_t cfg = NCCL_CONFIG_INITIALIZER;
+    cfg.minCTAs = 1;
+    cfg.maxCTAs = max_ctas;
+    r = g_nccl.CommInitRankConfig(&c->comm, nranks, id, rank, &cfg);
+  } else {
+    r = g_nccl.CommInitRank(&c->comm, nranks, id, rank);
+  }
   if (r != ncclSuccess) {
     tsdf_set_error("ncclCommInitRank: %s", g_nccl.GetErrorString(r));
     delete c;

@@ -635,9 +635,10 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   const bool vec4 = (g.n_fast % 4) == 0;
   const bool literal = (v->variant & 1) != 0;
   // A/B knobs (tsdf_set_variant): bit0 literal math; bits1-2 prefetch 1=L2 2=L1 (default L2);
-  // bit5 prefetch off; bits3-4 rows per block x64 / x32 (default x16); bit6/bit7 segment cull off/on
+  // bit5 prefetch off; bits3-4 rows per block x64 / x32 (default x16); bit6/bit7 segment cull off/on;
+  // bits8-9 rows per block x8 / x4
   g_prefetch_mode = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
-  g_rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : 16);
+  g_rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
   // projects inside every frame's image (then no segment can be culled by the frustum and the
   // plain kernel is ~2-5 % faster); a pure performance choice, results are identical

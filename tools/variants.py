@@ -1,9 +1,10 @@
 """A/B timing of kernel variants (evidence for DESIGN.md choices).
 usage: python tools/variants.py <scene> <dim> [variant ...]
-  scene: full  = S-full (every voxel written; the roofline workload)
+  scene: slab  = z-slab [dim/2, dim/2+dim/8) of S-full (one rank of 8)
+         full  = S-full (every voxel written; the roofline workload)
          real  = S-real with fr3_office keyframe poses (C2-like, ~7 % coverage)
          kitti = S-kitti 1241x376 into (dim, dim/4, dim) at 102.4 m / dim voxels (C3-like)
-  variant bits: 1 literal math, 2/4 prefetch L2/L1, 8/16 rows-per-block x64/x32, 32 prefetch off,
+  variant bits: 1 literal math, 2/4 prefetch L2/L1, 8/16/256/512 rows-per-block x64/x32/x8/x4, 32 prefetch off,
                 64 segment cull off, 128 cull + staged probe
 Variants are timed round-robin (R rounds of 5 launches each per frame) so that clock / power
 drift hits all of them alike; the report is the median and the minimum over rounds."""
@@ -17,7 +18,11 @@ dim = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
 variants = [int(v) for v in sys.argv[3:]] or [0, 64]
 R = int(os.environ.get("AB_ROUNDS", "7"))
 kw = {}
-if scene == "full":
+if scene == "slab":      # one of 8 z-slabs of the S-full grid (what each rank of an 8-GPU run integrates)
+    dims, vs = (dim,) * 3, 2.048 / dim
+    origin, frames = synth.s_full(dims, vs, n_frames=2)
+    kw = dict(z_range=(dim // 2, dim // 2 + dim // 8))
+elif scene == "full":
     dims, vs = (dim,) * 3, 2.048 / dim
     origin, frames = synth.s_full(dims, vs, n_frames=2)
 elif scene == "real":
