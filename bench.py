@@ -419,18 +419,19 @@ def extras(pkg, line, frames, origin):
             ms = v2.timer_stop()
             ksum, kn = v2.kernel_timing_read()
             wr = v2.stats().voxels_written
-            v2.extract_count(pkg.PRED_ABS_LT, 0.5, 1.5)   # warm (scratch alloc + kernel load)
+            v2.extract_count(pkg.PRED_ABS_LT, 0.5, 1.25)  # warm (scratch alloc + kernel load); other
+            # thresholds, so the timed call below is a full mark + scan pass, not the cached one
             t0 = time.perf_counter()
             npts = v2.extract_count(pkg.PRED_ABS_LT, 0.5, 1.5)
             ext_ms = (time.perf_counter() - t0) * 1e3
             t0 = time.perf_counter()
-            pts = v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5)
+            pts = v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5)   # reuses the mark pass above: emit + D2H only
             ext_full_ms = (time.perf_counter() - t0) * 1e3
         line["extra_c2"] = {"workload": "C2: 300 frames (12 distinct, fr3_office keyframe poses) into 512^3 @ 1 cm, "
                                         "scene S-real, pageable host frames through tsdf_integrate_async",
                             "value": nfr * 512 ** 3 / (ms * 1e-3) / 1e9, "unit": UNIT, "frames_per_sec": nfr / (ms * 1e-3),
                             "kernel_ms": ksum / max(kn, 1), "coverage_last_frame": wr / 512 ** 3,
-                            "extract_count_ms": ext_ms, "extract_points_to_host_ms": ext_full_ms,
+                            "extract_count_ms": ext_ms, "extract_emit_to_host_ms": ext_full_ms,
                             "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts}
     except Exception as e:
         line["extra_c2"] = {"error": str(e)}

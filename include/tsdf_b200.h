@@ -70,8 +70,11 @@ enum { TSDF_SEM_TSDFCU = 0, TSDF_SEM_FUSIONPY = 1 };
  *                     (Zeng's original, src/obselete/tsdf.cpp:16,33)       */
 enum { TSDF_PRED_NONZERO = 0, TSDF_PRED_ABS_LT = 1 };
 
-/* Raw depth sample formats accepted by tsdf_integrate_raw. */
-enum { TSDF_DEPTH_F32 = 0, TSDF_DEPTH_U16 = 1 };
+/* Raw depth sample formats accepted by tsdf_integrate_raw.
+ * The RANGE formats are lidar images whose pixels hold the distance along the ray; the depth is
+ * d = range*scale / sqrt(x*x + y*y + 1), x = (col-cx)/fx, y = (row-cy)/fy
+ * (src/DoN.cpp:86-100 and src/Object.cpp:611-619, mSensor == 1), computed on the device. */
+enum { TSDF_DEPTH_F32 = 0, TSDF_DEPTH_U16 = 1, TSDF_DEPTH_RANGE_F32 = 2, TSDF_DEPTH_RANGE_U16 = 3 };
 
 typedef struct tsdf_vol tsdf_vol;     /* one volume (or one z-slab of it) on one GPU */
 typedef struct tsdf_comm tsdf_comm;   /* one NCCL rank                              */
@@ -243,6 +246,15 @@ int tsdf_memcpy_d2h(int device, void* dst, const void* src, size_t bytes);
 /* ---- host-side helpers restated from the reference (K6) -------------------- */
 void tsdf_multiply_matrix(const float m1[16], const float m2[16], float out[16]); /* src/tsdf.cu:253-273 */
 int tsdf_invert_matrix(const float m[16], float out[16]); /* src/tsdf.cu:276-403; TSDF_E_SINGULAR */
+
+/* Pose ingest for the off-line replay: reads the keyframe poses of a saved run
+ * from `bundle.txt` — header "<n_cams> <n_pts>", then per camera one intrinsics line, three
+ * rows of Rcw and one row of tcw (written by src/ORB_SLAM2/System.cc:884-917, parsed by
+ * examples/label_instance_rgbd.cpp:289-330) — and returns what Engine::Run feeds the TSDF:
+ * Twc = KF->GetPoseInverse() (src/Engine.cpp:222), i.e. [Rcw^T | -Rcw^T tcw], row-major 4x4,
+ * fp32.  Twc: cap*16 floats or NULL; *n_cams receives the camera count of the file (call with
+ * cap = 0 to size).  TSDF_E_IO on open/parse failure, TSDF_E_CAPACITY if cap is too small.  */
+int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int* n_cams);
 
 /* ---- measurement hooks (used by bench.py; no effect on results) ------------ */
 /* Times `iters` back-to-back launches of the integrate kernel on the frame

@@ -71,6 +71,8 @@ class Oracle:
         L.oracle_multiply_matrix.argtypes = [_f32p, _f32p, _f32p]
         L.oracle_pack_color.argtypes = [_u8p, C.c_int64, _f32p]
         L.oracle_instance_origin.argtypes = [_f32p, C.c_void_p, C.c_int, C.c_int, _f32p, _f32p]
+        L.oracle_range_to_depth.argtypes = [_f32p, C.c_int, C.c_int, _f32p, C.c_float, _f32p]
+        L.oracle_range_to_depth.restype = None
         L.oracle_save_bin.restype = C.c_int
         L.oracle_save_bin.argtypes = [C.c_char_p, C.POINTER(OracleParams), _f32p]
         L.oracle_save_ply.restype = C.c_int
@@ -155,6 +157,14 @@ class Oracle:
         self.lib.oracle_instance_origin(np.ascontiguousarray(depth, np.float32).reshape(-1), m, H, W,
                                         np.ascontiguousarray(K, np.float32).reshape(9), out)
         return out
+
+    def range_to_depth(self, rng, K, scale=1.0):
+        """Lidar range image -> camera-z depth (reference src/DoN.cpp:86-100, src/Object.cpp:611-619)."""
+        H, W = rng.shape
+        out = np.empty(H * W, np.float32)
+        self.lib.oracle_range_to_depth(np.ascontiguousarray(rng, np.float32).reshape(-1), H, W,
+                                       np.ascontiguousarray(K, np.float32).reshape(-1), np.float32(scale), out)
+        return out.reshape(H, W)
 
     def save_bin(self, path, p, tsdf):
         return bool(self.lib.oracle_save_bin(path.encode(), C.byref(p), tsdf))

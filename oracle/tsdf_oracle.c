@@ -288,6 +288,22 @@ void oracle_instance_origin(const float* depth, const uint8_t* mask, int H, int 
 }
 
 /* .bin writer — src/tsdf.cu:116-132: dims as floats, origin, voxel_size, trunc, tsdf. */
+/* Lidar frames store a RANGE (distance along the ray) per pixel; the reference turns it into a
+ * camera-z depth with  x = (col - cx)/fx, y = (row - cy)/fy, rim = sqrt(x*x + y*y + 1),
+ * d = range*scale/rim   (src/DoN.cpp:86-100, mSensor==1; src/Object.cpp:611-619 is the same
+ * with scale 1).  sqrt() of the float sum rounded to float == sqrtf (sqrt is correctly rounded
+ * and double rounding float<-double is innocuous for it).  range == 0 stays 0 (:87 skips it). */
+void oracle_range_to_depth(const float* range, int H, int W, const float* K, float scale, float* depth) {
+  const float fx = K[0], cx = K[2], fy = K[4], cy = K[5];
+  for (int r = 0; r < H; ++r)
+    for (int c = 0; c < W; ++c) {
+      const float x = ((float)c - cx) / fx;
+      const float y = ((float)r - cy) / fy;
+      const float rim = sqrtf(x * x + y * y + 1);
+      depth[(size_t)r * W + c] = range[(size_t)r * W + c] * scale / rim;
+    }
+}
+
 int oracle_save_bin(const char* path, const oracle_params* p, const float* tsdf) {
   FILE* f = fopen(path, "wb");
   if (!f) return 0;

@@ -16,7 +16,7 @@ LIB_PATH = os.environ.get("TSDF_B200_LIB") or os.path.join(HERE, "libtsdf_b200.s
 OK, E_INVALID, E_CUDA, E_NOMEM, E_CAPACITY, E_IO, E_NCCL, E_SINGULAR, E_NODEVICE = range(9)
 SEM_TSDFCU, SEM_FUSIONPY = 0, 1
 PRED_NONZERO, PRED_ABS_LT = 0, 1
-DEPTH_F32, DEPTH_U16 = 0, 1
+DEPTH_F32, DEPTH_U16, DEPTH_RANGE_F32, DEPTH_RANGE_U16 = 0, 1, 2, 3
 
 
 class Config(C.Structure):
@@ -93,6 +93,7 @@ SIGNATURES = {
     "tsdf_memcpy_d2h": (_I, [_I, _VP, _VP, C.c_size_t]),
     "tsdf_multiply_matrix": (None, [_VP, _VP, _VP]),
     "tsdf_invert_matrix": (_I, [_VP, _VP]),
+    "tsdf_read_bundle_poses": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
     "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
     "tsdf_set_variant": (_I, [_VP, _I]),
     "tsdf_timer_start": (_I, [_VP]),

@@ -238,6 +238,7 @@ extern "C" int tsdf_destroy(tsdf_vol* v) {
 }
 
 extern "C" int tsdf_reset(tsdf_vol* v) {
+  if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   REQUIRE(v, "null handle");
   DeviceGuard g(v->cfg.device);
   int rc = launch_fill(v->d_tsdf, 1.0f, v->n_local, v->s_compute);  // src/tsdf.cu:79-80
@@ -302,7 +303,8 @@ static int to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, s
 }
 
 int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
-                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot) {
+                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot,
+                const float* K) {
   FrameSlot& s = v->slot[slot_index];
   int rc = ensure_slot(v, s);
   if (rc) return rc;
@@ -311,7 +313,9 @@ int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, f
     s.in_flight = false;
   }
   const size_t px = frame_pixels(v->cfg);
-  const size_t dbytes = px * (depth_fmt == TSDF_DEPTH_U16 ? 2 : 4);
+  const size_t dbytes = px * ((depth_fmt == TSDF_DEPTH_U16 || depth_fmt == TSDF_DEPTH_RANGE_U16) ? 2 : 4);
+  const float* k = K ? K : v->cfg.K;
+  const float intr[4] = {k[0], k[2], k[4], k[5]};
   const void* d_depth = nullptr;
   const void* d_rgb = nullptr;
   rc = to_device(v, s, depth, dbytes, 0, &d_depth);
@@ -322,7 +326,7 @@ int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, f
   }
   rc = launch_frame_prep(d_depth, depth_fmt, depth_scale, sub_c, sub_r,
                          reinterpret_cast<const uint8_t*>(d_rgb), nullptr, v->cfg.im_h, v->cfg.im_w,
-                         v->cfg.max_depth, want_color, s.d_frame, v->s_copy);
+                         v->cfg.max_depth, want_color, intr, s.d_frame, v->s_copy);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(s.uploaded, v->s_copy));
   *out_slot = &s;
@@ -361,6 +365,7 @@ bool account_weights(tsdf_vol* v, const FrameP* fp, int nf) {
 
 // Launches the integrate kernel for nf prepared frames and records stats/events.
 static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
+  if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
   cudaEvent_t k0 = v->ev_k0, k1 = v->ev_k1;
   if (v->ktiming) {  // a private event pair per launch
@@ -398,14 +403,18 @@ extern "C" int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int dept
                                         float depth_scale, int sub_c, int sub_r, const uint8_t* rgb,
                                         const float* K, const float* T_wc, float obs_weight) {
   REQUIRE(v && depth && T_wc, "null argument");
-  REQUIRE(depth_fmt == TSDF_DEPTH_F32 || depth_fmt == TSDF_DEPTH_U16, "bad depth format");
+  REQUIRE(depth_fmt >= TSDF_DEPTH_F32 && depth_fmt <= TSDF_DEPTH_RANGE_U16, "bad depth format");
+  if (depth_fmt >= TSDF_DEPTH_RANGE_F32) {
+    const float* k = K ? K : v->cfg.K;
+    REQUIRE(k[0] != 0.0f && k[4] != 0.0f, "range formats need non-zero fx, fy");
+  }
   REQUIRE(obs_weight >= 1e-6f && obs_weight <= 1e6f, "obs_weight must be in [1e-6, 1e6]");
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   FrameSlot* s = nullptr;
   CU_CHECK(cudaEventRecord(v->ev_u0, v->s_copy));
   int rc = stage_frame(v, (int)(v->seq % 3), depth, depth_fmt, depth_scale, sub_c < 1 ? 1 : sub_c,
-                       sub_r < 1 ? 1 : sub_r, rgb, color, &s);
+                       sub_r < 1 ? 1 : sub_r, rgb, color, &s, K);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(v->ev_u1, v->s_copy));
   ++v->seq;
@@ -492,6 +501,7 @@ extern "C" int tsdf_set_variant(tsdf_vol* v, int variant) {
 }
 
 extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
+  if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   REQUIRE(v && avg_ms && iters > 0, "bad argument");
   REQUIRE(v->last_nf > 0, "no frame integrated yet");
   DeviceGuard g(v->cfg.device);
@@ -559,6 +569,7 @@ extern "C" int tsdf_download(tsdf_vol* v, float* tsdf, float* weight, float* col
 
 extern "C" int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, const float* color,
                            int global_layout) {
+  if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   REQUIRE(v, "null handle");
   DeviceGuard g(v->cfg.device);
   int rc = tsdf_sync(v);
@@ -666,6 +677,7 @@ extern "C" int tsdf_save_bin(tsdf_vol* v, const char* path) {
 }
 
 extern "C" int tsdf_load_bin(tsdf_vol* v, const char* path) {
+  if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   REQUIRE(v && path, "null argument");
   REQUIRE(v->dzl == v->cfg.dim_z, "tsdf_load_bin needs a whole-grid handle");
   FILE* fp = fopen(path, "rb");
@@ -788,7 +800,7 @@ int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const fl
   const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
   int rc = launch_frame_prep(s->d_raw, TSDF_DEPTH_F32, 1.0f, 1, 1,
                              color ? reinterpret_cast<const uint8_t*>(s->d_raw) + rgb_off : nullptr,
-                             nullptr, v->cfg.im_h, v->cfg.im_w, v->cfg.max_depth, color, s->d_frame,
+                             nullptr, v->cfg.im_h, v->cfg.im_w, v->cfg.max_depth, color, nullptr, s->d_frame,
                              v->s_copy);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(s->uploaded, v->s_copy));
@@ -796,6 +808,47 @@ int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const fl
   FrameP fp;
   make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
   return submit(v, &s, &fp, 1, color);
+}
+
+// ---- pose ingest ------------------------------------------------------------
+extern "C" int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int* n_cams) {
+  REQUIRE(path && n_cams, "null argument");
+  FILE* f = fopen(path, "r");
+  if (!f) { tsdf_set_error("tsdf_read_bundle_poses: cannot open %s", path); return TSDF_E_IO; }
+  auto fail = [&](const char* what) {
+    fclose(f);
+    tsdf_set_error("tsdf_read_bundle_poses: %s in %s", what, path);
+    return TSDF_E_IO;
+  };
+  char line[1024];
+  long m = 0, n = 0;
+  if (!fgets(line, sizeof line, f) || sscanf(line, "%ld %ld", &m, &n) < 1 || m < 0) return fail("bad header");
+  *n_cams = (int)m;
+  if (!Twc || cap == 0) { fclose(f); return TSDF_OK; }
+  if (cap < m) {
+    fclose(f);
+    tsdf_set_error("tsdf_read_bundle_poses: capacity %d < %ld cameras", cap, m);
+    return TSDF_E_CAPACITY;
+  }
+  for (long i = 0; i < m; ++i) {
+    float R[9], t[3];
+    if (!fgets(line, sizeof line, f)) return fail("truncated file");          // intrinsics line
+    for (int j = 0; j < 3; ++j)                                                 // rows of Rcw
+      if (!fgets(line, sizeof line, f) || sscanf(line, "%f %f %f", &R[3 * j], &R[3 * j + 1], &R[3 * j + 2]) != 3)
+        return fail("bad rotation row");
+    if (!fgets(line, sizeof line, f) || sscanf(line, "%f %f %f", &t[0], &t[1], &t[2]) != 3)
+      return fail("bad translation row");
+    float* T = Twc + 16 * i;
+    // Rwc = Rcw^T, Ow = -Rwc*tcw (ORB-SLAM2 KeyFrame::SetPose), fp32, left to right
+    for (int r = 0; r < 3; ++r) {
+      for (int c = 0; c < 3; ++c) T[4 * r + c] = R[3 * c + r];
+      T[4 * r + 3] = -((R[0 + r] * t[0] + R[3 + r] * t[1]) + R[6 + r] * t[2]);
+    }
+    T[12] = T[13] = T[14] = 0.0f;
+    T[15] = 1.0f;
+  }
+  fclose(f);
+  return TSDF_OK;
 }
 
 // ---- measurement hooks ---------------------------------------------------------------------------

@@ -126,6 +126,7 @@ extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, con
   for (int i = 0; i < n_active; ++i) {
     REQUIRE(active[i] >= 0 && active[i] < b->n, "instance id out of range");
     tsdf_vol* v = b->vols[active[i]];
+    ++v->epoch;
     const tsdf_config& c = v->cfg;
     BatchDesc& d = b->h_descs[i];
     (void)c;

@@ -130,6 +130,14 @@ struct tsdf_vol {
   // extraction scratch
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
+  // every operation that can change the voxel arrays bumps `epoch`; the mark pass of the last
+  // extraction is reused while epoch and predicate are unchanged
+  uint64_t epoch = 0;
+  bool mark_valid = false;
+  uint64_t mark_epoch = 0;
+  int mark_pred = 0;
+  float mark_tt = 0, mark_wt = 0;
+  int64_t mark_total = 0;
 };
 
 inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
@@ -152,7 +160,8 @@ bool account_weights(tsdf_vol* v, const FrameP* fp, int nf);  // updates intw/w_
 // frame.cu
 int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
                       const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
-                      bool with_color, void* d_frame, cudaStream_t st);
+                      bool with_color, const float intr[4] /* fx,cx,fy,cy: RANGE formats only */,
+                      void* d_frame, cudaStream_t st);
 int launch_fill(float* p, float val, int64_t n, cudaStream_t st);
 int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, int W, float fx,
                            float cx, float fy, float cy, float* d_out3, cudaStream_t st);
@@ -166,4 +175,5 @@ int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);
 int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
                       const void* d_frame, FrameP* out);
 int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
-                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot);
+                int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot,
+                const float* K = nullptr);

@@ -70,27 +70,51 @@ k_mark(const float* __restrict__ tsdf, const float* __restrict__ weight, int64_t
   }
 }
 
-// Exclusive scan of m uint32 counts into int64 offsets; offsets[m] = total.  One block.
+// Exclusive scan of m uint32 counts into int64 offsets; offsets[m] = total.  One block of
+// 1024 threads walks the array in coalesced 4096-entry tiles (uint4 per thread), scans each
+// tile with warp shuffles and carries the running total (<= 131072 entries at 1024^3).
 __global__ void __launch_bounds__(1024)
 k_scan(const uint32_t* __restrict__ cnt, int64_t m, int64_t* __restrict__ off) {
-  __shared__ int64_t s_part[1024];
-  const int tid = threadIdx.x;
-  const int64_t per = (m + 1023) / 1024;
-  const int64_t lo = tid * per, hi = lo + per < m ? lo + per : m;
-  int64_t s = 0;
-  for (int64_t i = lo; i < hi; ++i) s += cnt[i];
-  s_part[tid] = s;
+  __shared__ int64_t s_warp[32];
+  __shared__ int64_t s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_carry = 0;
   __syncthreads();
-  // Hillis-Steele inclusive scan over 1024 partials
-  for (int o = 1; o < 1024; o <<= 1) {
-    int64_t v = tid >= o ? s_part[tid - o] : 0;
+  for (int64_t base = 0; base < m; base += 4096) {
+    const int64_t i0 = base + 4 * tid;
+    uint32_t c[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) c[j] = (i0 + j < m) ? cnt[i0 + j] : 0u;
+    const int64_t mine = (int64_t)c[0] + c[1] + c[2] + c[3];
+    int64_t incl = mine;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int64_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
-    s_part[tid] += v;
+    if (warp == 0) {
+      int64_t w = s_warp[lane], wi = w;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int64_t v = __shfl_up_sync(0xffffffffu, wi, o);
+        if (lane >= o) wi += v;
+      }
+      s_warp[lane] = wi - w;  // exclusive prefix of the warp totals
+    }
+    __syncthreads();
+    int64_t run = s_carry + s_warp[warp] + incl - mine;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (i0 + j < m) off[i0 + j] = run;
+      run += c[j];
+    }
+    __syncthreads();                      // everyone has read s_carry / s_warp
+    if (tid == 1023) s_carry = run;       // inclusive total so far
     __syncthreads();
   }
-  int64_t run = s_part[tid] - s;  // exclusive prefix of this thread's range
-  for (int64_t i = lo; i < hi; ++i) { off[i] = run; run += cnt[i]; }
-  if (tid == 1023) off[m] = s_part[1023];
+  if (tid == 0) off[m] = s_carry;
 }
 
 struct EmitP {
@@ -172,6 +196,7 @@ int ensure_scratch(tsdf_vol* v, size_t bytes) {
   if (v->scratch_bytes >= bytes) return TSDF_OK;
   if (v->d_scratch) cudaFree(v->d_scratch);
   v->d_scratch = nullptr;
+  v->mark_valid = false;
   v->scratch_bytes = 0;
   CU_CHECK(cudaMalloc(&v->d_scratch, bytes));
   v->scratch_bytes = bytes;
@@ -194,14 +219,23 @@ int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_t
   uint32_t* d_cnt = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(v->d_scratch) + off_bytes);
   uint32_t* d_bal = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(v->d_scratch) + off_bytes + cnt_bytes);
   cudaStream_t st = v->s_compute;
-  k_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(v->d_tsdf, v->d_weight, n, predicate, tsdf_thresh,
-                                                 weight_thresh, d_bal, d_cnt);
-  CU_CHECK(cudaGetLastError());
-  k_scan<<<1, 1024, 0, st>>>(d_cnt, n_tiles, d_off);
-  CU_CHECK(cudaGetLastError());
-  int64_t total = 0;
-  CU_CHECK(cudaMemcpyAsync(&total, d_off + n_tiles, 8, cudaMemcpyDeviceToHost, st));
-  CU_CHECK(cudaStreamSynchronize(st));
+  // The usual pattern is a sizing call followed by the real one: the ballots and offsets of the
+  // first are still valid for the second when nothing has touched the volume in between.
+  const bool cached = v->mark_valid && v->mark_epoch == v->epoch && v->mark_pred == predicate &&
+                      v->mark_tt == tsdf_thresh && v->mark_wt == weight_thresh;
+  int64_t total = v->mark_total;
+  if (!cached) {
+    v->mark_valid = false;
+    k_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(v->d_tsdf, v->d_weight, n, predicate, tsdf_thresh,
+                                                   weight_thresh, d_bal, d_cnt);
+    CU_CHECK(cudaGetLastError());
+    k_scan<<<1, 1024, 0, st>>>(d_cnt, n_tiles, d_off);
+    CU_CHECK(cudaGetLastError());
+    CU_CHECK(cudaMemcpyAsync(&total, d_off + n_tiles, 8, cudaMemcpyDeviceToHost, st));
+    CU_CHECK(cudaStreamSynchronize(st));
+    v->mark_valid = true; v->mark_epoch = v->epoch; v->mark_pred = predicate;
+    v->mark_tt = tsdf_thresh; v->mark_wt = weight_thresh; v->mark_total = total;
+  }
   if (count) *count = total;
   if (!d_xyz && !d_rgb && !d_idx) return TSDF_OK;  // sizing call
   if (cap < total) {

@@ -19,12 +19,20 @@ namespace {
 __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scale, int sub_c,
                              int sub_r, const uint8_t* __restrict__ rgb,
                              const uint8_t* __restrict__ mask, int H, int W, float max_depth,
-                             bool with_color, void* __restrict__ out, int* __restrict__ dmax_bits) {
+                             bool with_color, float4 intr /* fx, cx, fy, cy */, void* __restrict__ out,
+                             int* __restrict__ dmax_bits) {
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   float d = 0.0f;
   if (i < H * W) {
-    if (fmt == TSDF_DEPTH_U16) d = (float)reinterpret_cast<const uint16_t*>(depth)[i] * scale;
-    else                       d = reinterpret_cast<const float*>(depth)[i] * scale;
+    if (fmt == TSDF_DEPTH_U16 || fmt == TSDF_DEPTH_RANGE_U16) d = (float)reinterpret_cast<const uint16_t*>(depth)[i] * scale;
+    else                                                      d = reinterpret_cast<const float*>(depth)[i] * scale;
+    if (fmt >= TSDF_DEPTH_RANGE_F32) {  // lidar range -> camera-z depth, src/DoN.cpp:90-98
+      const int r = i / W, c = i - r * W;
+      const float x = ((float)c - intr.y) / intr.x;
+      const float y = ((float)r - intr.w) / intr.z;
+      const float rim = sqrtf(x * x + y * y + 1.0f);
+      d = d / rim;
+    }
     if (sub_c > 1 || sub_r > 1) {  // examples/label_instance_rgbd.cpp:89-97
       int r = i / W, c = i - r * W;
       if ((c % sub_c) != 0 || (r % sub_r) != 0) d = 0.0f;
@@ -104,12 +112,13 @@ __global__ void k_instance_origin(const float* __restrict__ depth, const uint8_t
 
 int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
                       const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
-                      bool with_color, void* d_frame, cudaStream_t st) {
+                      bool with_color, const float intr[4], void* d_frame, cudaStream_t st) {
   int n = H * W;
+  const float4 k4 = intr ? make_float4(intr[0], intr[1], intr[2], intr[3]) : make_float4(1.f, 0.f, 1.f, 0.f);
   int* d_dmax = reinterpret_cast<int*>(frame_dmax_ptr(d_frame, (size_t)n));
   CU_CHECK(cudaMemsetAsync(d_dmax, 0, sizeof(int), st));
   k_frame_prep<<<(n + 255) / 256, 256, 0, st>>>(d_depth, depth_fmt, depth_scale, sub_c, sub_r, d_rgb,
-                                                d_mask, H, W, max_depth, with_color, d_frame, d_dmax);
+                                                d_mask, H, W, max_depth, with_color, k4, d_frame, d_dmax);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }

@@ -143,9 +143,11 @@ class Volume:
         if sync:
             self._keep.clear()
 
-    def integrate_raw(self, depth_u16, depth_scale, rgb, T_wc, K=None, obs_weight=1.0, subsample=(1, 1)):
-        depth, rgb, Kc, T = self._frame_args(depth_u16, rgb, K, T_wc, dtype=np.uint16)
-        check(self.lib.tsdf_integrate_raw_async(self.h, ptr(depth), DEPTH_U16, np.float32(depth_scale),
+    def integrate_raw(self, depth_u16, depth_scale, rgb, T_wc, K=None, obs_weight=1.0, subsample=(1, 1), fmt=DEPTH_U16):
+        """fmt: DEPTH_U16 / DEPTH_F32 raw depth, DEPTH_RANGE_* lidar range images."""
+        dt = np.uint16 if fmt in (DEPTH_U16, capi.DEPTH_RANGE_U16) else np.float32
+        depth, rgb, Kc, T = self._frame_args(depth_u16, rgb, K, T_wc, dtype=dt)
+        check(self.lib.tsdf_integrate_raw_async(self.h, ptr(depth), int(fmt), np.float32(depth_scale),
                                                 int(subsample[0]), int(subsample[1]), ptr(rgb), ptr(Kc),
                                                 ptr(T), np.float32(obs_weight)))
         self.sync()

@@ -68,6 +68,25 @@ def test_host_matrix_helpers_match_oracle(pkg, oracle, synth):
     assert lib.tsdf_invert_matrix(Z.ctypes.data, out.ctypes.data) == pkg.capi.E_SINGULAR
 
 
+def test_read_bundle_poses_matches_fixture(pkg, tmp_path):
+    """bundle.txt ingest (reference examples/label_instance_rgbd.cpp:289-330): the first cameras of
+    the reference's saved fr3_office run against the committed Twc fixture made from the same file."""
+    import ctypes as C
+    lib = pkg.load()
+    path = os.path.join(ROOT, "tests", "golden", "bundle_head.txt").encode()
+    n = C.c_int(0)
+    assert lib.tsdf_read_bundle_poses(path, None, 0, C.byref(n)) == 0 and n.value == 4
+    T = np.zeros((4, 16), np.float32)
+    assert lib.tsdf_read_bundle_poses(path, T.ctypes.data_as(C.c_void_p), 2, C.byref(n)) == pkg.capi.E_CAPACITY
+    assert lib.tsdf_read_bundle_poses(path, T.ctypes.data_as(C.c_void_p), 4, C.byref(n)) == 0
+    ref = np.load(os.path.join(ROOT, "tests", "golden", "fr3_office_Twc.npy"))[:4]
+    assert np.array_equal(T.reshape(4, 4, 4)[:, :3, :3], ref.reshape(4, 4, 4)[:, :3, :3])   # transpose is exact
+    assert np.max(np.abs(T - ref)) < 1e-6 and (T[:, 12:] == [0, 0, 0, 1]).all()
+    assert lib.tsdf_read_bundle_poses(str(tmp_path / "missing.txt").encode(), None, 0, C.byref(n)) == pkg.capi.E_IO
+    (tmp_path / "bad.txt").write_text("2 0\n0 0 0\n1 0 0\n0 1\n")
+    assert lib.tsdf_read_bundle_poses(str(tmp_path / "bad.txt").encode(), T.ctypes.data_as(C.c_void_p), 4, C.byref(n)) == pkg.capi.E_IO
+
+
 def test_slab_ranges_partition_the_grid(pkg):
     for dz in (1024, 256, 200, 130, 7):
         for n in (1, 2, 3, 4, 8):

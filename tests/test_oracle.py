@@ -112,3 +112,25 @@ def test_oracle_extract_predicates_and_origin(oracle, synth):
     x = ((u.astype(np.float32) - K[2]) * z * (np.float32(1) / K[0]))[ok]
     y = ((v.astype(np.float32) - K[5]) * z * (np.float32(1) / K[4]))[ok]
     assert np.allclose(og, [x.min(), y.min(), z[ok].min()], rtol=0, atol=0)
+
+
+def test_oracle_range_to_depth_known_answers(oracle, synth):
+    """Lidar range -> depth (reference src/DoN.cpp:86-100): on the principal ray d == range; a
+    pixel whose ray has x = 3/4, y = 1 has rim = sqrt(9/16 + 1 + 1) = 1.6007810593582121."""
+    K = np.array([400, 0, 100, 0, 300, 50, 0, 0, 1], np.float32)
+    rng = np.zeros((120, 500), np.float32)
+    rng[50, 100] = 7.0           # principal point: x = y = 0
+    rng[350 % 120, 0] = 0.0
+    rng[110, 400] = 4.0          # x = 300/400, y = 60/300 -> rim = sqrt(0.5625 + 0.04 + 1)
+    d = oracle.range_to_depth(rng, K, scale=0.5)
+    assert d[50, 100] == np.float32(3.5)
+    x, y = np.float32(300) / np.float32(400), np.float32(60) / np.float32(300)
+    rim = np.sqrt(np.float32(x * x + y * y + np.float32(1)), dtype=np.float32)
+    assert d[110, 400] == np.float32(np.float32(4.0 * 0.5) / rim)
+    assert d[0, 0] == 0 and np.count_nonzero(d) == 2
+    # against float64 geometry: depth = range * cos(angle to the optical axis)
+    rr = np.full((120, 500), 10.0, np.float32)
+    dd = oracle.range_to_depth(rr, K, 1.0)
+    cc, rw = np.meshgrid(np.arange(500), np.arange(120))
+    ref = 10.0 / np.sqrt(((cc - 100.0) / 400.0) ** 2 + ((rw - 50.0) / 300.0) ** 2 + 1.0)
+    assert np.max(np.abs(dd - ref)) < 5e-6

@@ -232,6 +232,30 @@ def test_raw_u16_depth_and_subsampling(pkg, oracle, synth):
     assert_volume_equal(gt, gw, gc, t, w, c)
 
 
+def test_lidar_range_input_mode(pkg, oracle, synth):
+    """TSDF_DEPTH_RANGE_*: the frame holds ranges along the ray; the prep kernel converts them with
+    the reference's formula (src/DoN.cpp:86-100, src/Object.cpp:611-619) bit for bit."""
+    dims, vs = (64, 48, 64), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=55)
+    K = synth.TUM3_K
+    H, W = synth.TUM3_HW
+    cc, rr = np.meshgrid(np.arange(W, dtype=np.float64), np.arange(H, dtype=np.float64))
+    rim = np.sqrt(((cc - K[2]) / K[0]) ** 2 + ((rr - K[5]) / K[4]) ** 2 + 1.0)
+    ranges = [(d.astype(np.float64) * rim).astype(np.float32) for d, _, _ in frames]       # metres
+    ranges_u16 = [np.clip(np.round(r.astype(np.float64) * 500.0), 0, 65535).astype(np.uint16) for r in ranges]
+    for fmt, imgs, scale in ((pkg.capi.DEPTH_RANGE_F32, ranges, 1.0), (pkg.capi.DEPTH_RANGE_U16, ranges_u16, 1.0 / 500.0)):
+        conv = [oracle.range_to_depth(np.asarray(im, np.float32), K, np.float32(scale)) for im in imgs]
+        oframes = [(c, f[1], f[2]) for c, f in zip(conv, frames)]
+        p, t, w, c, ow = oracle_run(oracle, dims, vs, origin, oframes, SEM_FUSIONPY, True)
+        cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+        with pkg.Volume(cfg) as vol:
+            for im, (_, rgb, T) in zip(imgs, frames):
+                vol.integrate_raw(im, scale, rgb, T, fmt=fmt)
+            gt, gw, gc = vol.download()
+        assert sum(ow) > 0
+        assert_volume_equal(gt, gw, gc, t, w, c)
+
+
 def test_instance_origin_on_device(pkg, oracle, synth):
     import ctypes as C
     _, frames = synth.s_real((32, 32, 32), 0.05, n_frames=1, seed=81)
