@@ -435,6 +435,77 @@ def extras(pkg, line, frames, origin):
                             "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts}
     except Exception as e:
         line["extra_c2"] = {"error": str(e)}
+    # C3: KITTI-shaped 1241x376 stereo-depth frames into the 1024x256x1024 outdoor grid (10 cm voxels,
+    # max_depth 50 m), whole grid on this GPU (the 8-way z-slab version of it is a parity test)
+    try:
+        dims, vs, nfr = (1024, 256, 1024), 0.1, 100
+        o3, fr3 = synth.s_kitti(n_frames=4, voxel_size=vs, dims=dims)
+        cfg = pkg.make_config(dims, vs, o3, semantics=pkg.SEM_FUSIONPY, with_color=True, K=synth.KITTI_K,
+                              im_hw=synth.KITTI_HW, max_depth=50.0)
+        with pkg.Volume(cfg) as v3:
+            for i in range(3):
+                v3.integrate(*fr3[i % 4][:2], fr3[i % 4][2], sync=False)
+            v3.sync()
+            v3.reset()
+            v3.kernel_timing(True)
+            v3.timer_start()
+            for i in range(nfr):
+                d, c, T = fr3[i % 4]
+                v3.integrate(d, c, T, sync=False)
+            ms = v3.timer_stop()
+            ksum, kn = v3.kernel_timing_read()
+            wr = v3.stats().voxels_written
+        nv = dims[0] * dims[1] * dims[2]
+        line["extra_c3"] = {"workload": "C3: 100 KITTI-shaped 1241x376 frames (4 distinct) into 1024x256x1024 @ 10 cm, "
+                                        "scene S-kitti, max_depth 50 m, pageable host frames, 1 GPU",
+                            "value": nfr * nv / (ms * 1e-3) / 1e9, "unit": UNIT, "frames_per_sec": nfr / (ms * 1e-3),
+                            "kernel_ms": ksum / max(kn, 1), "coverage_last_frame": wr / nv}
+    except Exception as e:
+        line["extra_c3"] = {"error": str(e)}
+    # C5: 256 per-instance 128^3 volumes (4 mm voxels, class-TSDF semantics, origins by the
+    # Object::Object rule) integrated per frame from ONE shared frame + 256 masks in ONE launch
+    try:
+        n_inst, dims, vs, nfr = 256, (128, 128, 128), 0.004, 20
+        _, fr5 = synth.s_real((64, 64, 64), 0.08, n_frames=4, seed=91)
+        masks, boxes5 = synth.instance_masks(n_inst, seed=92)
+        base = fr5[0][2]
+        lib, d0 = pkg.load(), np.ascontiguousarray(fr5[0][0], np.float32)
+
+        def origin_of(m):   # device-side Object::Object origin rule (tsdf_instance_origin, src/Object.cpp:37-49)
+            out = np.zeros(3, np.float32)
+            pkg.capi.check(lib.tsdf_instance_origin(0, d0.ctypes.data, m.ctypes.data, d0.shape[0], d0.shape[1],
+                                                    synth.TUM3_K.ctypes.data, out.ctypes.data))
+            return out
+        cfgs = [pkg.make_config(dims, vs, origin_of(masks[i]), semantics=pkg.SEM_TSDFCU, with_color=False,
+                                base2world=base, max_depth=30.0, vol_id=i) for i in range(n_inst)]
+        act = np.arange(n_inst, dtype=np.int32)
+        bx, crops = pkg.Batch.crop_masks(masks, boxes5)   # what a Mask-RCNN host holds: boxes + masks
+        with pkg.Batch(cfgs) as b:
+            for i in range(2):
+                b.integrate(fr5[i % 4][0], None, act, masks, fr5[i % 4][2])
+                b.integrate_boxes(fr5[i % 4][0], None, act, bx, crops, fr5[i % 4][2])
+            b.sync()
+            t0 = time.perf_counter()
+            for i in range(nfr):
+                b.integrate(fr5[i % 4][0], None, act, masks, fr5[i % 4][2])
+            b.sync()
+            dt_full = time.perf_counter() - t0
+            t0 = time.perf_counter()
+            for i in range(nfr):
+                b.integrate_boxes(fr5[i % 4][0], None, act, bx, crops, fr5[i % 4][2])
+            b.sync()
+            dt = time.perf_counter() - t0
+            st = b.stats()
+        nv = n_inst * dims[0] * dims[1] * dims[2]
+        line["extra_c5"] = {"workload": f"C5: {n_inst} instance volumes of 128^3 @ 4 mm, one shared 640x480 frame + {n_inst} "
+                                        "8-bit masks cropped to their boxes (pageable host) per step, one launch per step; host wall clock",
+                            "value": nfr * nv / dt / 1e9, "unit": UNIT, "frames_per_sec": nfr / dt,
+                            "instances_per_sec": nfr * n_inst / dt, "kernel_ms": st.last_kernel_ms,
+                            "mask_upload_MB_per_step": crops.nbytes / 1e6,
+                            "full_frame_masks": {"frames_per_sec": nfr / dt_full, "mask_upload_MB_per_step": masks.nbytes / 1e6},
+                            "written_last_frame": int(st.voxels_written)}
+    except Exception as e:
+        line["extra_c5"] = {"error": str(e)}
 
 
 def main():

@@ -202,6 +202,15 @@ int tsdf_batch_size(const tsdf_batch* b, int* n);
 int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
                                const int32_t* active, int n_active, const uint8_t* masks,
                                const float* K, const float* T_wc, float obs_weight);
+/* Same, with the masks cropped to their Mask-RCNN bounding boxes (boxes[i], reference
+ * src/Engine.cpp:127,197): boxes = n_active x {x, y, w, h} pixels inside the image; mask_crops =
+ * the n_active crops concatenated, crop i is h_i rows of w_i bytes.  Pixels outside a box count
+ * as mask 0.  Uploads sum(w*h) bytes instead of n_active*H*W; results are identical to the
+ * full-frame call.                                                              */
+int tsdf_batch_integrate_boxes_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
+                                     const int32_t* active, int n_active, const int32_t* boxes,
+                                     const uint8_t* mask_crops, const float* K, const float* T_wc,
+                                     float obs_weight);
 int tsdf_batch_sync(tsdf_batch* b);
 int tsdf_batch_get_stats(tsdf_batch* b, tsdf_stats* s);
 int tsdf_batch_download(tsdf_batch* b, int instance, float* tsdf, float* weight, float* color);

@@ -75,6 +75,7 @@ SIGNATURES = {
     "tsdf_batch_destroy": (_I, [_VP]),
     "tsdf_batch_size": (_I, [_VP, C.POINTER(_I)]),
     "tsdf_batch_integrate_async": (_I, [_VP, _VP, _VP, _VP, _I, _VP, _VP, _VP, _F]),
+    "tsdf_batch_integrate_boxes_async": (_I, [_VP, _VP, _VP, _VP, _I, _VP, _VP, _VP, _VP, _F]),
     "tsdf_batch_sync": (_I, [_VP]),
     "tsdf_batch_get_stats": (_I, [_VP, C.POINTER(Stats)]),
     "tsdf_batch_download": (_I, [_VP, _I, _VP, _VP, _VP]),

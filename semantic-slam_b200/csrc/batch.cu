@@ -11,6 +11,24 @@
 
 #include "common.cuh"
 
+struct MaskBox { int x, y, w, h; long long off; };  // bounding box of a cropped mask + its offset in the crop block
+
+namespace {
+// Boxes path: the host uploads only the mask pixels inside each instance's bounding box
+// (Mask-RCNN gives boxes[i] next to masks[i], reference src/Engine.cpp:127,197); this kernel
+// rebuilds the full-frame 8-bit masks the integrate kernel gathers from (zero outside the box).
+__global__ void k_expand_masks(const uint8_t* __restrict__ crops, const MaskBox* __restrict__ boxes,
+                               int H, int W, uint8_t* __restrict__ masks) {
+  const MaskBox bx = boxes[blockIdx.y];
+  uint8_t* out = masks + (size_t)blockIdx.y * H * W;
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; p < H * W; p += gridDim.x * blockDim.x) {
+    const int r = p / W, c = p - r * W;
+    const bool in = r >= bx.y && r < bx.y + bx.h && c >= bx.x && c < bx.x + bx.w;
+    out[p] = in ? crops[bx.off + (long long)(r - bx.y) * bx.w + (c - bx.x)] : (uint8_t)0;
+  }
+}
+}  // namespace
+
 struct tsdf_batch {
   int n = 0;
   std::vector<tsdf_vol*> vols;   // per-instance state (arrays, config, base pose); own streams unused
@@ -19,6 +37,9 @@ struct tsdf_batch {
   BatchDesc* h_descs = nullptr;  // pinned
   uint8_t* d_masks = nullptr;    // n * H*W
   uint8_t* h_masks = nullptr;    // pinned staging, n * H*W
+  uint8_t* d_crops = nullptr;    // cropped masks as uploaded (boxes path), <= n * H*W
+  MaskBox* d_boxes = nullptr;
+  MaskBox* h_boxes = nullptr;    // pinned
   unsigned long long* d_written = nullptr;
   unsigned long long* h_written = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr, masks_free = nullptr;
@@ -34,7 +55,8 @@ extern "C" int tsdf_batch_destroy(tsdf_batch* b) {
     DeviceGuard g(b->frame_owner->cfg.device);
     cudaStreamSynchronize(b->frame_owner->s_compute);
     cudaStreamSynchronize(b->frame_owner->s_copy);
-    cudaFree(b->d_descs); cudaFree(b->d_masks); cudaFree(b->d_written);
+    cudaFree(b->d_descs); cudaFree(b->d_masks); cudaFree(b->d_written); cudaFree(b->d_crops); cudaFree(b->d_boxes);
+    if (b->h_boxes) cudaFreeHost(b->h_boxes);
     if (b->h_descs) cudaFreeHost(b->h_descs);
     if (b->h_masks) cudaFreeHost(b->h_masks);
     if (b->h_written) cudaFreeHost(b->h_written);
@@ -72,6 +94,8 @@ extern "C" int tsdf_batch_create(const tsdf_config* cfgs, int n, tsdf_batch** ou
   if (cudaHostAlloc(&b->h_descs, sizeof(BatchDesc) * (size_t)n, cudaHostAllocDefault)) return fail("cudaHostAlloc descs");
   if (cudaMalloc(&b->d_masks, px * (size_t)n)) return fail("cudaMalloc masks");
   if (cudaHostAlloc(&b->h_masks, px * (size_t)n, cudaHostAllocDefault)) return fail("cudaHostAlloc masks");
+  if (cudaMalloc(&b->d_boxes, sizeof(MaskBox) * (size_t)n)) return fail("cudaMalloc boxes");
+  if (cudaHostAlloc(&b->h_boxes, sizeof(MaskBox) * (size_t)n, cudaHostAllocDefault)) return fail("cudaHostAlloc boxes");
   if (cudaMalloc(&b->d_written, 8)) return fail("cudaMalloc counter");
   if (cudaHostAlloc(&b->h_written, 8, cudaHostAllocDefault)) return fail("cudaHostAlloc counter");
   *b->h_written = 0;
@@ -87,9 +111,9 @@ extern "C" int tsdf_batch_size(const tsdf_batch* b, int* n) {
   return TSDF_OK;
 }
 
-extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
-                                          const int32_t* active, int n_active, const uint8_t* masks,
-                                          const float* K, const float* T_wc, float obs_weight) {
+static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb, const int32_t* active,
+                           int n_active, const uint8_t* masks, const int32_t* boxes, const uint8_t* crops,
+                           const float* K, const float* T_wc, float obs_weight) {
   REQUIRE(b && depth && T_wc && active && n_active >= 1 && n_active <= b->n, "bad argument");
   tsdf_vol* fo = b->frame_owner;
   DeviceGuard g(fo->cfg.device);
@@ -104,7 +128,34 @@ extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, con
   ++fo->seq;
   // 2. masks: one block copy (device masks are used in place)
   const uint8_t* d_masks = nullptr;
-  if (masks) {
+  if (boxes) {  // cropped masks: upload sum(w*h) bytes, expand to full frames on the device
+    const int H = fo->cfg.im_h, W = fo->cfg.im_w;
+    long long total = 0;
+    for (int i = 0; i < n_active; ++i) {
+      const int32_t* q = boxes + 4 * i;
+      REQUIRE(q[0] >= 0 && q[1] >= 0 && q[2] >= 0 && q[3] >= 0 && q[0] + q[2] <= W && q[1] + q[3] <= H,
+              "mask box outside the image");
+      b->h_boxes[i] = MaskBox{q[0], q[1], q[2], q[3], total};
+      total += (long long)q[2] * q[3];
+    }
+    if (!b->d_crops) CU_CHECK(cudaMalloc(&b->d_crops, px * (size_t)b->n));
+    if (total > 0) {
+      REQUIRE(crops, "boxes given without mask crops");
+      cudaPointerAttributes a;
+      const bool known = cudaPointerGetAttributes(&a, crops) == cudaSuccess;
+      cudaGetLastError();
+      const void* src = crops;
+      if (!(known && (a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged))) {
+        memcpy(b->h_masks, crops, (size_t)total);  // pageable -> pinned staging
+        src = b->h_masks;
+      }
+      CU_CHECK(cudaMemcpyAsync(b->d_crops, src, (size_t)total, cudaMemcpyDefault, fo->s_copy));
+    }
+    CU_CHECK(cudaMemcpyAsync(b->d_boxes, b->h_boxes, sizeof(MaskBox) * (size_t)n_active, cudaMemcpyHostToDevice, fo->s_copy));
+    k_expand_masks<<<dim3(32, n_active), 256, 0, fo->s_copy>>>(b->d_crops, b->d_boxes, H, W, b->d_masks);
+    CU_CHECK(cudaGetLastError());
+    d_masks = b->d_masks;
+  } else if (masks) {
     cudaPointerAttributes a;
     bool on_dev = cudaPointerGetAttributes(&a, masks) == cudaSuccess &&
                   (a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged);
@@ -161,6 +212,20 @@ extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, con
   b->last_visited = visited;
   b->last_color = color;
   return TSDF_OK;
+}
+
+extern "C" int tsdf_batch_integrate_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
+                                          const int32_t* active, int n_active, const uint8_t* masks,
+                                          const float* K, const float* T_wc, float obs_weight) {
+  return batch_integrate(b, depth, rgb, active, n_active, masks, nullptr, nullptr, K, T_wc, obs_weight);
+}
+
+extern "C" int tsdf_batch_integrate_boxes_async(tsdf_batch* b, const float* depth, const uint8_t* rgb,
+                                                const int32_t* active, int n_active, const int32_t* boxes,
+                                                const uint8_t* mask_crops, const float* K, const float* T_wc,
+                                                float obs_weight) {
+  REQUIRE(boxes, "null boxes");
+  return batch_integrate(b, depth, rgb, active, n_active, nullptr, boxes, mask_crops, K, T_wc, obs_weight);
 }
 
 extern "C" int tsdf_batch_sync(tsdf_batch* b) {

@@ -243,6 +243,83 @@ class Volume:
         check(self.lib.tsdf_load_bin(self.h, path.encode()))
 
 
+class Batch:
+    """N per-instance volumes that share one frame per call (`tsdf_batch*`): BASELINE config 5, the
+    Engine::Run mask loop (reference src/Engine.cpp:172-233) as ONE upload + ONE launch."""
+
+    def __init__(self, cfgs):
+        self.lib = capi.load()
+        self.n = len(cfgs)
+        arr = (Config * self.n)(*cfgs)
+        self.h = C.c_void_p()
+        check(self.lib.tsdf_batch_create(arr, self.n, C.byref(self.h)))
+        self.dims = [(c.dim_x, c.dim_y, c.dim_z) for c in cfgs]
+        self.with_color = [bool(c.with_color) for c in cfgs]
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.tsdf_batch_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def integrate(self, depth, rgb, active, masks, T_wc, K=None, obs_weight=1.0, sync=False):
+        """masks: len(active) x H x W uint8 (0/255) or None; depth/rgb/masks may be device pointers."""
+        a = np.ascontiguousarray(active, np.int32)
+        T = f32(T_wc, 16)
+        Kc = None if K is None else f32(K, 9)
+        self._keep.append((depth, rgb, a, masks, T, Kc))
+        check(self.lib.tsdf_batch_integrate_async(self.h, ptr(depth), ptr(rgb), ptr(a), len(a), ptr(masks),
+                                                  ptr(Kc), ptr(T), np.float32(obs_weight)))
+        if sync:
+            self.sync()
+
+    def integrate_boxes(self, depth, rgb, active, boxes, crops, T_wc, K=None, obs_weight=1.0, sync=False):
+        """boxes: len(active) x 4 int32 {x, y, w, h}; crops: the masks inside their boxes, concatenated."""
+        a = np.ascontiguousarray(active, np.int32)
+        bx = np.ascontiguousarray(boxes, np.int32).reshape(-1, 4)
+        T = f32(T_wc, 16)
+        Kc = None if K is None else f32(K, 9)
+        self._keep.append((depth, rgb, a, bx, crops, T, Kc))
+        check(self.lib.tsdf_batch_integrate_boxes_async(self.h, ptr(depth), ptr(rgb), ptr(a), len(a), ptr(bx),
+                                                        ptr(crops), ptr(Kc), ptr(T), np.float32(obs_weight)))
+        if sync:
+            self.sync()
+
+    @staticmethod
+    def crop_masks(masks, boxes):
+        """Full-frame masks + boxes {x, y, w, h} -> (clipped boxes, concatenated crops)."""
+        H, W = masks.shape[1:]
+        bx = np.array(boxes, np.int32).reshape(-1, 4).copy()
+        x0, y0 = np.clip(bx[:, 0], 0, W), np.clip(bx[:, 1], 0, H)
+        x1, y1 = np.clip(bx[:, 0] + bx[:, 2], 0, W), np.clip(bx[:, 1] + bx[:, 3], 0, H)
+        bx = np.stack([x0, y0, x1 - x0, y1 - y0], 1).astype(np.int32)
+        crops = np.concatenate([masks[i, b[1]:b[1] + b[3], b[0]:b[0] + b[2]].reshape(-1) for i, b in enumerate(bx)])
+        return bx, np.ascontiguousarray(crops, np.uint8)
+
+    def sync(self):
+        check(self.lib.tsdf_batch_sync(self.h))
+        self._keep.clear()
+
+    def stats(self):
+        s = Stats()
+        check(self.lib.tsdf_batch_get_stats(self.h, C.byref(s)))
+        self._keep.clear()
+        return s
+
+    def download(self, i):
+        n = int(np.prod(self.dims[i]))
+        t, w = np.empty(n, np.float32), np.empty(n, np.float32)
+        c = np.empty(n, np.float32) if self.with_color[i] else None
+        check(self.lib.tsdf_batch_download(self.h, int(i), ptr(t), ptr(w), ptr(c)))
+        return t, w, c
+
+
 class TSDF:
     """Mirror of the reference's `class TSDF` (include/tsdf.hpp:22-98).
 

@@ -351,6 +351,38 @@ def test_batched_instances_match_per_instance_oracle(pkg, oracle, synth):
         lib.tsdf_batch_destroy(hb)
 
 
+def test_batched_instances_cropped_masks_equal_full_masks(pkg, oracle, synth):
+    """tsdf_batch_integrate_boxes_async (masks cropped to their Mask-RCNN boxes, reference
+    src/Engine.cpp:127,197) gives the volumes of the full-frame mask call, colour included, and
+    matches the per-instance oracle."""
+    n_inst, dims, vs = 5, (32, 32, 32), 0.02
+    _, frames = synth.s_real((64, 64, 64), 0.08, n_frames=3, seed=93)
+    masks, boxes = synth.instance_masks(n_inst, seed=94)
+    origins = [oracle.instance_origin(frames[0][0], masks[i], synth.TUM3_K) for i in range(n_inst)]
+    cfgs = [pkg.make_config(dims, vs, origins[i], semantics=SEM_FUSIONPY, with_color=True, vol_id=i)
+            for i in range(n_inst)]
+    active_sets = [[0, 1, 2, 3, 4], [3, 1], [4, 0, 2]]
+    with pkg.Batch(cfgs) as full, pkg.Batch(cfgs) as crop:
+        for (d, rgb, T), act in zip(frames, active_sets):
+            full.integrate(d, rgb, act, np.ascontiguousarray(masks[act]), T, sync=True)
+            bx, crops = pkg.Batch.crop_masks(masks[act], boxes[act])
+            assert crops.size < 0.2 * masks[act].size
+            crop.integrate_boxes(d, rgb, act, bx, crops, T, sync=True)
+        assert full.stats().voxels_written == crop.stats().voxels_written
+        for i in range(n_inst):
+            ft, fw, fc = full.download(i)
+            ct, cw, cc = crop.download(i)
+            assert np.array_equal(bits(ft), bits(ct)) and np.array_equal(fw, cw) and np.array_equal(fc, cc)
+            p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), origins[i], synth.TUM3_HW, synth.TUM3_K,
+                              np.inf, SEM_FUSIONPY)
+            t, w, c = oracle.new_volume(p, True)
+            for (d, rgb, T), act in zip(frames, active_sets):
+                if i in act:
+                    md = (d * (masks[i] >= 128)).astype(np.float32)
+                    oracle.integrate(p, T.reshape(16), md, oracle.pack_color(rgb), 1.0, t, w, c)
+            assert_volume_equal(ct, cw, cc, t, w, c)
+
+
 def test_full_size_properties_c1(pkg, synth):
     """BASELINE config 1 size (256^3, 2 cm) through size-independent properties: S-full writes
     every voxel every frame (N_written == N_vox, weights == frame count everywhere, tsdf stays
