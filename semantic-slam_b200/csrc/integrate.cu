@@ -35,9 +35,10 @@ template <int VEC> struct VecT;
 template <> struct VecT<4> { using type = float4; };
 template <> struct VecT<1> { using type = float; };
 
+template <bool L2_ONLY>
 __device__ __forceinline__ void prefetch_line(const float* p, int mode) {
-  if (mode == 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
-  else           asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+  if (L2_ONLY || mode == 1) asm volatile("prefetch.global.L2 [%0];" ::"l"(p));
+  else                      asm volatile("prefetch.global.L1 [%0];" ::"l"(p));  // A/B only (legacy kernel)
 }
 
 template <int VEC>
@@ -163,7 +164,10 @@ __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, f
   p.ok = inr && u > -0.5f && u < g.w_lim && v > -0.5f && v < g.h_lim;
   const int px = em::round_half_away_nonneg_int(u);
   const int py = em::round_half_away_nonneg_int(v);
-  p.pix = p.ok ? py * g.W + px : 0;
+  // select, not branch: the rounding of an out-of-image u/v is harmless, and a branch here
+  // would sit between the four gathers of a run
+  int pix = py * g.W + px, okm = p.ok ? -1 : 0;
+  asm("and.b32 %0, %1, %2;" : "=r"(p.pix) : "r"(pix), "r"(okm));
   return p;
 }
 
@@ -390,15 +394,15 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     if (pf) {
       if (lr == tr) {
         const int64_t pb = (int64_t)r * g.n_fast + f0;
-        prefetch_line(g.tsdf + pb, pf);
-        prefetch_line(g.weight + pb, pf);
-        if constexpr (COLOR) prefetch_line(g.color + pb, pf);
+        prefetch_line<CULL != 1>(g.tsdf + pb, pf);
+        prefetch_line<CULL != 1>(g.weight + pb, pf);
+        if constexpr (COLOR) prefetch_line<CULL != 1>(g.color + pb, pf);
       }
       if (any_prev && lr + rp < rows_per_block && r + rp < n_rows) {
         const int64_t pb = (int64_t)(r + rp) * g.n_fast + f0;
-        prefetch_line(g.tsdf + pb, pf);
-        prefetch_line(g.weight + pb, pf);
-        if constexpr (COLOR) prefetch_line(g.color + pb, pf);
+        prefetch_line<CULL != 1>(g.tsdf + pb, pf);
+        prefetch_line<CULL != 1>(g.weight + pb, pf);
+        if constexpr (COLOR) prefetch_line<CULL != 1>(g.color + pb, pf);
       }
     }
     Hit hit[NF][VEC];
@@ -423,7 +427,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           hit[f][j] = probe_literal_body<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, camx[j], camy[j], camz[j]);
           any = any || hit[f][j].ok;
         }
-      } else if constexpr (CULL != 2) {
+      } else if constexpr (CULL == 1) {  // legacy one-piece probe (A/B baseline, variant bit 10)
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
           hit[f][j] = probe_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, camx[j], camy[j], camz[j]);
@@ -448,7 +452,10 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
             pr[j] = project_exact(P.f[f], g, camx[j], camy[j], camz[j]);
             in_image = in_image || pr[j].ok;
           }
-          if (in_image) {  // else: the whole run projects outside the image, no gather
+          // CULL == 2 (sparse frames): a run that projects outside the image stops before the
+          // gather.  CULL == 0 (dense frames): no early-out, the run is branch-free from here, so
+          // the four gathers issue back to back.
+          if (CULL == 0 || in_image) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
               hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, pr[j], camz[j]);
@@ -478,9 +485,21 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       const float obs = P.f[f].obs_weight;
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        if (hit[f][j].ok) {
-          update_voxel<COLOR, MATH, WMODE>(t[j], w[j], col[j], hit[f][j], obs);
-          ++n_written;
+        if constexpr (CULL == 0) {
+          // dense frames: nearly every voxel of a written run is updated, so compute the update
+          // unconditionally and select (no divergence bookkeeping around 60 instructions)
+          float nt = t[j], nw = w[j], nc = col[j];
+          update_voxel<COLOR, MATH, WMODE>(nt, nw, nc, hit[f][j], obs);
+          const bool ok = hit[f][j].ok;
+          t[j] = ok ? nt : t[j];
+          w[j] = ok ? nw : w[j];
+          col[j] = ok ? nc : col[j];
+          n_written += ok ? 1u : 0u;
+        } else {
+          if (hit[f][j].ok) {
+            update_voxel<COLOR, MATH, WMODE>(t[j], w[j], col[j], hit[f][j], obs);
+            ++n_written;
+          }
         }
       }
     }
@@ -527,7 +546,7 @@ __global__ void k_publish(unsigned long long* __restrict__ written, unsigned lon
 }
 
 int g_prefetch_mode = 1;  // 0 off, 1 L2, 2 L1 (set per launch from the handle's variant bits)
-int g_cull = 1;           // 0: plain kernel, 1: segment cull + staged probe (chosen per launch)
+int g_cull = 1;           // 0: dense kernel, 1: segment cull + staged probe (chosen per launch), 2: legacy dense
 int g_rows_mult = 16;
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
@@ -553,8 +572,9 @@ int launch_t(const GridP& g, const FrameP* frames, cudaStream_t st) {
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
   Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1);
-  if (g_cull) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
-  else        k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  if (g_cull == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  else if (g_cull == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }
@@ -642,7 +662,8 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
   // projects inside every frame's image (then no segment can be culled by the frustum and the
   // plain kernel is ~2-5 % faster); a pure performance choice, results are identical
-  g_cull = (v->variant & 64) ? 0 : ((v->variant & 128) ? 1 : (slab_inside_every_frustum(g, frames, nf) ? 0 : 1));
+  g_cull = (v->variant & 1024) ? 2 /* legacy dense kernel, A/B only */
+         : (v->variant & 64) ? 0 : ((v->variant & 128) ? 1 : (slab_inside_every_frustum(g, frames, nf) ? 0 : 1));
   const int wmode = (color && v->wmode_ok) ? 1 : 0;
   if (literal || !vec4 || !(nf == 1 || nf == 2 || nf == 4 || nf == 8)) {
     for (int i = 0; i < nf; ++i) {
