@@ -268,7 +268,7 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   const size_t px = frame_pixels(v->cfg);
   if (!s.d_raw) {
     CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
-    CU_CHECK(cudaMalloc(&s.d_frame, frame_alloc_bytes(px)));  // float4 per pixel (float when no colour) + tail
+    CU_CHECK(cudaMalloc(&s.d_frame, frame_alloc_bytes(v->cfg.im_h, v->cfg.im_w)));  // float4 per pixel (float when no colour) + tail
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
   }

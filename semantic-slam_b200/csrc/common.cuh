@@ -141,10 +141,20 @@ struct tsdf_vol {
 };
 
 inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
-// A prepared frame is px*16 bytes of pixels followed by a 64-byte tail whose first word is the
-// frame's largest depth (written by k_frame_prep).
-constexpr size_t kFrameTailBytes = 64;
-inline size_t frame_alloc_bytes(size_t px) { return px * 16 + kFrameTailBytes; }
+// A prepared frame is px*16 bytes of pixels followed by a tail written by k_frame_prep:
+//   word 0            the frame's largest depth (float bits; +inf when the frame holds a NaN)
+//   words 16 ...      max-depth tiles, level 0: 16x16 px tiles, row-major tw0 x th0
+//   then              max-depth tiles, level 1: 64x64 px tiles, row-major tw1 x th1
+// The integrate kernel's segment cull reads them ("everything this segment can project to is
+// nearer than the segment, or invalid").
+constexpr int kTile0Log2 = 4, kTile1Log2 = 6, kTailHeadWords = 16;
+__host__ __device__ inline int tiles_across(int n, int log2) { return (n + (1 << log2) - 1) >> log2; }
+inline size_t frame_tail_bytes(int H, int W) {
+  size_t words = kTailHeadWords + (size_t)tiles_across(W, kTile0Log2) * tiles_across(H, kTile0Log2) +
+                 (size_t)tiles_across(W, kTile1Log2) * tiles_across(H, kTile1Log2);
+  return (words * 4 + 63) & ~(size_t)63;
+}
+inline size_t frame_alloc_bytes(int H, int W) { return (size_t)H * W * 16 + frame_tail_bytes(H, W); }
 inline float* frame_dmax_ptr(const void* d_frame, size_t px) {
   return reinterpret_cast<float*>(reinterpret_cast<char*>(const_cast<void*>(d_frame)) + px * 16);
 }

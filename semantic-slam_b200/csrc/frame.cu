@@ -48,13 +48,29 @@ __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scal
       reinterpret_cast<float*>(out)[i] = d;
     }
   }
-  // Largest depth of the prepared frame, for the integrate kernel's conservative "beyond every
-  // surface" cull.  Stored depths are >= +0 or NaN; a NaN (which the reference integrates)
-  // counts as +inf so that it disables the cull.  Non-negative floats order like their bits.
+  // Largest depth of the frame and of its 16x16 / 64x64 pixel tiles, for the integrate kernel's
+  // conservative segment cull.  Stored depths are >= +0 or NaN; a NaN (which the reference
+  // integrates) counts as +inf so that it disables the cull.  Non-negative floats order like
+  // their bits, so integer atomicMax works; lanes of a warp that share a tile are reduced first.
+  const int lane = threadIdx.x & 31;
   int b = (d != d) ? 0x7f800000 : __float_as_int(d);
+  {
+    const int r = i < H * W ? i / W : 0, c = i < H * W ? i - r * W : 0;
+    const int tw0 = tiles_across(W, kTile0Log2), tw1 = tiles_across(W, kTile1Log2);
+    const int t0 = i < H * W ? (r >> kTile0Log2) * tw0 + (c >> kTile0Log2) : -1;
+    const int t1 = i < H * W ? (r >> kTile1Log2) * tw1 + (c >> kTile1Log2) : -1;
+    int* tiles0 = dmax_bits + kTailHeadWords;
+    int* tiles1 = tiles0 + tw0 * tiles_across(H, kTile0Log2);
+    unsigned m = __match_any_sync(0xffffffffu, t0);
+    int mx = __reduce_max_sync(m, b);
+    if (t0 >= 0 && mx > 0 && lane == __ffs(m) - 1) atomicMax(tiles0 + t0, mx);
+    m = __match_any_sync(0xffffffffu, t1);
+    mx = __reduce_max_sync(m, b);
+    if (t1 >= 0 && mx > 0 && lane == __ffs(m) - 1) atomicMax(tiles1 + t1, mx);
+  }
   b = __reduce_max_sync(0xffffffffu, b);
   __shared__ int wmax[8];
-  if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = b;
+  if (lane == 0) wmax[threadIdx.x >> 5] = b;
   __syncthreads();
   if (threadIdx.x == 0) {
     for (int k = 1; k < 8; ++k) b = max(b, wmax[k]);
@@ -116,7 +132,7 @@ int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int
   int n = H * W;
   const float4 k4 = intr ? make_float4(intr[0], intr[1], intr[2], intr[3]) : make_float4(1.f, 0.f, 1.f, 0.f);
   int* d_dmax = reinterpret_cast<int*>(frame_dmax_ptr(d_frame, (size_t)n));
-  CU_CHECK(cudaMemsetAsync(d_dmax, 0, sizeof(int), st));
+  CU_CHECK(cudaMemsetAsync(d_dmax, 0, frame_tail_bytes(H, W), st));
   k_frame_prep<<<(n + 255) / 256, 256, 0, st>>>(d_depth, depth_fmt, depth_scale, sub_c, sub_r, d_rgb,
                                                 d_mask, H, W, max_depth, with_color, k4, d_frame, d_dmax);
   CU_CHECK(cudaGetLastError());

@@ -202,7 +202,7 @@ __device__ __forceinline__ Hit sample_exact(const FrameP& f, const GridP& g, con
 // than the frame's largest depth plus the truncation).  Never true on NaN/Inf input.
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, float xa, float ya, float za,
-                                               float xb, float yb, float zb, float dmax) {
+                                               float xb, float yb, float zb, const int* __restrict__ tail) {
   const float big = 3.0e38f;
   const bool fin = fabsf(xa) <= big && fabsf(ya) <= big && fabsf(za) <= big &&
                    fabsf(xb) <= big && fabsf(yb) <= big && fabsf(zb) <= big;
@@ -212,6 +212,7 @@ __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, 
   const float zlo = fminf(za, zb), zhi = fmaxf(za, zb);
   if (zhi <= 0.0f) return true;                                   // :39 for every voxel
   if (!(zlo > 0.0f)) return false;                                // straddles the camera plane
+  const float dmax = __int_as_float(__ldg(tail));                 // largest depth of the frame
   if (dmax - zlo < -g.trunc) return true;                         // :49: d - z <= dmax - zlo
   // the four bounds below need RN quotients; inside the exponent window the shared-reciprocal
   // form is the IEEE quotient (exactmath.cuh) at a fraction of the cost of eight `/`
@@ -225,7 +226,30 @@ __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, 
   const float vmax = f.fy * em::div_rn(yhi, a2 ? zlo : zhi, a2 ? rlo : rhi) + f.cy;
   const float vmin = f.fy * em::div_rn(ylo, a3 ? zhi : zlo, a3 ? rhi : rlo) + f.cy;
   // :43 left of / right of / above / below the image
-  return umax <= -0.5f || umin >= g.w_lim || vmax <= -0.5f || vmin >= g.h_lim;
+  if (umax <= -0.5f || umin >= g.w_lim || vmax <= -0.5f || vmin >= g.h_lim) return true;
+  // Occlusion / invalid-depth test on the max-depth tiles of k_frame_prep.  Every voxel of the
+  // box that passes :43 reads a pixel (px, py) = (floor(u + 1/2), floor(v + 1/2)) with u in
+  // [umin, umax], v in [vmin, vmax]; the pixel rectangle below contains them all (directed
+  // roundings), so the largest depth over the tiles it touches bounds every depth the box can
+  // see.  0 there = only invalid pixels (:46); otherwise :49 as for the whole-frame maximum.
+  const int pxl = max(0, (int)floorf(__fadd_rd(fmaxf(umin, -0.5f), 0.5f)));
+  const int pxh = min(g.W - 1, (int)floorf(__fadd_ru(fminf(umax, g.w_lim), 0.5f)));
+  const int pyl = max(0, (int)floorf(__fadd_rd(fmaxf(vmin, -0.5f), 0.5f)));
+  const int pyh = min(g.H - 1, (int)floorf(__fadd_ru(fminf(vmax, g.h_lim), 0.5f)));
+  const int tw0 = tiles_across(g.W, kTile0Log2), th0 = tiles_across(g.H, kTile0Log2);
+  const int* tiles = tail + kTailHeadWords;
+  int sh = kTile0Log2, tw = tw0;
+  if ((pxh >> sh) - (pxl >> sh) > 2 || (pyh >> sh) - (pyl >> sh) > 2) {
+    tiles += tw0 * th0;
+    sh = kTile1Log2;
+    tw = tiles_across(g.W, kTile1Log2);
+    if ((pxh >> sh) - (pxl >> sh) > 2 || (pyh >> sh) - (pyl >> sh) > 2) return false;  // too wide: no local bound
+  }
+  int m = 0;
+  for (int ty = pyl >> sh; ty <= (pyh >> sh); ++ty)
+    for (int tx = pxl >> sh; tx <= (pxh >> sh); ++tx) m = max(m, __ldg(tiles + ty * tw + tx));
+  if (m == 0) return true;                                        // :46 nothing valid to hit
+  return __int_as_float(m) - zlo < -g.trunc;                      // :49 behind everything it can hit
 }
 
 // fast-axis terms of the camera transform of voxel index k (global on z), and their
@@ -289,11 +313,6 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   const int n_rows = g.n_mid * g.n_slow;
   const int row0 = blockIdx.x * rows_per_block;
   if (row0 >= n_rows) return;  // batched launches size the grid for the largest instance
-  float dmax[NF];                // largest depth of each frame (issued early: needed after the barrier)
-  if constexpr (CULL != 0) {
-#pragma unroll
-    for (int f = 0; f < NF; ++f) dmax[f] = __ldg(P.f[f].dmax);
-  }
 
   // ---- prologue 1: per-row terms of the camera transform -> shared memory ---------------
   for (int lr = threadIdx.x; lr < rows_per_block; lr += kThreads) {
@@ -364,7 +383,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           cam_coords<ZFAST>(ea, eb, p0, p1, p2, xa, ya, za);
           fast_terms<ZFAST>(P.f[f].c, bfb, p0, p1, p2);
           cam_coords<ZFAST>(ea, eb, p0, p1, p2, xb, yb, zb);
-          skip = skip && box_is_skipped(P.f[f], g, xa, ya, za, xb, yb, zb, dmax[f]);
+          skip = skip && box_is_skipped(P.f[f], g, xa, ya, za, xb, yb, zb, reinterpret_cast<const int*>(P.f[f].dmax));
         }
       }
       const unsigned b = __ballot_sync(0xffffffffu, skip);
