@@ -44,6 +44,7 @@ __device__ __forceinline__ void prefetch_line(const float* p, int mode) {
 template <int VEC>
 __device__ __forceinline__ void load_vec(const float* p, float (&v)[VEC]) {
   if constexpr (VEC == 4) {
+    // (plain loads/stores: the streaming .cs hints measured 0.6 % slower on the dense frame)
     float4 t = *reinterpret_cast<const float4*>(p);
     v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
   } else {

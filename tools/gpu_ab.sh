@@ -1,14 +1,11 @@
 #!/bin/bash
-# A/B on one box: previous build (tools/ab/libtsdf_prev.so) vs the current one, interleaved.
+# Round-robin A/B of kernel variants on one GPU box (see tools/variants.py for the variant bits).
+# usage: bash tools/gpu_ab.sh <tag> "<variants>" ["<scene> <dim>" ...]   then GPU parity tests
 O=gpurun_out/${1:-ab}; mkdir -p $O
-timeout 600 python -m pytest tests -m gpu -x -q --timeout 120 > $O/pytest.log 2>&1; echo "pytest rc=$?"; tail -5 $O/pytest.log
-for rep in 1 2; do
-  for a in "full 1024" "full 512"; do
-    [ -f tools/ab/libtsdf_prev.so ] && TSDF_B200_LIB=$PWD/tools/ab/libtsdf_prev.so timeout 300 python tools/variants.py $a 0 2>&1 | tail -1 | sed 's/^/prev /' | tee -a $O/variants.jsonl
-    timeout 300 python tools/variants.py $a 0 128 64 2>&1 | tail -1 | sed 's/^/cur  /' | tee -a $O/variants.jsonl
-  done
+V=${2:-"0 128 64"}
+shift; shift
+[ $# -eq 0 ] && set -- "full 512" "real 512" "kitti 1024"
+for a in "$@"; do
+  timeout 300 python tools/variants.py $a $V 2>&1 | tail -1 | tee -a $O/variants.jsonl
 done
-for a in "real 512" "kitti 1024"; do
-  [ -f tools/ab/libtsdf_prev.so ] && TSDF_B200_LIB=$PWD/tools/ab/libtsdf_prev.so timeout 300 python tools/variants.py $a 0 2>&1 | tail -1 | sed 's/^/prev /' | tee -a $O/variants.jsonl
-  timeout 300 python tools/variants.py $a 0 128 64 2>&1 | tail -1 | sed 's/^/cur  /' | tee -a $O/variants.jsonl
-done
+timeout 600 python -m pytest tests -m gpu -x -q --timeout 120 2>&1 | tail -3
