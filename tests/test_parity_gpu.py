@@ -416,3 +416,56 @@ def test_full_size_properties_c1(pkg, synth):
             assert np.array_equal(idx, np.flatnonzero(sel))
             cc = c[idx].astype(np.int64)
             assert np.array_equal(rgb, np.stack([cc & 255, (cc >> 8) & 255, cc >> 16], 1).astype(np.uint8))
+
+
+def test_full_size_properties_c2(pkg, synth):
+    """BASELINE config 2 size (512^3, 1 cm, fr3_office keyframe poses) through size-independent
+    properties: k frames fused into one pass == k single passes (bit for bit, all three arrays),
+    the segment cull never changes a result, and N_written adds up."""
+    dims, vs = (512, 512, 512), 0.01
+    poses = synth.load_pose_fixture()[::24]
+    origin, frames = synth.s_real(dims, vs, n_frames=8, poses=poses)
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+    with pkg.Volume(cfg) as vol:
+        total = 0
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T)
+            total += vol.stats().voxels_written
+        seq = vol.download()
+        n_seq = vol.extract_count(PRED_ABS_LT, 0.5, 1.5)
+        vol.reset()
+        vol.integrate_multi([f[0] for f in frames], [f[1] for f in frames], [f[2] for f in frames])
+        assert vol.stats().voxels_written == total
+        fused = vol.download()
+        vol.reset()
+        vol.set_variant(64)                       # cull off
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T, sync=False)
+        plain = vol.download()
+        assert vol.extract_count(PRED_ABS_LT, 0.5, 1.5) == n_seq
+    assert 0 < total < 8 * np.prod(dims)
+    for a, b, c in zip(seq, fused, plain):
+        assert np.array_equal(bits(a), bits(b)) and np.array_equal(bits(a), bits(c))
+
+
+def test_full_size_properties_c4(pkg, synth):
+    """BASELINE config 4 size (1024^3, the bench workload) without downloading 13 GB: S-full
+    writes every voxel every frame, so after k frames the extraction predicate
+    `weight > k - 0.5` selects all N voxels and `weight > k + 0.5` none; an 8-way z-slab of the
+    same grid writes exactly its share."""
+    dims, vs = (1024, 1024, 1024), 0.002
+    origin, frames = synth.s_full(dims, vs, n_frames=3)
+    n = int(np.prod(dims))
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+    with pkg.Volume(cfg) as vol:
+        for k, (d, rgb, T) in enumerate(frames, 1):
+            vol.integrate(d, rgb, T)
+            assert vol.stats().voxels_written == n
+            assert vol.extract_count(PRED_NONZERO, 0.0, k - 0.5) == n     # tsdf == 1 != 0 everywhere
+            assert vol.extract_count(PRED_NONZERO, 0.0, k + 0.5) == 0
+        assert vol.extract_count(PRED_ABS_LT, 1.0, 0.5) == 0              # |tsdf| < 1 nowhere: free space
+    zr = pkg.slab_range(dims[2], 8, 5)
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True, z_range=zr)
+    with pkg.Volume(cfg) as slab:
+        slab.integrate(*frames[0][:2], frames[0][2])
+        assert slab.stats().voxels_written == dims[0] * dims[1] * (zr[1] - zr[0]) == slab.n_local
