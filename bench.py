@@ -435,6 +435,32 @@ def extras(pkg, line, frames, origin):
                             "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts}
     except Exception as e:
         line["extra_c2"] = {"error": str(e)}
+    # The reference's own GPU kernel (lifted verbatim, nvcc defaults) on this box, as the bar to
+    # beat: its hard-coded 200^3 grid and the bench's 1024^3 grid, depth + weight only, against
+    # this library in the same semantics (class TSDF, no colour: 16 B per written voxel)
+    try:
+        from oracle.oracle import RefGpu, ref_available
+        if ref_available("gpu"):
+            out = {}
+            for dim in (200, 1024):
+                vs_r = 2.048 / dim
+                o_r, fr_r = synth.s_full((dim,) * 3, vs_r, n_frames=2)
+                trunc_r = np.float32(vs_r) * np.float32(5)
+                ref = RefGpu((dim,) * 3, synth.TUM3_HW, synth.TUM3_K)
+                ref.integrate(fr_r[0][2].reshape(16), fr_r[0][0], o_r, vs_r, trunc_r)
+                ms_ref = min(ref.integrate(fr_r[i % 2][2].reshape(16), fr_r[i % 2][0], o_r, vs_r, trunc_r) for i in range(3))
+                ref.close()
+                cfg = pkg.make_config((dim,) * 3, vs_r, o_r, semantics=pkg.SEM_TSDFCU, with_color=False, max_depth=1e9)
+                with pkg.Volume(cfg) as vr:
+                    vr.integrate(fr_r[0][0], None, fr_r[0][2])
+                    vr.bench_kernel(3)
+                    ms_own = min(vr.bench_kernel(5) for _ in range(3))
+                out[f"{dim}^3"] = {"reference_kernel_ms": ms_ref, "this_library_kernel_ms": ms_own,
+                                   "reference_Gvox_per_s": dim ** 3 / ms_ref / 1e6, "this_library_Gvox_per_s": dim ** 3 / ms_own / 1e6}
+            line["reference_gpu_kernel"] = {"what": "src/tsdf.cu:15-60 compiled by nvcc for sm_100a + its upload sequence (:161-167), "
+                                                    "S-full frame, depth+weight only; this library in class-TSDF semantics beside it", **out}
+    except Exception as e:
+        line["reference_gpu_kernel"] = {"error": str(e)}
     # C3: KITTI-shaped 1241x376 stereo-depth frames into the 1024x256x1024 outdoor grid (10 cm voxels,
     # max_depth 50 m), whole grid on this GPU (the 8-way z-slab version of it is a parity test)
     try:

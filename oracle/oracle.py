@@ -218,3 +218,47 @@ class RefLift:
         self.lib.ref_save_ply(path.encode(), int(dims[0]), int(dims[1]), int(dims[2]), np.float32(vs),
                               np.float32(origin[0]), np.float32(origin[1]), np.float32(origin[2]),
                               tsdf, weight, np.float32(tsdf_thresh), np.float32(weight_thresh))
+
+
+class RefGpu:
+    """The reference's own __global__ GpuIntegrate (src/tsdf.cu:15-60) compiled by nvcc for sm_100a
+    with nvcc's defaults (mul+add contracted to FMA, as the reference's CMake would build it) and
+    driven by the call sequence of src/tsdf.cu:161-167 (oracle/ref_gpu_epilogue.inc).  Checker and
+    "bar to beat" only; needs dim_y <= 1024 (one thread per y, `<<<dim_z, dim_y>>>`)."""
+
+    def __init__(self, dims, hw, K):
+        self.lib = C.CDLL(os.path.join(HERE, "_ref", "libtsdf_ref_gpu.so"))
+        L = self.lib
+        L.ref_gpu_create.restype = C.c_void_p
+        L.ref_gpu_create.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _f32p]
+        L.ref_gpu_integrate.restype = C.c_float
+        L.ref_gpu_integrate.argtypes = [C.c_void_p, _f32p, _f32p, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float]
+        L.ref_gpu_download.restype = C.c_int
+        L.ref_gpu_download.argtypes = [C.c_void_p, _f32p, _f32p]
+        L.ref_gpu_destroy.argtypes = [C.c_void_p]
+        assert dims[1] <= 1024
+        self.dims = tuple(int(d) for d in dims)
+        self.h = L.ref_gpu_create(self.dims[0], self.dims[1], self.dims[2], int(hw[0]), int(hw[1]),
+                                  np.ascontiguousarray(K, np.float32).reshape(9))
+        if not self.h:
+            raise RuntimeError("ref_gpu_create failed (no device / out of memory)")
+
+    def integrate(self, cam2base, depth, origin, vs, trunc):
+        """Returns the CUDA-event ms of the reference's upload + launch."""
+        ms = self.lib.ref_gpu_integrate(self.h, np.ascontiguousarray(cam2base, np.float32).reshape(16),
+                                        np.ascontiguousarray(depth, np.float32).reshape(-1), np.float32(origin[0]),
+                                        np.float32(origin[1]), np.float32(origin[2]), np.float32(vs), np.float32(trunc))
+        if ms < 0:
+            raise RuntimeError("reference kernel failed")
+        return float(ms)
+
+    def download(self):
+        n = int(np.prod(self.dims))
+        t, w = np.empty(n, np.float32), np.empty(n, np.float32)
+        assert self.lib.ref_gpu_download(self.h, t, w) == 0
+        return t, w
+
+    def close(self):
+        if self.h:
+            self.lib.ref_gpu_destroy(self.h)
+            self.h = None
