@@ -370,7 +370,9 @@ def run_b200(args, rank, world, local_rank):
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": workload_config(world),
+                "config": dict(workload_config(world), frame_distribution=(
+                    "none (1 GPU)" if sv is None else "peer-pull fused into the prep kernel (NVLink, cudaIpc)"
+                    if sv.peer_pull() else "ncclBroadcast")),
                 "frames_per_sec": args.steps / (ms * 1e-3),
                 "coverage": written_total / n_total,
                 "clocks": clocks,

@@ -228,14 +228,20 @@ int tsdf_comm_destroy(tsdf_comm* c);
 /* Slab of `rank` out of `nranks` for a grid with dim_z slices: contiguous,
  * sizes differ by at most one 4-slice group (keeps 128-bit alignment).      */
 void tsdf_slab_range(int dim_z, int nranks, int rank, int* z_begin, int* z_end);
-/* Collective over all ranks of `c`: the root's images (depth, rgb; ignored elsewhere, may be
- * NULL there) are broadcast over NVLink into every rank's frame slot (one grouped NCCL
- * launch), then every rank integrates its own slab.  The ~100 bytes of metadata (K, T_wc,
+/* Collective over all ranks of `c` (SPMD: every rank makes the same sequence of calls on its
+ * handle): the root's images (depth, rgb; ignored elsewhere, may be NULL there) reach every
+ * rank over NVLink — by peer-pull fused into the prep kernel, else by a grouped ncclBroadcast
+ * into every rank's frame slot — then every rank integrates its own slab.  The ~100 bytes of metadata (K, T_wc,
  * obs_weight) travel on the caller's control plane: pass the SAME values on every rank.
  * Colour is broadcast iff the volume was created with_color (then the root must pass rgb). */
 int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float* depth,
                                const uint8_t* rgb, const float* K, const float* T_wc,
                                float obs_weight);
+/* *active = 1 when frames are distributed by peer-pull (every non-root rank's prep kernel reads
+ * the root's raw frame slot through NVLink, cudaIpc-mapped; set up by the first
+ * tsdf_integrate_bcast_async call), 0 when ncclBroadcast is used (fallback, or
+ * TSDF_B200_BCAST=nccl in the environment).  Results are identical either way.           */
+int tsdf_comm_peer_pull(const tsdf_comm* c, int* active);
 /* Collective: every rank extracts its slab; the root receives all points,
  * merged to ascending GLOBAL reference index.  Non-root ranks pass NULL/0
  * buffers and get their LOCAL count in *count; the root gets the total.

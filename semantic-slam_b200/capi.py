@@ -83,6 +83,7 @@ SIGNATURES = {
     "tsdf_comm_unique_id": (_I, [_VP]),
     "tsdf_comm_create": (_I, [_VP, _I, _I, _I, C.POINTER(_VP)]),
     "tsdf_comm_destroy": (_I, [_VP]),
+    "tsdf_comm_peer_pull": (_I, [_VP, C.POINTER(_I)]),
     "tsdf_slab_range": (None, [_I, _I, _I, C.POINTER(_I), C.POINTER(_I)]),
     "tsdf_integrate_bcast_async": (_I, [_VP, _VP, _I, _VP, _VP, _VP, _VP, _F]),
     "tsdf_gather_points": (_I, [_VP, _VP, _I, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),

@@ -275,6 +275,8 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   return TSDF_OK;
 }
 
+int ensure_frame_slot(tsdf_vol* v, int index) { return ensure_slot(v, v->slot[index]); }
+
 enum PtrKind { PTR_PAGEABLE, PTR_PINNED, PTR_DEVICE };
 static PtrKind ptr_kind(const void* p) {
   cudaPointerAttributes a;
@@ -287,10 +289,16 @@ static PtrKind ptr_kind(const void* p) {
 // Moves `bytes` from src (any kind) to where the prep kernel can read it; returns the device
 // pointer to read from.  Pageable data goes through the slot's pinned buffer.
 static int to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
-                     const void** d_out) {
+                     const void** d_out, bool into_slot = false) {
   PtrKind k = ptr_kind(src);
-  if (k == PTR_DEVICE) { *d_out = src; return TSDF_OK; }
   char* dst = reinterpret_cast<char*>(s.d_raw) + raw_off;
+  if (k == PTR_DEVICE) {
+    if (!into_slot) { *d_out = src; return TSDF_OK; }
+    // peers read the frame from this slot's raw buffer: device inputs are copied into it
+    CU_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToDevice, v->s_copy));
+    *d_out = dst;
+    return TSDF_OK;
+  }
   if (k == PTR_PAGEABLE) {
     if (!s.h_pinned) CU_CHECK(cudaHostAlloc(&s.h_pinned, frame_pixels(v->cfg) * 7 + 64, cudaHostAllocDefault));
     char* stage = reinterpret_cast<char*>(s.h_pinned) + raw_off;
@@ -768,7 +776,7 @@ extern "C" int tsdf_memcpy_d2h(int device, void* dst, const void* src, size_t by
 // buffer; bcast_finish preps the slot and launches the integrate.
 int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rgb, bool color,
                 FrameSlot** slot, void** d_depth, void** d_rgb, const void** send_depth,
-                const void** send_rgb) {
+                const void** send_rgb, bool into_slot) {
   FrameSlot& s = v->slot[v->seq % 3];
   int rc = ensure_slot(v, s);
   if (rc) return rc;
@@ -783,10 +791,10 @@ int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rg
   *send_depth = *d_depth;
   *send_rgb = *d_rgb;
   if (is_root) {
-    rc = to_device(v, s, depth, px * 4, 0, send_depth);   // device inputs are sent from where they are
+    rc = to_device(v, s, depth, px * 4, 0, send_depth, into_slot);   // device inputs are sent from where they are
     if (rc) return rc;
     if (color) {
-      rc = to_device(v, s, rgb, px * 3, rgb_off, send_rgb);
+      rc = to_device(v, s, rgb, px * 3, rgb_off, send_rgb, into_slot);
       if (rc) return rc;
     }
   }
@@ -795,14 +803,16 @@ int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rg
 }
 
 int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const float* T_wc,
-                 float obs_weight) {
+                 float obs_weight, const void* src_raw, int (*after_prep)(void*, cudaStream_t), void* after_arg) {
   const size_t px = frame_pixels(v->cfg);
   const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
-  int rc = launch_frame_prep(s->d_raw, TSDF_DEPTH_F32, 1.0f, 1, 1,
-                             color ? reinterpret_cast<const uint8_t*>(s->d_raw) + rgb_off : nullptr,
+  const void* raw = src_raw ? src_raw : s->d_raw;   // peer-pull: the root's raw slot through NVLink
+  int rc = launch_frame_prep(raw, TSDF_DEPTH_F32, 1.0f, 1, 1,
+                             color ? reinterpret_cast<const uint8_t*>(raw) + rgb_off : nullptr,
                              nullptr, v->cfg.im_h, v->cfg.im_w, v->cfg.max_depth, color, nullptr, s->d_frame,
                              v->s_copy);
   if (rc) return rc;
+  if (after_prep && (rc = after_prep(after_arg, v->s_copy))) return rc;
   CU_CHECK(cudaEventRecord(s->uploaded, v->s_copy));
   ++v->seq;
   FrameP fp;

@@ -82,10 +82,70 @@ int load_nccl() {
 
 }  // namespace
 
+// ---- peer-pull frame distribution (fused broadcast + prep) ------------------------------------
+// Instead of an NCCL broadcast followed by the prep kernel, every non-root rank's prep kernel
+// reads the root's raw frame slot directly through NVLink (cudaIpc-mapped peer memory) and
+// writes its own prepared frame: one kernel does the transfer and the conversion, and no NCCL
+// CTAs spin on the SMs the integrate kernel is using.  Ordering is by two kinds of sequence
+// flags in the ROOT's memory: ready (root -> peers: "frame s is in its slot") and done[r]
+// (peer r -> root: "I have consumed frame s", so the slot may be overwritten three frames
+// later).  The waits are single-thread kernels on the copy streams, bounded by a timeout that
+// raises an error flag instead of hanging.
+namespace {
+constexpr int kFlagWords = 64;          // [0] ready, [8 + r] done of rank r
+constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;
+
+__device__ __forceinline__ unsigned ld_flag(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.volatile.global.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ unsigned long long now_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+// waits until *flag >= target (sequence numbers; target <= 0 passes at once)
+__global__ void k_wait_flag(const unsigned* flag, int target, int* err) {
+  if (target <= 0) return;
+  const unsigned long long t0 = now_ns();
+  while ((int)ld_flag(flag) < target) {
+    __nanosleep(200);
+    if (now_ns() - t0 > kWaitTimeoutNs) { *err = 1; __threadfence_system(); return; }
+  }
+}
+// waits until every done[r] >= target, r != root
+__global__ void k_wait_all(const unsigned* done, int nranks, int root, int target, int* err) {
+  const int r = threadIdx.x;
+  if (target <= 0 || r >= nranks || r == root) return;
+  const unsigned long long t0 = now_ns();
+  while ((int)ld_flag(done + r) < target) {
+    __nanosleep(200);
+    if (now_ns() - t0 > kWaitTimeoutNs) { *err = 2; __threadfence_system(); return; }
+  }
+}
+__global__ void k_set_flag(unsigned* flag, unsigned value) {
+  __threadfence_system();   // everything this stream did before (frame bytes / prep reads) is complete
+  asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(flag), "r"(value));
+  __threadfence_system();
+}
+}  // namespace
+
 struct tsdf_comm {
   ncclComm_t comm = nullptr;
   int nranks = 1, rank = 0, device = 0;
   int64_t* d_counts = nullptr;  // nranks entries
+  // peer-pull state
+  bool p2p_tried = false, p2p_ok = false;
+  int p2p_root = -1;
+  tsdf_vol* p2p_vol = nullptr;     // the volume whose raw frame slots are exported / imported
+  unsigned* d_flags = nullptr;     // this rank's flag words (only the root's are used)
+  void* d_handles = nullptr;       // 4 cudaIpcMemHandle_t staged for the one-time exchange
+  void* peer_raw[3] = {nullptr, nullptr, nullptr};  // root's raw slots (non-root ranks)
+  unsigned* peer_flags = nullptr;  // root's flag words (non-root ranks)
+  int* h_err = nullptr;            // pinned, device-visible: set by a wait kernel on timeout
+  int* hd_err = nullptr;
+  int bseq = 0;                    // frames distributed so far (same on every rank)
 };
 
 static_assert(sizeof(ncclUniqueId) == 128, "uid128 contract");
@@ -134,12 +194,17 @@ extern "C" int tsdf_comm_create(const void* uid128, int nranks, int rank, int de
     delete c;
     return TSDF_E_NCCL;
   }
-  if (cudaMalloc(&c->d_counts, sizeof(int64_t) * (size_t)nranks) != cudaSuccess) {
+  if (cudaMalloc(&c->d_flags, kFlagWords * 4) != cudaSuccess || cudaMemset(c->d_flags, 0, kFlagWords * 4) != cudaSuccess ||
+      cudaMalloc(&c->d_handles, 4 * sizeof(cudaIpcMemHandle_t)) != cudaSuccess ||
+      cudaHostAlloc(&c->h_err, sizeof(int), cudaHostAllocMapped | cudaHostAllocPortable) != cudaSuccess ||
+      cudaHostGetDevicePointer(reinterpret_cast<void**>(&c->hd_err), c->h_err, 0) != cudaSuccess ||
+      cudaMalloc(&c->d_counts, sizeof(int64_t) * (size_t)nranks) != cudaSuccess) {
     g_nccl.CommDestroy(c->comm);
     delete c;
     tsdf_set_error("tsdf_comm_create: device allocation failed");
     return TSDF_E_NOMEM;
   }
+  *c->h_err = 0;
   *out = c;
   return TSDF_OK;
 }
@@ -147,18 +212,90 @@ extern "C" int tsdf_comm_create(const void* uid128, int nranks, int rank, int de
 extern "C" int tsdf_comm_destroy(tsdf_comm* c) {
   if (!c) return TSDF_OK;
   DeviceGuard g(c->device);
+  cudaDeviceSynchronize();   // our use of the peers' memory is over
+  for (void* p : c->peer_raw) if (p) cudaIpcCloseMemHandle(p);
+  if (c->peer_flags) cudaIpcCloseMemHandle(c->peer_flags);
+  if (c->p2p_ok && c->comm && c->p2p_vol) {
+    // every rank agreed on p2p_ok, so every rank gets here: a barrier (tiny all-gather) keeps the
+    // root from freeing its exported slots before the importers have closed their mappings
+    cudaStream_t st = nullptr;
+    if (g_nccl.AllGather(c->d_counts + c->rank, c->d_counts, 1, ncclInt64, c->comm, st) == ncclSuccess)
+      cudaStreamSynchronize(st);
+  }
+  cudaFree(c->d_flags); cudaFree(c->d_handles);
+  if (c->h_err) cudaFreeHost(c->h_err);
   cudaFree(c->d_counts);
   if (c->comm) g_nccl.CommDestroy(c->comm);
   delete c;
   return TSDF_OK;
 }
 
+extern "C" int tsdf_comm_peer_pull(const tsdf_comm* c, int* active) {
+  REQUIRE(c && active, "null argument");
+  *active = c->p2p_ok ? 1 : 0;
+  return TSDF_OK;
+}
+
 // defined in api.cu
 int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rgb, bool color,
                 FrameSlot** slot, void** d_depth, void** d_rgb, const void** send_depth,
-                const void** send_rgb);
+                const void** send_rgb, bool into_slot);
 int bcast_finish(tsdf_vol* v, FrameSlot* slot, bool color, const float* K, const float* T_wc,
-                 float obs_weight);
+                 float obs_weight, const void* src_raw, int (*after_prep)(void*, cudaStream_t), void* after_arg);
+int ensure_frame_slot(tsdf_vol* v, int index);
+
+// One-time collective: export the root's three raw frame slots and its flag words with cudaIpc,
+// ship the handles with one ncclBroadcast, open them on the other ranks, and agree (all-gather
+// of a status word) whether every rank succeeded.  Any failure leaves the NCCL path in place.
+static int p2p_setup(tsdf_vol* v, tsdf_comm* c, int root) {
+  c->p2p_tried = true;
+  const char* mode = getenv("TSDF_B200_BCAST");
+  bool ok = !(mode && strcmp(mode, "nccl") == 0) && c->nranks > 1;
+  for (int k = 0; k < 3 && ok; ++k) ok = ensure_frame_slot(v, k) == TSDF_OK;
+  cudaIpcMemHandle_t hs[4];
+  memset(hs, 0, sizeof hs);
+  if (ok && c->rank == root) {
+    for (int k = 0; k < 3 && ok; ++k) ok = cudaIpcGetMemHandle(&hs[k], v->slot[k].d_raw) == cudaSuccess;
+    ok = ok && cudaIpcGetMemHandle(&hs[3], c->d_flags) == cudaSuccess;
+    cudaGetLastError();
+  }
+  if (c->rank == root) CU_CHECK(cudaMemcpyAsync(c->d_handles, hs, sizeof hs, cudaMemcpyHostToDevice, v->s_copy));
+  NCCL_CHECK(g_nccl.Broadcast(c->d_handles, c->d_handles, sizeof hs, ncclUint8, root, c->comm, v->s_copy));
+  CU_CHECK(cudaMemcpyAsync(hs, c->d_handles, sizeof hs, cudaMemcpyDeviceToHost, v->s_copy));
+  CU_CHECK(cudaStreamSynchronize(v->s_copy));
+  if (ok && c->rank != root) {
+    void* p = nullptr;
+    for (int k = 0; k < 3 && ok; ++k) {
+      ok = cudaIpcOpenMemHandle(&p, hs[k], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      if (ok) c->peer_raw[k] = p;
+    }
+    if (ok) {
+      ok = cudaIpcOpenMemHandle(&p, hs[3], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+      if (ok) c->peer_flags = reinterpret_cast<unsigned*>(p);
+    }
+    cudaGetLastError();
+  }
+  // agreement: every rank must have succeeded (the root's handles are all-zero if it failed)
+  int64_t mine = ok ? 1 : 0;
+  CU_CHECK(cudaMemcpyAsync(c->d_counts + c->rank, &mine, 8, cudaMemcpyHostToDevice, v->s_copy));
+  NCCL_CHECK(g_nccl.AllGather(c->d_counts + c->rank, c->d_counts, 1, ncclInt64, c->comm, v->s_copy));
+  std::vector<int64_t> all((size_t)c->nranks, 0);
+  CU_CHECK(cudaMemcpyAsync(all.data(), c->d_counts, 8 * (size_t)c->nranks, cudaMemcpyDeviceToHost, v->s_copy));
+  CU_CHECK(cudaStreamSynchronize(v->s_copy));
+  bool all_ok = true;
+  for (int64_t a : all) all_ok = all_ok && a == 1;
+  c->p2p_ok = all_ok;
+  c->p2p_root = root;
+  c->p2p_vol = v;
+  return TSDF_OK;
+}
+
+static int set_done_flag(void* arg, cudaStream_t st) {   // after_prep hook of a non-root rank
+  tsdf_comm* c = static_cast<tsdf_comm*>(arg);
+  k_set_flag<<<1, 1, 0, st>>>(c->peer_flags + 8 + c->rank, (unsigned)c->bseq);
+  CU_CHECK(cudaGetLastError());
+  return TSDF_OK;
+}
 
 extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float* depth,
                                           const uint8_t* rgb, const float* K, const float* T_wc,
@@ -174,7 +311,33 @@ extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, c
   FrameSlot* slot = nullptr;
   void *d_depth = nullptr, *d_rgb = nullptr;
   const void *s_depth = nullptr, *s_rgb = nullptr;
-  int rc = bcast_stage(v, is_root, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb);
+  int rc;
+  if (!c->p2p_tried && c->nranks > 1 && (rc = p2p_setup(v, c, root))) return rc;
+  if (*c->h_err) {
+    tsdf_set_error("peer-pull frame distribution: flag wait timed out (code %d): a rank is gone or stalled", *c->h_err);
+    return TSDF_E_NCCL;
+  }
+  if (c->p2p_ok && root == c->p2p_root && v == c->p2p_vol) {
+    // ---- peer-pull: fused broadcast + prep (see the comment at k_wait_flag) ----------------
+    const int seq = ++c->bseq;
+    const int k = (int)(v->seq % 3);   // the slot bcast_stage picks; the same on every rank (SPMD)
+    if (is_root) {
+      // slot k last held frame seq-3: wait until every peer has consumed it, then overwrite
+      k_wait_all<<<1, 32, 0, v->s_copy>>>(c->d_flags + 8, c->nranks, root, seq - 3, c->hd_err);
+      CU_CHECK(cudaGetLastError());
+      rc = bcast_stage(v, true, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, true);
+      if (rc) return rc;
+      k_set_flag<<<1, 1, 0, v->s_copy>>>(c->d_flags, (unsigned)seq);   // ready: frame seq is in slot k
+      CU_CHECK(cudaGetLastError());
+      return bcast_finish(v, slot, color, K, T_wc, obs_weight, nullptr, nullptr, nullptr);
+    }
+    rc = bcast_stage(v, false, nullptr, nullptr, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, false);
+    if (rc) return rc;
+    k_wait_flag<<<1, 1, 0, v->s_copy>>>(c->peer_flags, seq, c->hd_err);
+    CU_CHECK(cudaGetLastError());
+    return bcast_finish(v, slot, color, K, T_wc, obs_weight, c->peer_raw[k], set_done_flag, c);
+  }
+  rc = bcast_stage(v, is_root, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, false);
   if (rc) return rc;
   const size_t px = frame_pixels(v->cfg);
   if (c->nranks > 1) {
@@ -186,7 +349,7 @@ extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, c
     if (s_depth != d_depth) CU_CHECK(cudaMemcpyAsync(d_depth, s_depth, px * 4, cudaMemcpyDeviceToDevice, v->s_copy));
     if (color && s_rgb != d_rgb) CU_CHECK(cudaMemcpyAsync(d_rgb, s_rgb, px * 3, cudaMemcpyDeviceToDevice, v->s_copy));
   }
-  return bcast_finish(v, slot, color, K, T_wc, obs_weight);
+  return bcast_finish(v, slot, color, K, T_wc, obs_weight, nullptr, nullptr, nullptr);
 }
 
 extern "C" int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predicate, float tsdf_thresh,

@@ -81,6 +81,12 @@ class ShardedVolume:
         check(self.lib.tsdf_integrate_bcast_async(self.vol.h, self.comm, root, ptr(depth), ptr(rgb),
                                                   ptr(Kc), ptr(T), np.float32(obs_weight)))
 
+    def peer_pull(self):
+        """True when frames are distributed by the fused peer-pull prep (else ncclBroadcast)."""
+        a = C.c_int(0)
+        check(self.lib.tsdf_comm_peer_pull(self.comm, C.byref(a)))
+        return bool(a.value)
+
     def sync(self):
         self.vol.sync()
         self._keep.clear()

@@ -37,6 +37,9 @@ def main():
             else:
                 sv.integrate_bcast(None, None, T)
         sv.sync()
+        want_nccl = os.environ.get("TSDF_B200_BCAST") == "nccl"
+        assert not (want_nccl and sv.peer_pull())
+        mode = "peer-pull" if sv.peer_pull() else "nccl"
         gt, gw, gc = sv.vol.download()
         p = o.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, sem, zr)
         t, w, c = o.new_volume(p, color)
@@ -61,7 +64,7 @@ def main():
         dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
-        print("dist_worker ok", world)
+        print("dist_worker ok", world, mode)
 
 
 if __name__ == "__main__":
