@@ -575,20 +575,23 @@ __global__ void k_publish(unsigned long long* __restrict__ written, unsigned lon
   *written = 0ull;
 }
 
-int g_prefetch_mode = 1;  // 0 off, 1 L2, 2 L1 (set per launch from the handle's variant bits)
-int g_cull = 1;           // 0: dense kernel, 1: segment cull + staged probe (chosen per launch), 2: legacy dense
-int g_rows_mult = 16;
+// Per-launch choices (no global state: handles may be driven from different host threads).
+struct LaunchOpts {
+  int prefetch = 1;    // 0 off, 1 L2, 2 L1 (legacy kernel only)
+  int kernel = 1;      // 0: dense kernel, 1: segment cull + staged probe, 2: legacy dense (A/B only)
+  int rows_mult = 16;  // row iterations per thread
+};
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
 
-Geometry plan(int n_fast, int n_rows, int vec, int nz) {
+Geometry plan(int n_fast, int n_rows, int vec, int nz, int rows_mult = 16) {
   Geometry q;
   int vec_per_row = (n_fast + vec - 1) / vec;
   q.tpr_log2 = 0;
   while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < kThreads) ++q.tpr_log2;
   int tpr = 1 << q.tpr_log2;
   int rp = kThreads / tpr;
-  q.rows_per_block = rp * g_rows_mult;
+  q.rows_per_block = rp * rows_mult;
   if (q.rows_per_block > kMaxRowsPerBlock) q.rows_per_block = kMaxRowsPerBlock;
   if (q.rows_per_block < rp) q.rows_per_block = rp;
   q.grid = dim3((n_rows + q.rows_per_block - 1) / q.rows_per_block, (vec_per_row + tpr - 1) / tpr, nz);
@@ -596,14 +599,14 @@ Geometry plan(int n_fast, int n_rows, int vec, int nz) {
 }
 
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
-int launch_t(const GridP& g, const FrameP* frames, cudaStream_t st) {
-  const int pf = g_prefetch_mode;
+int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
+  const int pf = o.prefetch;
   LaunchP<NF> P;
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
-  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1);
-  if (g_cull == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
-  else if (g_cull == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult);
+  if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
@@ -611,19 +614,19 @@ int launch_t(const GridP& g, const FrameP* frames, cudaStream_t st) {
 
 // layout (and with it the truncation compare) x colour x integer-weight mode, for one NF/VEC/MATH
 template <int NF, int VEC, int MATH>
-int launch_sem(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, cudaStream_t st) {
+int launch_sem(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, const LaunchOpts& o, cudaStream_t st) {
   if (zfast) {
     if (color) {
-      if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<true, true, false, NF, VEC, MATH, 1>(g, fr, st); }
-      return launch_t<true, true, false, NF, VEC, MATH, 0>(g, fr, st);
+      if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<true, true, false, NF, VEC, MATH, 1>(g, fr, o, st); }
+      return launch_t<true, true, false, NF, VEC, MATH, 0>(g, fr, o, st);
     }
-    return launch_t<true, false, false, NF, VEC, MATH, 0>(g, fr, st);
+    return launch_t<true, false, false, NF, VEC, MATH, 0>(g, fr, o, st);
   }
   if (color) {
-    if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<false, true, true, NF, VEC, MATH, 1>(g, fr, st); }
-    return launch_t<false, true, true, NF, VEC, MATH, 0>(g, fr, st);
+    if constexpr (MATH == MATH_EXACT) { if (wmode == 1) return launch_t<false, true, true, NF, VEC, MATH, 1>(g, fr, o, st); }
+    return launch_t<false, true, true, NF, VEC, MATH, 0>(g, fr, o, st);
   }
-  return launch_t<false, false, true, NF, VEC, MATH, 0>(g, fr, st);
+  return launch_t<false, false, true, NF, VEC, MATH, 0>(g, fr, o, st);
 }
 
 }  // namespace
@@ -687,30 +690,31 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   // A/B knobs (tsdf_set_variant): bit0 literal math; bits1-2 prefetch 1=L2 2=L1 (default L2);
   // bit5 prefetch off; bits3-4 rows per block x64 / x32 (default x16); bit6/bit7 segment cull off/on;
   // bits8-9 rows per block x8 / x4
-  g_prefetch_mode = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
-  g_rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
+  LaunchOpts o;
+  o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
+  o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
   // projects inside every frame's image (then no segment can be culled by the frustum and the
   // plain kernel is ~2-5 % faster); a pure performance choice, results are identical
-  g_cull = (v->variant & 1024) ? 2 /* legacy dense kernel, A/B only */
+  o.kernel = (v->variant & 1024) ? 2 /* legacy dense kernel, A/B only */
          : (v->variant & 64) ? 0 : ((v->variant & 128) ? 1 : (slab_inside_every_frustum(g, frames, nf) ? 0 : 1));
   const int wmode = (color && v->wmode_ok) ? 1 : 0;
   if (literal || !vec4 || !(nf == 1 || nf == 2 || nf == 4 || nf == 8)) {
     for (int i = 0; i < nf; ++i) {
       int rc;
-      if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, st)
-                             : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, st);
-      else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, st)
-                             : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, st);
+      if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o, st)
+                             : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o, st);
+      else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o, st)
+                             : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o, st);
       if (rc) return rc;
     }
     return TSDF_OK;
   }
   switch (nf) {
-    case 1: return launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
-    case 2: return launch_sem<2, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
-    case 4: return launch_sem<4, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
-    default: return launch_sem<8, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, st);
+    case 1: return launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, o, st);
+    case 2: return launch_sem<2, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, o, st);
+    case 4: return launch_sem<4, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, o, st);
+    default: return launch_sem<8, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames, o, st);
   }
 }
 
@@ -719,7 +723,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st) {
   Geometry q = plan(max_fast, max_rows, vec4 ? 4 : 1, n_active);
-#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, g_prefetch_mode)
+#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, 1 /* L2 prefetch */)
   if (zfast) {
     if (color) { if (wmode == 1) { if (vec4) LB(true, true, false, 4, 1); else LB(true, true, false, 1, 1); }
                  else            { if (vec4) LB(true, true, false, 4, 0); else LB(true, true, false, 1, 0); } }
