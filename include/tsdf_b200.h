@@ -145,10 +145,13 @@ int tsdf_integrate_async(tsdf_vol* v, const float* depth, const uint8_t* rgb,
 int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int depth_fmt, float depth_scale,
                              int subsample_cols, int subsample_rows, const uint8_t* rgb,
                              const float* K, const float* T_wc, float obs_weight);
-/* k frames fused into ONE pass over the volume: voxel state is
- * read once, updated k times in frame order in registers, written once.
- * Results are bit-identical to k successive tsdf_integrate calls.
- * depth: k*H*W, rgb: k*H*W*3 or NULL, K: 9 or NULL, T_wc: k*16.             */
+/* k frames in one call (the off-line keyframe replay of
+ * examples/label_instance_rgbd.cpp:79-110): the frames are staged as a group (uploads of the
+ * whole group overlap the integration of the previous one) and integrated in frame order;
+ * results are bit-identical to k successive tsdf_integrate calls.  A single fused pass over
+ * the volume for all k frames was built and measured slower than k passes on B200 (the
+ * per-voxel arithmetic, not the HBM traffic, bounds it — DESIGN.md §4.1), so each frame is its
+ * own launch.  depth: k*H*W, rgb: k*H*W*3 or NULL, K: 9 or NULL, T_wc: k*16.   */
 int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth, const uint8_t* rgb,
                                const float* K, const float* T_wc, float obs_weight);
 int tsdf_sync(tsdf_vol* v);
