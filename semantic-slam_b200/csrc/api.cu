@@ -356,6 +356,7 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
   out->fx = k[0]; out->cx = k[2]; out->fy = k[4]; out->cy = k[5];
   out->obs_weight = obs_weight;
   out->pad_ = 0;
+  out->mb_x0 = 0; out->mb_y0 = 0; out->mb_x1 = v->cfg.im_w - 1; out->mb_y1 = v->cfg.im_h - 1;
   out->img = d_frame;
   out->dmax = frame_dmax_ptr(d_frame, frame_pixels(v->cfg));
   return TSDF_OK;

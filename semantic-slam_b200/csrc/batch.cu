@@ -186,6 +186,10 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
     make_frame_params(v, K, T_wc, obs_weight, slot->d_frame, &d.f);
     wmode = account_weights(v, &d.f, 1) && wmode;
     d.mask = d_masks ? d_masks + px * (size_t)i : nullptr;
+    if (boxes) {  // outside its box the instance's mask is 0: segments that cannot project into it are culled
+      const int32_t* q = boxes + 4 * i;
+      d.f.mb_x0 = q[0]; d.f.mb_y0 = q[1]; d.f.mb_x1 = q[0] + q[2] - 1; d.f.mb_y1 = q[1] + q[3] - 1;
+    }
     max_fast = d.g.n_fast > max_fast ? d.g.n_fast : max_fast;
     int rows = d.g.n_mid * d.g.n_slow;
     max_rows = rows > max_rows ? rows : max_rows;

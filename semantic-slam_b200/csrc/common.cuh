@@ -48,6 +48,8 @@ struct FrameP {       // one camera frame
   float fx, cx, fy, cy;  // K[0],K[2],K[4],K[5], src/tsdf.cu:41-42
   float obs_weight;
   int pad_;
+  int mb_x0, mb_y0, mb_x1, mb_y1;  // pixel rectangle (inclusive) outside which the frame is known to be
+                                   // invalid for this launch: the instance's mask box, else the image
   const void* img;    // prepared frame: float depth[H*W]  or  float4 {depth, c0, c1, c2}[H*W]
   const float* dmax;  // largest depth of the prepared frame (+inf when it holds a NaN)
 };

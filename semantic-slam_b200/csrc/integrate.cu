@@ -237,6 +237,8 @@ __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, 
   const int pxh = min(g.W - 1, (int)floorf(__fadd_ru(fminf(umax, g.w_lim), 0.5f)));
   const int pyl = max(0, (int)floorf(__fadd_rd(fmaxf(vmin, -0.5f), 0.5f)));
   const int pyh = min(g.H - 1, (int)floorf(__fadd_ru(fminf(vmax, g.h_lim), 0.5f)));
+  // (batched instances: the mask is 0 outside the instance's box, i.e. depth * 0 = invalid, :46)
+  if (pxh < f.mb_x0 || pxl > f.mb_x1 || pyh < f.mb_y0 || pyl > f.mb_y1) return true;
   const int tw0 = tiles_across(g.W, kTile0Log2), th0 = tiles_across(g.H, kTile0Log2);
   const int* tiles = tail + kTailHeadWords;
   int sh = kTile0Log2, tw = tw0;
