@@ -368,29 +368,52 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     const int ka = (blockIdx.y * tpr + (tf & ~31)) * VEC;
     int kb = ka + tw * VEC - 1;
     if (kb > g.n_fast - 1) kb = g.n_fast - 1;
-    const float bfa = fast_coord<ZFAST>(g, ka), bfb = fast_coord<ZFAST>(g, kb);
-    for (int pass = 0; (pass << tw_log2) < n_iter; ++pass) {
-      const int it = (pass << tw_log2) + kk;
+    // box test of fast-axis voxels [a, b] of local row lr against every frame
+    auto seg_skipped = [&](int lr, int a, int b) {
+      const float bfa = fast_coord<ZFAST>(g, a), bfb = fast_coord<ZFAST>(g, b);
+      bool skip = true;
+#pragma unroll
+      for (int f = 0; f < NF; ++f) {
+        const float4* e = tab + (lr * NF + f) * NT;
+        const float4 ea = e[0];
+        float4 eb = ea;
+        if constexpr (!ZFAST) eb = e[1];
+        float p0, p1, p2, xa, ya, za, xb, yb, zb;
+        fast_terms<ZFAST>(P.f[f].c, bfa, p0, p1, p2);
+        cam_coords<ZFAST>(ea, eb, p0, p1, p2, xa, ya, za);
+        fast_terms<ZFAST>(P.f[f].c, bfb, p0, p1, p2);
+        cam_coords<ZFAST>(ea, eb, p0, p1, p2, xb, yb, zb);
+        skip = skip && box_is_skipped(P.f[f], g, xa, ya, za, xb, yb, zb, reinterpret_cast<const int*>(P.f[f].dmax));
+      }
+      return skip;
+    };
+    if (tw == 32 && n_iter <= 16) {
+      // Usual case (one segment per warp, <= 16 rows per thread): all 32 lanes work — lane L
+      // tests two quarter-segments (8 runs each) of row (L & 15), half (L >> 4); a row segment is
+      // culled iff its four quarter boxes are, which is tighter than one box around all of it.
+      const int it = lane & 15, half = lane >> 4;
       const int lr = tr + it * rp;
       bool skip = false;
       if (it < n_iter && row0 + lr < n_rows && ka <= kb) {
         skip = true;
+        const int qlen = 8 * VEC;
 #pragma unroll
-        for (int f = 0; f < NF; ++f) {
-          const float4* e = tab + (lr * NF + f) * NT;
-          const float4 ea = e[0];
-          float4 eb = ea;
-          if constexpr (!ZFAST) eb = e[1];
-          float p0, p1, p2, xa, ya, za, xb, yb, zb;
-          fast_terms<ZFAST>(P.f[f].c, bfa, p0, p1, p2);
-          cam_coords<ZFAST>(ea, eb, p0, p1, p2, xa, ya, za);
-          fast_terms<ZFAST>(P.f[f].c, bfb, p0, p1, p2);
-          cam_coords<ZFAST>(ea, eb, p0, p1, p2, xb, yb, zb);
-          skip = skip && box_is_skipped(P.f[f], g, xa, ya, za, xb, yb, zb, reinterpret_cast<const int*>(P.f[f].dmax));
+        for (int q = 0; q < 2; ++q) {
+          const int qa = ka + (2 * half + q) * qlen;
+          const int qb = qa + qlen - 1 < kb ? qa + qlen - 1 : kb;
+          if (qa <= kb) skip = skip && seg_skipped(lr, qa, qb);
         }
       }
       const unsigned b = __ballot_sync(0xffffffffu, skip);
-      rowmask |= (unsigned long long)((b >> gshift) & gmask) << (pass << tw_log2);
+      rowmask = (unsigned long long)(b & (b >> 16) & 0xffffu);
+    } else {
+      for (int pass = 0; (pass << tw_log2) < n_iter; ++pass) {
+        const int it = (pass << tw_log2) + kk;
+        const int lr = tr + it * rp;
+        const bool skip = it < n_iter && row0 + lr < n_rows && ka <= kb && seg_skipped(lr, ka, kb);
+        const unsigned b = __ballot_sync(0xffffffffu, skip);
+        rowmask |= (unsigned long long)((b >> gshift) & gmask) << (pass << tw_log2);
+      }
     }
   }
   if (f0 >= g.n_fast) return;  // (after the ballots: they need the whole warp)
