@@ -93,7 +93,9 @@ int load_nccl() {
 // raises an error flag instead of hanging.
 namespace {
 constexpr int kFlagWords = 64;          // [0] ready, [8 + r] done of rank r
-constexpr unsigned long long kWaitTimeoutNs = 4000000000ull;
+// a root that is slow to produce a frame (file IO, a stalled host) must not trip this; a rank that
+// died must not hang the others for ever.  TSDF_B200_PEER_TIMEOUT_MS overrides.
+unsigned long long g_wait_timeout_ns = 20000000000ull;
 
 __device__ __forceinline__ unsigned ld_flag(const unsigned* p) {
   unsigned v;
@@ -106,22 +108,22 @@ __device__ __forceinline__ unsigned long long now_ns() {
   return t;
 }
 // waits until *flag >= target (sequence numbers; target <= 0 passes at once)
-__global__ void k_wait_flag(const unsigned* flag, int target, int* err) {
+__global__ void k_wait_flag(const unsigned* flag, int target, int* err, unsigned long long timeout_ns) {
   if (target <= 0) return;
   const unsigned long long t0 = now_ns();
   while ((int)ld_flag(flag) < target) {
     __nanosleep(200);
-    if (now_ns() - t0 > kWaitTimeoutNs) { *err = 1; __threadfence_system(); return; }
+    if (now_ns() - t0 > timeout_ns) { *err = 1; __threadfence_system(); return; }
   }
 }
 // waits until every done[r] >= target, r != root
-__global__ void k_wait_all(const unsigned* done, int nranks, int root, int target, int* err) {
+__global__ void k_wait_all(const unsigned* done, int nranks, int root, int target, int* err, unsigned long long timeout_ns) {
   const int r = threadIdx.x;
   if (target <= 0 || r >= nranks || r == root) return;
   const unsigned long long t0 = now_ns();
   while ((int)ld_flag(done + r) < target) {
     __nanosleep(200);
-    if (now_ns() - t0 > kWaitTimeoutNs) { *err = 2; __threadfence_system(); return; }
+    if (now_ns() - t0 > timeout_ns) { *err = 2; __threadfence_system(); return; }
   }
 }
 __global__ void k_set_flag(unsigned* flag, unsigned value) {
@@ -249,6 +251,10 @@ int ensure_frame_slot(tsdf_vol* v, int index);
 // of a status word) whether every rank succeeded.  Any failure leaves the NCCL path in place.
 static int p2p_setup(tsdf_vol* v, tsdf_comm* c, int root) {
   c->p2p_tried = true;
+  if (const char* t = getenv("TSDF_B200_PEER_TIMEOUT_MS")) {
+    const long long ms = atoll(t);
+    if (ms > 0) g_wait_timeout_ns = (unsigned long long)ms * 1000000ull;
+  }
   const char* mode = getenv("TSDF_B200_BCAST");
   bool ok = !(mode && strcmp(mode, "nccl") == 0) && c->nranks > 1;
   for (int k = 0; k < 3 && ok; ++k) ok = ensure_frame_slot(v, k) == TSDF_OK;
@@ -323,7 +329,7 @@ extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, c
     const int k = (int)(v->seq % 3);   // the slot bcast_stage picks; the same on every rank (SPMD)
     if (is_root) {
       // slot k last held frame seq-3: wait until every peer has consumed it, then overwrite
-      k_wait_all<<<1, 32, 0, v->s_copy>>>(c->d_flags + 8, c->nranks, root, seq - 3, c->hd_err);
+      k_wait_all<<<1, 32, 0, v->s_copy>>>(c->d_flags + 8, c->nranks, root, seq - 3, c->hd_err, g_wait_timeout_ns);
       CU_CHECK(cudaGetLastError());
       rc = bcast_stage(v, true, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, true);
       if (rc) return rc;
@@ -333,7 +339,7 @@ extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, c
     }
     rc = bcast_stage(v, false, nullptr, nullptr, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, false);
     if (rc) return rc;
-    k_wait_flag<<<1, 1, 0, v->s_copy>>>(c->peer_flags, seq, c->hd_err);
+    k_wait_flag<<<1, 1, 0, v->s_copy>>>(c->peer_flags, seq, c->hd_err, g_wait_timeout_ns);
     CU_CHECK(cudaGetLastError());
     return bcast_finish(v, slot, color, K, T_wc, obs_weight, c->peer_raw[k], set_done_flag, c);
   }
