@@ -12,7 +12,12 @@
 //   * the camera transform is split into a per-row part (staged once per block in shared
 //     memory) and a per-run part (registers), so the per-voxel cost is three adds;
 //   * volume loads are issued only when at least one voxel of the run is updated;
-//   * k frames can be fused into one pass (state read once, updated k times, written once).
+//   * two instantiations, picked per launch by a host-side frustum test: a dense-frame kernel
+//     whose run is branch-free (batched reciprocals and gathers, select update) and a
+//     sparse-frame kernel with a conservative, bit-exact segment cull (frustum, far depth,
+//     max-depth tiles, mask box) decided by warp ballots;
+//   * the kernel is written for NF frames per pass; only NF = 1 is instantiated (a fused pass
+//     measured slower than NF passes, see launch_integrate).
 //
 // Arithmetic: this file is compiled with -fmad=false; every fp32 operation below is a
 // single IEEE round-to-nearest op in the reference's source order,
