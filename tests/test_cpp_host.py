@@ -105,3 +105,32 @@ def test_cpp_replay_matches_oracle(replay_bin, synth, oracle, tmp_path, raw):
     assert np.array_equal(np.fromfile(tmp_path / "fusion_color.f32", np.float32), c2)
     assert oracle.save_ply(str(tmp_path / "o2.ply"), p2, t2, w2)
     assert (tmp_path / "o2.ply").read_bytes() == (tmp_path / "fusion_points.ply").read_bytes()
+
+
+@pytest.fixture(scope="module")
+def cvmat_bin(pkg, tmp_path_factory):
+    """tests/cpp/cvmat_overloads.cpp against the mock <opencv2/core.hpp> (OpenCV headers are absent
+    from the container): the -DTSDF_B200_WITH_OPENCV overloads of include/TSDFfusion.hpp must compile."""
+    out = tmp_path_factory.mktemp("cvm") / "cvmat_overloads"
+    libdir = os.path.dirname(pkg.capi.LIB_PATH)
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-Werror", "-DTSDF_B200_WITH_OPENCV",
+           "-I", os.path.join(ROOT, "tests", "mock_opencv"), "-I", os.path.join(ROOT, "include"),
+           os.path.join(ROOT, "tests", "cpp", "cvmat_overloads.cpp"), "-o", str(out),
+           "-L", libdir, "-ltsdf_b200", f"-Wl,-rpath,{libdir}"]
+    subprocess.run(cmd, check=True, capture_output=True, text=True)
+    return str(out)
+
+
+def test_cvmat_overloads_compile_and_fail_loudly_without_device(cvmat_bin, pkg):
+    if pkg.device_count() > 0:
+        pytest.skip("a GPU is present")
+    r = subprocess.run([cvmat_bin], capture_output=True, text=True)
+    assert r.returncode == 2 and "no CUDA device" in r.stderr
+
+
+@pytest.mark.gpu
+def test_cvmat_overloads_agree_with_raw_pointers(cvmat_bin):
+    """Integrate(cv::Mat imRGB, cv::Mat imD) — the reference's signature — and the pose-taking form
+    give the volume of the raw-pointer call; wrong Mat types throw std::runtime_error."""
+    r = subprocess.run([cvmat_bin], capture_output=True, text=True)
+    assert r.returncode == 0 and r.stdout.strip() == "ok", r.stderr
