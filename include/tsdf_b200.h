@@ -274,6 +274,19 @@ int tsdf_invert_matrix(const float m[16], float out[16]); /* src/tsdf.cu:276-403
  * cap = 0 to size).  TSDF_E_IO on open/parse failure, TSDF_E_CAPACITY if cap is too small.  */
 int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int* n_cams);
 
+/* Image-name ingest for the same replay: `associations.txt` of a saved run (written by
+ * src/ORB_SLAM2/System.cc:981; one line per keyframe "<t_rgb> <rgb file> <t_depth> <depth file>",
+ * parsed by LoadImageNames, examples/label_instance_rgbd.cpp:239-268, which pairs line i with
+ * keyframe i of bundle.txt, :79-87).  Empty lines are skipped like the reference does.
+ * t_rgb / t_depth: cap doubles each or NULL (the reference reads the stamps into a float and
+ * drops them; here they are kept, in double).  rgb_names / depth_names: cap * name_stride
+ * bytes each or NULL, entry i NUL-terminated at i * name_stride.  *n_lines receives the number
+ * of non-empty lines (call with cap = 0 to size).  TSDF_E_IO on open/parse failure,
+ * TSDF_E_CAPACITY if cap is too small or a name does not fit name_stride.  Decoding the PNGs
+ * stays with the caller (cv::imread in the reference) — this library takes raw pixels.  */
+int tsdf_read_associations(const char* path, double* t_rgb, double* t_depth, char* rgb_names,
+                           char* depth_names, int name_stride, int cap, int* n_lines);
+
 /* ---- measurement hooks (used by bench.py; no effect on results) ------------ */
 /* Times `iters` back-to-back launches of the integrate kernel on the frame
  * last uploaded to the handle (volume state keeps evolving) with CUDA events

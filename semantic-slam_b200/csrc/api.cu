@@ -862,6 +862,48 @@ extern "C" int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int
   return TSDF_OK;
 }
 
+extern "C" int tsdf_read_associations(const char* path, double* t_rgb, double* t_depth, char* rgb_names,
+                                      char* depth_names, int name_stride, int cap, int* n_lines) {
+  REQUIRE(path && n_lines, "null argument");
+  REQUIRE(cap >= 0 && ((!rgb_names && !depth_names) || name_stride > 1), "bad capacity / name_stride");
+  FILE* f = fopen(path, "r");
+  if (!f) { tsdf_set_error("tsdf_read_associations: cannot open %s", path); return TSDF_E_IO; }
+  const bool fill = cap > 0 && (t_rgb || t_depth || rgb_names || depth_names);
+  char line[2048], a[1024], b[1024];
+  int n = 0, rc = TSDF_OK;
+  while (fgets(line, sizeof line, f)) {
+    size_t len = strlen(line);
+    while (len && (line[len - 1] == '\n' || line[len - 1] == '\r' || line[len - 1] == ' ' || line[len - 1] == '\t')) line[--len] = 0;
+    if (!len) continue;
+    double ta = 0, tb = 0;
+    if (sscanf(line, "%lf %1023s %lf %1023s", &ta, a, &tb, b) != 4) {
+      tsdf_set_error("tsdf_read_associations: line %d of %s is not '<t> <rgb> <t> <depth>'", n + 1, path);
+      rc = TSDF_E_IO;
+      break;
+    }
+    if (fill) {
+      if (n >= cap) {
+        tsdf_set_error("tsdf_read_associations: capacity %d is too small for %s", cap, path);
+        rc = TSDF_E_CAPACITY;
+        break;
+      }
+      if ((rgb_names && (int)strlen(a) >= name_stride) || (depth_names && (int)strlen(b) >= name_stride)) {
+        tsdf_set_error("tsdf_read_associations: a file name on line %d does not fit name_stride %d", n + 1, name_stride);
+        rc = TSDF_E_CAPACITY;
+        break;
+      }
+      if (t_rgb) t_rgb[n] = ta;
+      if (t_depth) t_depth[n] = tb;
+      if (rgb_names) strcpy(rgb_names + (size_t)n * name_stride, a);
+      if (depth_names) strcpy(depth_names + (size_t)n * name_stride, b);
+    }
+    ++n;
+  }
+  fclose(f);
+  if (rc == TSDF_OK) *n_lines = n;
+  return rc;
+}
+
 // ---- measurement hooks ---------------------------------------------------------------------------
 extern "C" int tsdf_timer_start(tsdf_vol* v) {
   REQUIRE(v, "null handle");

@@ -87,6 +87,33 @@ def test_read_bundle_poses_matches_fixture(pkg, tmp_path):
     assert lib.tsdf_read_bundle_poses(str(tmp_path / "bad.txt").encode(), T.ctypes.data_as(C.c_void_p), 4, C.byref(n)) == pkg.capi.E_IO
 
 
+def test_read_associations_matches_fixture(pkg, tmp_path):
+    """associations.txt ingest (reference LoadImageNames, examples/label_instance_rgbd.cpp:239-268):
+    the first lines of the reference's saved run; empty lines skipped, malformed ones rejected."""
+    import ctypes as C
+    lib = pkg.load()
+    src = os.path.join(ROOT, "tests", "golden", "associations_head.txt")
+    text = open(src).read()
+    p2 = tmp_path / "assoc.txt"
+    p2.write_text(text.replace("\n", "\n\n", 1) + "\n")          # an empty line inside and at the end
+    n = C.c_int(0)
+    assert lib.tsdf_read_associations(str(p2).encode(), None, None, None, None, 0, 0, C.byref(n)) == 0 and n.value == 4
+    stride = 64
+    tr, td = np.zeros(4), np.zeros(4)
+    a, b = C.create_string_buffer(4 * stride), C.create_string_buffer(4 * stride)
+    args = (tr.ctypes.data_as(C.c_void_p), td.ctypes.data_as(C.c_void_p), a, b)
+    assert lib.tsdf_read_associations(str(p2).encode(), *args, stride, 2, C.byref(n)) == pkg.capi.E_CAPACITY
+    assert lib.tsdf_read_associations(str(p2).encode(), *args, 8, 4, C.byref(n)) == pkg.capi.E_CAPACITY   # names do not fit
+    assert lib.tsdf_read_associations(str(p2).encode(), *args, stride, 4, C.byref(n)) == 0 and n.value == 4
+    want = [ln.split() for ln in text.splitlines()]
+    for i, (t0, f0, t1, f1) in enumerate(want):
+        assert a.raw[i * stride:].split(b"\0")[0].decode() == f0 and b.raw[i * stride:].split(b"\0")[0].decode() == f1
+        assert tr[i] == float(t0) and td[i] == float(t1)
+    assert lib.tsdf_read_associations(str(tmp_path / "none.txt").encode(), None, None, None, None, 0, 0, C.byref(n)) == pkg.capi.E_IO
+    (tmp_path / "bad.txt").write_text("1.0 rgb/a.png 1.0\n")
+    assert lib.tsdf_read_associations(str(tmp_path / "bad.txt").encode(), None, None, None, None, 0, 0, C.byref(n)) == pkg.capi.E_IO
+
+
 def test_slab_ranges_partition_the_grid(pkg):
     for dz in (1024, 256, 200, 130, 7):
         for n in (1, 2, 3, 4, 8):
