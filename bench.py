@@ -423,6 +423,22 @@ def extras(pkg, line, frames, origin, vol=None):
     except Exception as e:  # the checker is optional on a stripped box; say so rather than hide it
         line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port",
                                 "sample": f"unavailable: {e}"}
+    if isinstance(line["cpu_baseline"].get("value"), float):
+        try:   # the plugin's CPU mode as a float64 numpy restatement, C1, one process
+            from oracle.fusion_numpy import TSDFVolumeF64
+            d1, vs1 = (256, 256, 256), 0.02
+            o1, fr1 = synth.s_full(d1, vs1, n_frames=1)
+            o64 = np.asarray(o1, np.float32).astype(np.float64)
+            v64 = TSDFVolumeF64(np.stack([o64, o64 + d1[0] * float(np.float32(vs1))], axis=1), float(np.float32(vs1)))
+            t0 = time.perf_counter()
+            v64.integrate(fr1[0][1], fr1[0][0], synth.TUM3_K, fr1[0][2].reshape(4, 4), 1.0)
+            dt = time.perf_counter() - t0
+            line["cpu_baseline"]["numpy_float64_c1"] = {
+                "value": d1[0] ** 3 / dt / 1e9, "unit": UNIT, "cores": 1, "seconds_per_frame": dt,
+                "sample": "C1 256^3 @ 2 cm, 1 S-full frame; oracle/fusion_numpy.py, restatement of the third-party "
+                          "plugin's CPU mode (upstream source unavailable offline, parity unpinned)"}
+        except Exception as e:
+            line["cpu_baseline"]["numpy_float64_c1"] = {"error": str(e)}
     # C2: 300-frame fr3_office-shaped sequence into 512^3 @ 1 cm (realistic coverage)
     try:
         dims, vs, nfr = (512, 512, 512), 0.01, 300

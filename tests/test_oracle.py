@@ -134,3 +134,35 @@ def test_oracle_range_to_depth_known_answers(oracle, synth):
     cc, rw = np.meshgrid(np.arange(500), np.arange(120))
     ref = 10.0 / np.sqrt(((cc - 100.0) / 400.0) ** 2 + ((rw - 50.0) / 300.0) ** 2 + 1.0)
     assert np.max(np.abs(dd - ref)) < 5e-6
+
+
+def test_numpy_float64_restatement_agrees_with_oracle(oracle, synth):
+    """oracle/fusion_numpy.py (the float64 'reference CPU TSDFfusion path' of SURVEY §8d, parity
+    unpinned) against the fp32 C oracle in SEM_FUSIONPY: same update counts up to pixel/truncation
+    flips from float64 vs float32 rounding, tsdf within 1e-5 and colour within one
+    step per channel (tie rounding) wherever the weights agree and no flip touched the voxel."""
+    from oracle.fusion_numpy import TSDFVolumeF64
+    dims, vs = (48, 40, 44), 0.03
+    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=5)
+    o64 = np.asarray(origin, np.float32).astype(np.float64)
+    bnds = np.stack([o64, o64 + np.array(dims) * float(np.float32(vs))], axis=1)
+    v = TSDFVolumeF64(bnds, float(np.float32(vs)))
+    assert tuple(v.dims) == dims
+    p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), origin, synth.TUM3_HW, synth.TUM3_K, np.inf, SEM_FUSIONPY)
+    t, w, c = oracle.new_volume(p, True)
+    n64 = n32 = 0
+    for d, rgb, T in frames:
+        n32 += oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb), 1.0, t, w, c)
+        n64 += v.integrate(rgb, d, synth.TUM3_K, T.reshape(4, 4), 1.0)
+    assert n32 > 10000 and abs(n64 - n32) <= 2e-3 * n32
+    same = v.weight == w
+    assert same.mean() > 0.995
+    # a voxel whose weights agree can still have sampled a neighbouring pixel in one frame: bounded fraction
+    dt = np.abs(v.tsdf[same] - t[same])
+    assert (dt > 1e-5).mean() < 5e-3
+    # colour: the float64 CPU mode rounds ties to even (np.round), the kernel arithmetic away from zero
+    # (roundf), and (o*w0 + n)/2 ties often: per channel the two may differ by one step, not more
+    clean = same & (np.abs(v.tsdf - t) <= 1e-5)
+    a, b = v.color[clean].astype(np.int64), c[clean].astype(np.int64)
+    step = np.maximum.reduce([np.abs((a >> s & 255) - (b >> s & 255)) for s in (0, 8, 16)])
+    assert (step > 1).mean() < 5e-3 and (step == 0).mean() > 0.9
