@@ -360,7 +360,7 @@ def run_b200(args, rank, world, local_rank):
         sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5)
     else:
         vol.extract_count(pkg.PRED_ABS_LT, 0.999, 0.5)
-    ms_e, _, _, _, _, n_pts, ext_ms = timed(True, args.steps, extract_at_end=True)
+    ms_e, ksum_e, kn_e, _, clocks_e, n_pts, ext_ms = timed(True, args.steps, extract_at_end=True)
     e2e = args.steps * n_total / (ms_e * 1e-3) / 1e9
     written_total = sum_over_ranks(float(written))
 
@@ -376,7 +376,8 @@ def run_b200(args, rank, world, local_rank):
                 "coverage": written_total / n_total,
                 "clocks": clocks,
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": H * W * 7, "d2h_bytes_per_step": 8,
-                        "ms_per_step": ms_e / args.steps,
+                        "ms_per_step": ms_e / args.steps, "kernel_ms": ksum_e / max(kn_e, 1),
+                        "sm_mhz": clocks_e.get("sm_mhz") if isinstance(clocks_e, dict) else None,
                         "includes": "per step: pinned-host frame H2D (+ distribution to the other ranks) + prep + "
                                     "integrate + the step's 8 B N_written written to host memory",
                         "extraction_pass_after_ms": ext_ms, "extracted_points": n_pts},

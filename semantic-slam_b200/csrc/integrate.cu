@@ -610,6 +610,7 @@ struct LaunchOpts {
   int prefetch = 1;    // 0 off, 1 L2, 2 L1 (legacy kernel only)
   int kernel = 1;      // 0: dense kernel, 1: segment cull + staged probe, 2: legacy dense (A/B only)
   int rows_mult = 16;  // row iterations per thread
+  bool balance = true; // dense kernel, few waves: size the blocks so that the grid fills whole waves
 };
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
@@ -628,6 +629,35 @@ Geometry plan(int n_fast, int n_rows, int vec, int nz, int rows_mult = 16) {
   return q;
 }
 
+// Small and mid-size dense volumes run only a few waves of blocks, so a last wave that is mostly
+// empty costs a whole block time (200^3: 625 blocks on 592 resident slots = 2 block times for
+// 1.06 waves of work).  Re-size the blocks so that the grid is just under a whole number of waves.
+// Work per voxel is uniform in the dense kernel; the sparse kernel keeps small blocks (its work per
+// block is not uniform and finer blocks balance better).
+void balance_waves(Geometry* q, int n_rows, int slots) {
+  const long blocks = (long)q->grid.x * q->grid.y * q->grid.z;
+  if (slots <= 0 || blocks > 8L * slots) return;
+  const int rp = kThreads >> q->tpr_log2;
+  const long passes = (n_rows + rp - 1) / rp;
+  const long waves = (blocks + slots - 1) / slots;
+  const long gx_target = std::max(1L, waves * slots / ((long)q->grid.y * q->grid.z));
+  long m = (passes + gx_target - 1) / gx_target;
+  m = std::min<long>(std::max<long>(m, 1), kMaxRowsPerBlock / rp);
+  q->rows_per_block = (int)m * rp;
+  q->grid.x = (unsigned)((n_rows + q->rows_per_block - 1) / q->rows_per_block);
+}
+
+int device_sm_count() {
+  static int sms[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
+  if (!sms[dev]) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess) sms[dev] = n;
+  }
+  return sms[dev];
+}
+
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
 int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
   const int pf = o.prefetch;
@@ -635,6 +665,13 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
   Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult);
+  if (o.kernel == 0 && o.balance) {
+    static int occ = 0;   // resident blocks per SM of this instantiation (same on every B200)
+    if (!occ && cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                    &occ, k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0>, kThreads, 0) != cudaSuccess)
+      occ = 0;
+    balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
+  }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
@@ -718,8 +755,9 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   const bool literal = (v->variant & 1) != 0;
   // A/B knobs (tsdf_set_variant): bit0 literal math; bits1-2 prefetch 1=L2 2=L1 (default L2);
   // bit5 prefetch off; bits3-4 rows per block x64 / x32 (default x16); bit6/bit7 segment cull off/on;
-  // bits8-9 rows per block x8 / x4
+  // bits8-9 rows per block x8 / x4; bit11 wave balancing off
   LaunchOpts o;
+  o.balance = (v->variant & 2048) == 0;
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab

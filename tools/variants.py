@@ -2,10 +2,11 @@
 usage: python tools/variants.py <scene> <dim> [variant ...]
   scene: slab  = z-slab [dim/2, dim/2+dim/8) of S-full (one rank of 8)
          full  = S-full (every voxel written; the roofline workload)
+         cu    = S-full in class-TSDF semantics (x-fast, depth + weight only; 200 = the reference's default volume)
          real  = S-real with fr3_office keyframe poses (C2-like, ~7 % coverage)
          kitti = S-kitti 1241x376 into (dim, dim/4, dim) at 102.4 m / dim voxels (C3-like)
   variant bits: 1 literal math, 2/4 prefetch L2/L1, 8/16/256/512 rows-per-block x64/x32/x8/x4, 32 prefetch off,
-                64 segment cull off, 128 cull + staged probe
+                64 segment cull off, 128 cull + staged probe, 2048 wave balancing off
 Variants are timed round-robin (R rounds of 5 launches each per frame) so that clock / power
 drift hits all of them alike; the report is the median and the minimum over rounds."""
 import importlib, sys, os, json
@@ -25,6 +26,10 @@ if scene == "slab":      # one of 8 z-slabs of the S-full grid (what each rank o
 elif scene == "full":
     dims, vs = (dim,) * 3, 2.048 / dim
     origin, frames = synth.s_full(dims, vs, n_frames=2)
+elif scene == "cu":
+    dims, vs = (dim,) * 3, 2.048 / dim
+    origin, frames = synth.s_full(dims, vs, n_frames=2)
+    kw = dict(semantics=pkg.SEM_TSDFCU, with_color=False, max_depth=6.0)
 elif scene == "real":
     dims, vs = (dim,) * 3, 5.12 / dim
     origin, frames = synth.s_real(dims, vs, n_frames=4, poses=synth.load_pose_fixture()[::48])
