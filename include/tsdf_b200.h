@@ -164,6 +164,13 @@ int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s); /* syncs the handle's stream */
  * is scattered into place (lets G handles fill one host mirror).
  * Any pointer may be NULL.                                                  */
 int tsdf_download(tsdf_vol* v, float* tsdf, float* weight, float* color, int global_layout);
+/* Chunked readback for volumes larger than a comfortable host buffer (a 1024^3 volume is
+ * 12.9 GB; the reference's destructor copies its 200^3 arrays whole, src/tsdf.cu:101-104):
+ * copies n_voxels voxels starting at linear index first_voxel of this handle's LOCAL slab, in
+ * the semantics' storage order (the order tsdf_download(..., 0) uses), to the start of each
+ * non-NULL host array.  TSDF_E_INVALID if the range leaves the slab.                       */
+int tsdf_download_range(tsdf_vol* v, int64_t first_voxel, int64_t n_voxels, float* tsdf,
+                        float* weight, float* color);
 int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, const float* color,
                 int global_layout);
 /* Surface/point extraction on the device (warp-ballot compaction), ascending

@@ -20,7 +20,7 @@ tu() {
 # strict: the parity pin for oracle/tsdf_oracle.c (same flags as liboracle.so)
 tu | g++ -x c++ -std=c++11 -w -O2 -fPIC -shared -ffp-contract=off -o "$OUT/libtsdf_ref.so" -
 # omp: the "reference CPU" timing arm (all host cores)
-tu | g++ -x c++ -std=c++11 -w -O3 -march=native -fopenmp -fPIC -shared -ffp-contract=off -o "$OUT/libtsdf_ref_omp.so" -
+tu | g++ -x c++ -std=c++11 -w -O3 -march=x86-64-v3 -fopenmp -fPIC -shared -ffp-contract=off -o "$OUT/libtsdf_ref_omp.so" -
 # gpu: the lifted kernel built by nvcc for sm_100a with nvcc's defaults (fmad on), as the
 # reference's CMake would (CMakeLists.txt:18-21 has no flags at all)
 if command -v nvcc >/dev/null 2>&1; then

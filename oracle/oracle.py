@@ -60,6 +60,9 @@ class Oracle:
         L.oracle_integrate.restype = C.c_int64
         L.oracle_integrate.argtypes = [C.POINTER(OracleParams), _f32p, _f32p, C.c_void_p, C.c_float,
                                        _f32p, _f32p, C.c_void_p]
+        L.oracle_integrate_range.restype = C.c_int64
+        L.oracle_integrate_range.argtypes = [C.POINTER(OracleParams), _f32p, _f32p, C.c_void_p, C.c_float,
+                                             C.c_int64, C.c_int64, _f32p, _f32p, C.c_void_p]
         L.oracle_extract.restype = C.c_int64
         L.oracle_extract.argtypes = [C.POINTER(OracleParams), _f32p, _f32p, C.c_void_p, C.c_int,
                                      C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -137,6 +140,15 @@ class Oracle:
         return int(self.lib.oracle_integrate(C.byref(p), np.ascontiguousarray(cam2base, np.float32).reshape(16),
                                              np.ascontiguousarray(depth, np.float32).reshape(-1), cp,
                                              np.float32(obs_weight), tsdf, weight, cv))
+
+    def integrate_range(self, p, cam2base, depth, color_packed, obs_weight, first, n, tsdf, weight, color):
+        """As integrate, but only the voxels [first, first + n) of the slab's storage order
+        (arrays of n voxels)."""
+        cp = None if color_packed is None else color_packed.ctypes.data
+        cv = None if color is None else color.ctypes.data
+        return int(self.lib.oracle_integrate_range(C.byref(p), np.ascontiguousarray(cam2base, np.float32).reshape(16),
+                                                   np.ascontiguousarray(depth, np.float32).reshape(-1), cp,
+                                                   np.float32(obs_weight), int(first), int(n), tsdf, weight, cv))
 
     def extract(self, p, tsdf, weight, color, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
         cv = None if color is None else color.ctypes.data

@@ -137,65 +137,95 @@ static inline int round_pix(float u, int n, int* ok) {
   return (int)r;
 }
 
-/* One frame into one slab.  Follows src/tsdf.cu:21-59 line by line (Appendix A of
- * SURVEY.md); SEM_FUSIONPY adds obs_weight, `<` truncation test and the colour average.
+/* One voxel of one frame.  Follows src/tsdf.cu:27-57 line by line (Appendix A of SURVEY.md);
+ * SEM_FUSIONPY adds obs_weight, `<` truncation test and the colour average.  (x,y,z) are GLOBAL
+ * voxel indices, idx the position in the caller's arrays.  Returns 1 if the voxel was written. */
+static inline int update_voxel(const oracle_params* p, const float* c, const float* depth,
+                               const float* color_packed, float obs_weight, int x, int y, int z,
+                               int64_t idx, float* tsdf, float* weight, float* color) {
+  const int W = p->im_w, H = p->im_h;
+  const float vs = p->voxel_size, trunc = p->trunc_margin;
+  const float* K = p->K;
+  const int sem = p->semantics;
+  float bx = p->origin[0] + (float)x * vs; /* :27 */
+  float by = p->origin[1] + (float)y * vs; /* :28 */
+  float bz = p->origin[2] + (float)z * vs; /* :29 (global z) */
+  float t0 = bx - c[3], t1 = by - c[7], t2 = bz - c[11]; /* :33-35 */
+  float cx_ = c[0] * t0 + c[4] * t1; cx_ = cx_ + c[8] * t2;  /* :36 */
+  float cy_ = c[1] * t0 + c[5] * t1; cy_ = cy_ + c[9] * t2;  /* :37 */
+  float cz_ = c[2] * t0 + c[6] * t1; cz_ = cz_ + c[10] * t2; /* :38 */
+  if (cz_ <= 0) return 0; /* :39 */
+  int okx, oky;
+  int px = round_pix(K[0] * (cx_ / cz_) + K[2], W, &okx); /* :41 */
+  int py = round_pix(K[4] * (cy_ / cz_) + K[5], H, &oky); /* :42 */
+  if (!okx || !oky) return 0; /* :43 */
+  float d = depth[(int64_t)py * W + px]; /* :45 */
+  if (d <= 0 || d > p->max_depth) return 0; /* :46 */
+  float diff = d - cz_; /* :48 */
+  if (sem == SEM_TSDFCU ? (diff <= -trunc) : (diff < -trunc)) return 0; /* :49 */
+  float dist = fminf(1.0f, diff / trunc); /* :53 */
+  float w0 = weight[idx]; /* :54 */
+  float w1 = w0 + obs_weight; /* :55 (1.0f in the TSDF class) */
+  weight[idx] = w1; /* :56 */
+  tsdf[idx] = (tsdf[idx] * w0 + dist) / w1; /* :57 */
+  if (color && color_packed) {
+    /* upstream colour average on float-packed B*65536+G*256+R */
+    float oc = color[idx];
+    float ob = floorf(oc / 65536.0f);
+    float og = floorf((oc - ob * 65536.0f) / 256.0f);
+    float orr = oc - ob * 65536.0f - og * 256.0f;
+    float nc = color_packed[(int64_t)py * W + px];
+    float nb = floorf(nc / 65536.0f);
+    float ng = floorf((nc - nb * 65536.0f) / 256.0f);
+    float nr = nc - nb * 65536.0f - ng * 256.0f;
+    nb = fminf(roundf((ob * w0 + nb) / w1), 255.0f);
+    ng = fminf(roundf((og * w0 + ng) / w1), 255.0f);
+    nr = fminf(roundf((orr * w0 + nr) / w1), 255.0f);
+    color[idx] = nb * 65536.0f + ng * 256.0f + nr;
+  }
+  return 1;
+}
+
+/* One frame into one slab: the loop nest of src/tsdf.cu:21-23 over the slab's voxels.
  * depth: H*W fp32.  color_packed: H*W fp32 = c2*65536+c1*256+c0 (may be NULL => no colour).
- * cam2base: 16 floats.  tsdf/weight/color: LOCAL slab arrays.
- * Returns the number of voxels written. */
+ * cam2base: 16 floats.  tsdf/weight/color: LOCAL slab arrays, index by src/tsdf.cu:52 or the
+ * plugin's [x][y][z] order.  Returns the number of voxels written. */
 int64_t oracle_integrate(const oracle_params* p, const float* cam2base, const float* depth,
                          const float* color_packed, float obs_weight, float* tsdf, float* weight,
                          float* color) {
   const int dx = p->dim_x, dy = p->dim_y;
   const int z0 = p->z_begin, z1 = p->z_end, dzl = z1 - z0;
-  const int W = p->im_w, H = p->im_h;
-  const float vs = p->voxel_size, trunc = p->trunc_margin;
-  const float* c = cam2base;
-  const float* K = p->K;
   const int sem = p->semantics;
   int64_t written = 0;
 #pragma omp parallel for collapse(2) schedule(static) reduction(+ : written)
   for (int z = z0; z < z1; ++z)
     for (int y = 0; y < dy; ++y)
-      for (int x = 0; x < dx; ++x) {
-        float bx = p->origin[0] + (float)x * vs; /* :27 */
-        float by = p->origin[1] + (float)y * vs; /* :28 */
-        float bz = p->origin[2] + (float)z * vs; /* :29 (global z) */
-        float t0 = bx - c[3], t1 = by - c[7], t2 = bz - c[11]; /* :33-35 */
-        float cx_ = c[0] * t0 + c[4] * t1; cx_ = cx_ + c[8] * t2;  /* :36 */
-        float cy_ = c[1] * t0 + c[5] * t1; cy_ = cy_ + c[9] * t2;  /* :37 */
-        float cz_ = c[2] * t0 + c[6] * t1; cz_ = cz_ + c[10] * t2; /* :38 */
-        if (cz_ <= 0) continue; /* :39 */
-        int okx, oky;
-        int px = round_pix(K[0] * (cx_ / cz_) + K[2], W, &okx); /* :41 */
-        int py = round_pix(K[4] * (cy_ / cz_) + K[5], H, &oky); /* :42 */
-        if (!okx || !oky) continue; /* :43 */
-        float d = depth[(int64_t)py * W + px]; /* :45 */
-        if (d <= 0 || d > p->max_depth) continue; /* :46 */
-        float diff = d - cz_; /* :48 */
-        if (sem == SEM_TSDFCU ? (diff <= -trunc) : (diff < -trunc)) continue; /* :49 */
-        int64_t idx = lin_index(sem, x, y, z - z0, dx, dy, dzl); /* :52 */
-        float dist = fminf(1.0f, diff / trunc); /* :53 */
-        float w0 = weight[idx]; /* :54 */
-        float w1 = w0 + obs_weight; /* :55 (1.0f in the TSDF class) */
-        weight[idx] = w1; /* :56 */
-        tsdf[idx] = (tsdf[idx] * w0 + dist) / w1; /* :57 */
-        ++written;
-        if (color && color_packed) {
-          /* upstream colour average on float-packed B*65536+G*256+R */
-          float oc = color[idx];
-          float ob = floorf(oc / 65536.0f);
-          float og = floorf((oc - ob * 65536.0f) / 256.0f);
-          float orr = oc - ob * 65536.0f - og * 256.0f;
-          float nc = color_packed[(int64_t)py * W + px];
-          float nb = floorf(nc / 65536.0f);
-          float ng = floorf((nc - nb * 65536.0f) / 256.0f);
-          float nr = nc - nb * 65536.0f - ng * 256.0f;
-          nb = fminf(roundf((ob * w0 + nb) / w1), 255.0f);
-          ng = fminf(roundf((og * w0 + ng) / w1), 255.0f);
-          nr = fminf(roundf((orr * w0 + nr) / w1), 255.0f);
-          color[idx] = nb * 65536.0f + ng * 256.0f + nr;
-        }
-      }
+      for (int x = 0; x < dx; ++x)
+        written += update_voxel(p, cam2base, depth, color_packed, obs_weight, x, y, z,
+                                lin_index(sem, x, y, z - z0, dx, dy, dzl), tsdf, weight, color);
+  return written;
+}
+
+/* The same frame into the voxels [first, first + n) of the slab's linear storage order only
+ * (arrays hold n voxels, entry i = slab voxel first + i): lets the tests check any window of a
+ * volume too large to mirror on the host, e.g. across the 2^31-voxel boundary. */
+int64_t oracle_integrate_range(const oracle_params* p, const float* cam2base, const float* depth,
+                               const float* color_packed, float obs_weight, int64_t first, int64_t n,
+                               float* tsdf, float* weight, float* color) {
+  const int64_t dx = p->dim_x, dy = p->dim_y, dzl = p->z_end - p->z_begin;
+  int64_t written = 0;
+#pragma omp parallel for schedule(static) reduction(+ : written)
+  for (int64_t i = 0; i < n; ++i) {
+    const int64_t g = first + i;
+    int x, y, zl;
+    if (p->semantics == SEM_TSDFCU) { /* inverse of src/tsdf.cu:52, as :201-203 */
+      zl = (int)(g / (dx * dy)); y = (int)((g - zl * dx * dy) / dx); x = (int)(g - zl * dx * dy - y * dx);
+    } else {
+      x = (int)(g / (dy * dzl)); y = (int)((g - x * dy * dzl) / dzl); zl = (int)(g - x * dy * dzl - y * dzl);
+    }
+    written += update_voxel(p, cam2base, depth, color_packed, obs_weight, x, y, zl + p->z_begin, i,
+                            tsdf, weight, color);
+  }
   return written;
 }
 

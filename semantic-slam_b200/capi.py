@@ -64,6 +64,7 @@ SIGNATURES = {
     "tsdf_sync": (_I, [_VP]),
     "tsdf_get_stats": (_I, [_VP, C.POINTER(Stats)]),
     "tsdf_download": (_I, [_VP, _VP, _VP, _VP, _I]),
+    "tsdf_download_range": (_I, [_VP, _I64, _I64, _VP, _VP, _VP]),
     "tsdf_upload": (_I, [_VP, _VP, _VP, _VP, _I]),
     "tsdf_extract_points": (_I, [_VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
     "tsdf_extract_points_device": (_I, [_VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),

@@ -576,6 +576,24 @@ extern "C" int tsdf_download(tsdf_vol* v, float* tsdf, float* weight, float* col
   return TSDF_OK;
 }
 
+extern "C" int tsdf_download_range(tsdf_vol* v, int64_t first_voxel, int64_t n_voxels, float* tsdf,
+                                   float* weight, float* color) {
+  REQUIRE(v, "null handle");
+  REQUIRE(first_voxel >= 0 && n_voxels >= 0 && first_voxel <= v->n_local && n_voxels <= v->n_local - first_voxel,
+          "voxel range outside the slab");
+  REQUIRE(!color || v->d_color, "volume has no colour array");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  const size_t bytes = (size_t)n_voxels * sizeof(float);
+  float* host[3] = {tsdf, weight, color};
+  const float* dev[3] = {v->d_tsdf, v->d_weight, v->d_color};
+  for (int i = 0; i < 3; ++i)
+    if (host[i] && bytes) CU_CHECK(cudaMemcpyAsync(host[i], dev[i] + first_voxel, bytes, cudaMemcpyDeviceToHost, v->s_compute));
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  return TSDF_OK;
+}
+
 extern "C" int tsdf_upload(tsdf_vol* v, const float* tsdf, const float* weight, const float* color,
                            int global_layout) {
   if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass

@@ -208,6 +208,15 @@ class Volume:
         check(self.lib.tsdf_download(self.h, ptr(t), ptr(w), ptr(c), 0))
         return t, w, c
 
+    def download_range(self, first_voxel, n_voxels, want_color=None):
+        """Voxels [first_voxel, first_voxel + n_voxels) of the local slab in storage order."""
+        t = np.empty(n_voxels, np.float32)
+        w = np.empty(n_voxels, np.float32)
+        has_c = bool(self.cfg.with_color) if want_color is None else want_color
+        c = np.empty(n_voxels, np.float32) if has_c else None
+        check(self.lib.tsdf_download_range(self.h, int(first_voxel), int(n_voxels), ptr(t), ptr(w), ptr(c)))
+        return t, w, c
+
     def download_into(self, tsdf, weight, color):
         """Scatter this slab into GLOBAL host arrays (global_layout=1)."""
         check(self.lib.tsdf_download(self.h, ptr(tsdf), ptr(weight), ptr(color), 1))

@@ -166,3 +166,24 @@ def test_numpy_float64_restatement_agrees_with_oracle(oracle, synth):
     a, b = v.color[clean].astype(np.int64), c[clean].astype(np.int64)
     step = np.maximum.reduce([np.abs((a >> s & 255) - (b >> s & 255)) for s in (0, 8, 16)])
     assert (step > 1).mean() < 5e-3 and (step == 0).mean() > 0.9
+
+
+def test_oracle_range_equals_whole(oracle, synth):
+    """oracle_integrate_range (a window of the linear storage order) against oracle_integrate on
+    the same slab, both semantics, whole grid and a z-slab."""
+    dims, vs = (40, 36, 44), 0.04
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=3)
+    for sem in (SEM_TSDFCU, SEM_FUSIONPY):
+        for zr in (None, (8, 30)):
+            p = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, sem, zr)
+            t, w, c = oracle.new_volume(p, True)
+            n = oracle.n_local(p)
+            first, cnt = n // 3, n // 2
+            t2, w2, c2 = np.ones(cnt, np.float32), np.zeros(cnt, np.float32), np.zeros(cnt, np.float32)
+            total = part = 0
+            for d, rgb, T in frames:
+                total += oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb), 1.0, t, w, c)
+                part += oracle.integrate_range(p, T.reshape(16), d, oracle.pack_color(rgb), 1.0, first, cnt, t2, w2, c2)
+            s = slice(first, first + cnt)
+            assert 0 < part < total and part == int(w[s].sum())
+            assert np.array_equal(bits(t[s]), bits(t2)) and np.array_equal(w[s], w2) and np.array_equal(c[s], c2)

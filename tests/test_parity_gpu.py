@@ -509,3 +509,63 @@ def test_against_reference_gpu_kernel(pkg, oracle, synth):
     assert flipped <= 1e-3 * gw.size, f"{flipped} of {gw.size} tsdf values differ by more than {TOL}"
     print(f"reference GPU kernel (FMA build): {differ} / {gw.size} weights differ, {flipped} tsdf values differ by "
           f"> {TOL} (pixel / truncation flips), median |diff| {np.median(dt[gw > 0]):.2e}")
+
+
+@pytest.mark.parametrize("sem", [SEM_TSDFCU, SEM_FUSIONPY])
+def test_more_than_2_31_voxels(pkg, oracle, synth, sem):
+    """Maximum sizes: a 1280 x 1280 x 1536 grid (2.52 G voxels > 2^31; 20-30 GB of HBM) — every
+    linear index, byte offset and extraction index must be 64-bit.  The volume is too large to
+    mirror on the host, so windows of the storage order (tsdf_download_range) are compared bit for
+    bit with the oracle restricted to the same windows (oracle_integrate_range): the first and
+    last 2^20 voxels, the window straddling voxel 2^31, and windows around written voxels found
+    through the extraction's own int64 indices."""
+    dims, vs = (1280, 1280, 1536), 0.004
+    color = sem == SEM_FUSIONPY
+    n = int(np.prod(dims))
+    assert n > 2 ** 31
+    # two views from near the centre, towards the +z and the +x wall of the room: the surfaces with
+    # the largest linear indices in either storage order
+    poses = [synth.look_at((0.1, 0.0, -1.0), (0.0, 0.2, 3.0)), synth.look_at((-1.0, 0.1, 0.0), (3.0, 0.2, 0.1))]
+    origin, frames = synth.s_real(dims, vs, n_frames=2, seed=11, poses=poses)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=6.0)
+    p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), origin, synth.TUM3_HW, synth.TUM3_K, 6.0, sem)
+    W = 1 << 20
+    with pkg.Volume(cfg) as vol:
+        assert vol.n_local == n
+        written = 0
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb if color else None, T)
+            written += vol.stats().voxels_written
+        assert written > 10 ** 6
+        xyz, _, idx = vol.extract_points(PRED_ABS_LT, 0.999, 0.5)
+        assert len(idx) > 10 ** 5 and np.all(np.diff(idx) > 0) and idx[0] >= 0 and idx[-1] < n
+        assert idx[-1] > 2 ** 31, "scene must reach past voxel 2^31"
+        hi = int(idx[np.searchsorted(idx, 2 ** 31)])
+        firsts = [0, 2 ** 31 - W // 2, n - W, max(0, int(idx[0]) - W // 2), min(n - W, hi - W // 2),
+                  min(n - W, int(idx[-1]) - W // 2)]
+        touched = 0
+        for first in firsts:
+            t, w, c = np.ones(W, np.float32), np.zeros(W, np.float32), (np.zeros(W, np.float32) if color else None)
+            for d, rgb, T in frames:
+                touched += oracle.integrate_range(p, T.reshape(16), d, oracle.pack_color(rgb) if color else None,
+                                                  1.0, first, W, t, w, c)
+            gt, gw, gc = vol.download_range(first, W)
+            assert np.array_equal(gw, w) and np.array_equal(bits(gt), bits(t)), first
+            if color:
+                assert np.array_equal(gc, c), first
+            # the extraction's indices inside the window are exactly the oracle's surface voxels
+            sel = np.flatnonzero((np.abs(t) < np.float32(0.999)) & (w > 0.5)) + first
+            a, b = np.searchsorted(idx, first), np.searchsorted(idx, first + W)
+            assert np.array_equal(idx[a:b], sel), first
+            if len(sel):   # coordinates of the last one (src/tsdf.cu:201-208 / the plugin's order)
+                g = int(sel[-1])
+                if sem == SEM_TSDFCU:
+                    z, r = divmod(g, dims[0] * dims[1]); y, x = divmod(r, dims[0])
+                else:
+                    x, r = divmod(g, dims[1] * dims[2]); y, z = divmod(r, dims[2])
+                o32, v32 = np.asarray(origin, np.float32), np.float32(vs)
+                want = np.array([o32[0] + np.float32(x) * v32, o32[1] + np.float32(y) * v32, o32[2] + np.float32(z) * v32], np.float32)
+                assert np.array_equal(bits(xyz[b - 1]), bits(want))
+        assert touched > 10 ** 4
+        with pytest.raises(Exception):
+            vol.download_range(n - 10, 11)
