@@ -619,6 +619,7 @@ Geometry plan(int n_fast, int n_rows, int vec, int nz, int rows_mult = 16) {
   Geometry q;
   int vec_per_row = (n_fast + vec - 1) / vec;
   q.tpr_log2 = 0;
+  while ((kThreads >> q.tpr_log2) > kMaxRowsPerBlock) ++q.tpr_log2;   // one pass of rows must fit the row table
   while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < kThreads) ++q.tpr_log2;
   int tpr = 1 << q.tpr_log2;
   int rp = kThreads / tpr;
@@ -642,7 +643,7 @@ void balance_waves(Geometry* q, int n_rows, int slots) {
   const long waves = (blocks + slots - 1) / slots;
   const long gx_target = std::max(1L, waves * slots / ((long)q->grid.y * q->grid.z));
   long m = (passes + gx_target - 1) / gx_target;
-  m = std::min<long>(std::max<long>(m, 1), kMaxRowsPerBlock / rp);
+  m = std::max<long>(std::min<long>(m, kMaxRowsPerBlock / rp), 1);
   q->rows_per_block = (int)m * rp;
   q->grid.x = (unsigned)((n_rows + q->rows_per_block - 1) / q->rows_per_block);
 }

@@ -39,6 +39,53 @@ def assert_volume_equal(gt, gw, gc, t, w, c):
         assert np.max(np.abs(gc - c), initial=0) <= TOL, "colour differs"
 
 
+@pytest.mark.parametrize("sem,color", [(SEM_TSDFCU, False), (SEM_FUSIONPY, True)])
+@pytest.mark.parametrize("dims", [(1100, 6, 10), (10, 6, 1100), (1027, 5, 3), (3, 5, 1027), (2052, 4, 4), (4, 4, 2052)])
+def test_long_and_ragged_fast_axis(pkg, oracle, synth, sem, color, dims):
+    """Rows longer than one block's 1024 voxels (several blocks along the fast axis) and row
+    lengths that are not a multiple of 4 (scalar path, partial last warp), in both storage
+    orders: S-full frames (every voxel written) and the same frames with the camera moved
+    sideways and turned so that part of the long axis leaves the image."""
+    vs = 0.004 if max(dims) < 2000 else 0.002     # keeps the wall behind the volume within max_depth
+    origin, frames = synth.s_full(dims, vs, n_frames=2)
+    turned = [(d, rgb, (T.reshape(4, 4) @ synth.pose(synth.rot_xyz(0.02 * (i + 1), 0.2 - 0.45 * i, 0.05),
+                                                     (1.1 - 2.4 * i, 0.05, 0.0))).astype(np.float32))
+              for i, (d, rgb, T) in enumerate(frames)]
+    frames = frames + turned
+    p, t, w, c, written = oracle_run(oracle, dims, vs, origin, frames, sem, color, max_depth=6.0)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=6.0)
+    with pkg.Volume(cfg) as vol:
+        for (d, rgb, T), ow in zip(frames, written):
+            vol.integrate(d, rgb if color else None, T)
+            assert vol.stats().voxels_written == ow
+        gt, gw, gc = vol.download()
+    n = int(np.prod(dims))
+    assert written[0] == n and any(0 < x < n for x in written[2:]), written
+    assert_volume_equal(gt, gw, gc, t, w, c)
+
+
+@pytest.mark.parametrize("sem,color", [(SEM_TSDFCU, False), (SEM_FUSIONPY, True)])
+@pytest.mark.parametrize("dims", [(48, 40, 1), (1, 40, 48), (48, 40, 4), (4, 40, 48), (2, 2, 2), (1, 1, 1), (5, 1, 7)])
+def test_degenerate_axes(pkg, oracle, synth, sem, color, dims):
+    """Axes of 1-4 voxels (a fast axis shorter than one vector, a single row, a single voxel): the
+    thread-to-row mapping must keep one pass of rows inside the block's row table."""
+    vs = 0.05
+    origin, frames = synth.s_full(dims, vs, n_frames=2)
+    frames = frames + [(d, rgb, (T.reshape(4, 4) @ synth.pose(synth.rot_xyz(0.03, 0.25 - 0.5 * i, 0.1),
+                                                              (0.6 - 1.2 * i, 0.1, 0.0))).astype(np.float32))
+                       for i, (d, rgb, T) in enumerate(frames)]
+    p, t, w, c, written = oracle_run(oracle, dims, vs, origin, frames, sem, color, max_depth=6.0)
+    cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=6.0)
+    with pkg.Volume(cfg) as vol:
+        for (d, rgb, T), ow in zip(frames, written):
+            vol.integrate(d, rgb if color else None, T)
+            assert vol.stats().voxels_written == ow
+        gt, gw, gc = vol.download()
+        n_pts = vol.extract_count(PRED_NONZERO, 1.2, 0.9)
+    assert written[0] == int(np.prod(dims)) and n_pts == int(((t != 0) & (w > 0.9)).sum())
+    assert_volume_equal(gt, gw, gc, t, w, c)
+
+
 @pytest.mark.parametrize("sem,color", [(SEM_TSDFCU, False), (SEM_FUSIONPY, True), (SEM_FUSIONPY, False)])
 @pytest.mark.parametrize("dims", [(64, 48, 64), (50, 44, 38), (33, 17, 21), (128, 8, 260)])
 def test_integrate_matches_oracle(pkg, oracle, synth, sem, color, dims):
