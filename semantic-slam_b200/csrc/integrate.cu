@@ -22,6 +22,7 @@
 // Arithmetic: this file is compiled with -fmad=false; every fp32 operation below is a
 // single IEEE round-to-nearest op in the reference's source order,
 // so results are bit-identical to oracle/tsdf_oracle.c.
+#include <climits>
 #include "common.cuh"
 #include "exactmath.cuh"
 
@@ -322,6 +323,11 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   const int row0 = blockIdx.x * rows_per_block;
   if (row0 >= n_rows) return;  // batched launches size the grid for the largest instance
 
+  // block hull of the row terms (sparse kernel): order-preserving integer keys, [2k] min, [2k+1] max
+  __shared__ int hull[4 * NT * 2];
+  if constexpr (CULL == 2 && NF == 1)
+    if (threadIdx.x < 4 * NT * 2) hull[threadIdx.x] = (threadIdx.x & 1) ? INT_MIN : INT_MAX;
+
   // ---- prologue 1: per-row terms of the camera transform -> shared memory ---------------
   for (int lr = threadIdx.x; lr < rows_per_block; lr += kThreads) {
     int r = row0 + lr;
@@ -347,6 +353,66 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     }
   }
   __syncthreads();
+
+  // ---- prologue 1b (sparse kernel): can ANY voxel of this block be touched? ---------------
+  // The computed camera coordinates of voxel k of row r are e_r + p_k (ZFAST) or (p_k + y_r) + z_r:
+  // fp32 additions, weakly monotone in each operand.  With [elo, ehi] the component-wise hull of
+  // the block's row terms and [plo, phi] that of the fast-axis terms at the two ends of the
+  // block's fast-axis window (monotone in k, as in box_is_skipped), the same additions applied to
+  // the hull ends bound every voxel's computed coordinates — in fp32, no error analysis.  One box
+  // test on that hull, identical in every thread, lets a block outside the frustum (or behind
+  // everything the frame sees) leave before the per-warp tests and the row loop.
+  if constexpr (CULL == 2 && NF == 1) {
+    if (flags & 4) {
+      bool bad = false;
+      if (threadIdx.x < kMaxRowsPerBlock) {             // whole warps: rows_per_block <= 128
+        const int lr = threadIdx.x;
+        const bool valid = lr < rows_per_block && row0 + lr < n_rows;
+        float v[4 * NT];
+#pragma unroll
+        for (int t = 0; t < NT; ++t) {
+          const float4 e = valid ? tab[lr * NT + t] : make_float4(0.f, 0.f, 0.f, 0.f);
+          v[4 * t] = e.x; v[4 * t + 1] = e.y; v[4 * t + 2] = e.z; v[4 * t + 3] = 0.0f;
+        }
+#pragma unroll
+        for (int i = 0; i < 4 * NT; ++i) {
+          if ((i & 3) == 3) continue;
+          bad = bad || (valid && !(fabsf(v[i]) <= 3.0e38f));
+          const int key = em::order_key(v[i]);
+          const int kmin = __reduce_min_sync(0xffffffffu, valid ? key : INT_MAX);
+          const int kmax = __reduce_max_sync(0xffffffffu, valid ? key : INT_MIN);
+          if ((threadIdx.x & 31) == 0) { atomicMin(&hull[2 * i], kmin); atomicMax(&hull[2 * i + 1], kmax); }
+        }
+      }
+      if (!__syncthreads_or(bad)) {
+        const int tprb = 1 << tpr_log2;
+        const int a = blockIdx.y * tprb * VEC;
+        int b = a + tprb * VEC - 1;
+        if (b > g.n_fast - 1) b = g.n_fast - 1;
+        float pa0, pa1, pa2, pb0, pb1, pb2;
+        fast_terms<ZFAST>(P.f[0].c, fast_coord<ZFAST>(g, a), pa0, pa1, pa2);
+        fast_terms<ZFAST>(P.f[0].c, fast_coord<ZFAST>(g, b), pb0, pb1, pb2);
+        float lo[3], hi[3];
+        const float plo[3] = {fminf(pa0, pb0), fminf(pa1, pb1), fminf(pa2, pb2)};
+        const float phi[3] = {fmaxf(pa0, pb0), fmaxf(pa1, pb1), fmaxf(pa2, pb2)};
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float e0lo = em::order_unkey(hull[2 * k]), e0hi = em::order_unkey(hull[2 * k + 1]);
+          if constexpr (ZFAST) {
+            lo[k] = e0lo + plo[k];
+            hi[k] = e0hi + phi[k];
+          } else {
+            const float e1lo = em::order_unkey(hull[2 * (4 + k)]), e1hi = em::order_unkey(hull[2 * (4 + k) + 1]);
+            lo[k] = (plo[k] + e0lo) + e1lo;
+            hi[k] = (phi[k] + e0hi) + e1hi;
+          }
+        }
+        if (box_is_skipped(P.f[0], g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                           reinterpret_cast<const int*>(P.f[0].dmax)))
+          return;   // block-uniform: every thread took the same decision
+      }
+    }
+  }
 
   // ---- this thread's run on the fast axis -----------------------------------------------
   const int tpr = 1 << tpr_log2;
@@ -611,16 +677,18 @@ struct LaunchOpts {
   int kernel = 1;      // 0: dense kernel, 1: segment cull + staged probe, 2: legacy dense (A/B only)
   int rows_mult = 16;  // row iterations per thread
   bool balance = true; // dense kernel, few waves: size the blocks so that the grid fills whole waves
+  bool compact = true;    // sparse kernel: compact block tiles (one warp per row segment)
+  bool block_test = true; // sparse kernel: block-level hull test before the per-warp tests
 };
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
 
-Geometry plan(int n_fast, int n_rows, int vec, int nz, int rows_mult = 16) {
+Geometry plan(int n_fast, int n_rows, int vec, int nz, int rows_mult = 16, int max_tpr = kThreads) {
   Geometry q;
   int vec_per_row = (n_fast + vec - 1) / vec;
   q.tpr_log2 = 0;
   while ((kThreads >> q.tpr_log2) > kMaxRowsPerBlock) ++q.tpr_log2;   // one pass of rows must fit the row table
-  while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < kThreads) ++q.tpr_log2;
+  while ((1 << q.tpr_log2) < vec_per_row && (1 << q.tpr_log2) < max_tpr) ++q.tpr_log2;
   int tpr = 1 << q.tpr_log2;
   int rp = kThreads / tpr;
   q.rows_per_block = rp * rows_mult;
@@ -665,7 +733,9 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   LaunchP<NF> P;
   P.g = g;
   for (int i = 0; i < NF; ++i) P.f[i] = frames[i];
-  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult);
+  // sparse kernel: one warp per row segment (32 runs), 8 rows in parallel, so that a block is a
+  // compact tile (128 rows x 128 voxels) the block-level hull test can reject as a whole
+  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult, (o.kernel == 1 && o.compact) ? 32 : kThreads);
   if (o.kernel == 0 && o.balance) {
     static int occ = 0;   // resident blocks per SM of this instantiation (same on every B200)
     if (!occ && cudaOccupancyMaxActiveBlocksPerMultiprocessor(
@@ -673,7 +743,7 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
       occ = 0;
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
-  if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
   else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   CU_CHECK(cudaGetLastError());
@@ -759,6 +829,8 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   // bits8-9 rows per block x8 / x4; bit11 wave balancing off
   LaunchOpts o;
   o.balance = (v->variant & 2048) == 0;
+  o.compact = (v->variant & 4096) == 0;      // bit12: old block shape (row-major, up to 256 threads per row)
+  o.block_test = (v->variant & 8192) == 0;   // bit13: block-level hull test off
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
@@ -790,7 +862,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st) {
   Geometry q = plan(max_fast, max_rows, vec4 ? 4 : 1, n_active);
-#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, 1 /* L2 prefetch */)
+#define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, 1 /* L2 prefetch */ | 4 /* block hull test */)
   if (zfast) {
     if (color) { if (wmode == 1) { if (vec4) LB(true, true, false, 4, 1); else LB(true, true, false, 1, 1); }
                  else            { if (vec4) LB(true, true, false, 4, 0); else LB(true, true, false, 1, 0); } }
