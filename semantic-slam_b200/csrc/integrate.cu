@@ -289,6 +289,24 @@ __device__ __forceinline__ void cam_coords(const float4& ea, const float4& eb, f
   }
 }
 
+// Row terms of the camera transform of row (slow, mid) — the ONE spelling used by the row table
+// and by the block-level hull test.  ZFAST: e0 = {A0,A1,A2}; !ZFAST: e0 = {Y0,Y1,Y2}, e1 = {Z0,Z1,Z2}.
+template <bool ZFAST>
+__device__ __forceinline__ void row_terms(const GridP& g, const float* c, int slow, int mid, float4& e0, float4& e1) {
+  const float by = g.oy + (float)mid * g.vs;                       // :28
+  const float t1 = by - c[7];                                      // :34
+  if constexpr (ZFAST) {
+    const float bx = g.ox + (float)slow * g.vs;                    // :27
+    const float t0 = bx - c[3];                                    // :33
+    e0 = make_float4(c[0] * t0 + c[4] * t1, c[1] * t0 + c[5] * t1, c[2] * t0 + c[6] * t1, 0.0f);
+  } else {
+    const float bz = g.oz + (float)(g.z0 + slow) * g.vs;           // :29 (global z)
+    const float t2 = bz - c[11];                                   // :35
+    e0 = make_float4(c[4] * t1, c[5] * t1, c[6] * t1, 0.0f);
+    e1 = make_float4(c[8] * t2, c[9] * t2, c[10] * t2, 0.0f);
+  }
+}
+
 // One voxel update, src/tsdf.cu:54-57 (+ colour).  WMODE: 0 general, 1 integer weights.
 template <bool COLOR, int MATH, int WMODE>
 __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, const Hit& h, float obs) {
@@ -323,96 +341,102 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   const int row0 = blockIdx.x * rows_per_block;
   if (row0 >= n_rows) return;  // batched launches size the grid for the largest instance
 
-  // block hull of the row terms (sparse kernel): order-preserving integer keys, [2k] min, [2k+1] max
-  __shared__ int hull[4 * NT * 2];
-  if constexpr (CULL == 2 && NF == 1)
-    if (threadIdx.x < 4 * NT * 2) hull[threadIdx.x] = (threadIdx.x & 1) ? INT_MIN : INT_MAX;
+  // ---- prologue 0 (sparse kernel): can ANY voxel of this block be touched? ----------------
+  // The computed camera coordinates of voxel k of row (slow, mid) are e(slow, mid) + p_k (ZFAST)
+  // or (p_k + y(mid)) + z(slow): every fp32 operation on the way is correctly rounded, hence
+  // weakly monotone in each operand, and the direction in which a coordinate moves with slow,
+  // mid or k is fixed by the sign of one pose coefficient.  So over the index box
+  // [s0, s1] x [mlo, mhi] x [a, b] that contains the block's voxels, each computed coordinate lies
+  // between the values the SAME operation sequence gives at the box's corners — in fp32, no error
+  // analysis.  One box_is_skipped on that hull, by warp 0 while the other warps build the row
+  // table (the kernel is issue-bound on sparse frames: 8 warps repeating the test cost 17 % of all
+  // warp instructions on S-kitti), lets a block outside the frustum, behind the camera or behind
+  // everything the frame sees leave at the row-table barrier.
+  __shared__ int blk_skip;
+  const bool blk_test = CULL == 2 && NF == 1 && (flags & 4);
+  if constexpr (CULL == 2 && NF == 1) {
+    if (blk_test && threadIdx.x < 32) {
+      const int r_last = min(row0 + rows_per_block, n_rows) - 1;
+      const int s0 = row0 / g.n_mid, s1 = r_last / g.n_mid;
+      const int mlo = s0 == s1 ? row0 - s0 * g.n_mid : 0;
+      const int mhi = s0 == s1 ? r_last - s0 * g.n_mid : g.n_mid - 1;
+      const float* c = P.f[0].c;
+      float elo[3], ehi[3], zlo[3] = {0.f, 0.f, 0.f}, zhi[3] = {0.f, 0.f, 0.f};
+      float4 e[2], z4[2];
+      if constexpr (ZFAST) {
+        float4 q[4];
+        row_terms<ZFAST>(g, c, s0, mlo, q[0], z4[0]);
+        row_terms<ZFAST>(g, c, s0, mhi, q[1], z4[0]);
+        row_terms<ZFAST>(g, c, s1, mlo, q[2], z4[0]);
+        row_terms<ZFAST>(g, c, s1, mhi, q[3], z4[0]);
+        e[0] = make_float4(fminf(fminf(q[0].x, q[1].x), fminf(q[2].x, q[3].x)), fminf(fminf(q[0].y, q[1].y), fminf(q[2].y, q[3].y)),
+                           fminf(fminf(q[0].z, q[1].z), fminf(q[2].z, q[3].z)), 0.f);
+        e[1] = make_float4(fmaxf(fmaxf(q[0].x, q[1].x), fmaxf(q[2].x, q[3].x)), fmaxf(fmaxf(q[0].y, q[1].y), fmaxf(q[2].y, q[3].y)),
+                           fmaxf(fmaxf(q[0].z, q[1].z), fmaxf(q[2].z, q[3].z)), 0.f);
+        // a non-finite corner must disable the test (fminf / fmaxf drop NaN operands)
+        const float chk = ((q[0].x + q[1].x) + (q[2].x + q[3].x)) + ((q[0].y + q[1].y) + (q[2].y + q[3].y)) +
+                          ((q[0].z + q[1].z) + (q[2].z + q[3].z));
+        if (!(fabsf(chk) <= 3.0e38f)) e[0].x = __int_as_float(0x7fc00000);
+      } else {
+        float4 ya, yb, za, zb;
+        row_terms<ZFAST>(g, c, s0, mlo, ya, za);
+        row_terms<ZFAST>(g, c, s1, mhi, yb, zb);
+        e[0] = make_float4(fminf(ya.x, yb.x), fminf(ya.y, yb.y), fminf(ya.z, yb.z), 0.f);
+        e[1] = make_float4(fmaxf(ya.x, yb.x), fmaxf(ya.y, yb.y), fmaxf(ya.z, yb.z), 0.f);
+        z4[0] = make_float4(fminf(za.x, zb.x), fminf(za.y, zb.y), fminf(za.z, zb.z), 0.f);
+        z4[1] = make_float4(fmaxf(za.x, zb.x), fmaxf(za.y, zb.y), fmaxf(za.z, zb.z), 0.f);
+        const float chk = ((ya.x + yb.x) + (ya.y + yb.y)) + ((ya.z + yb.z) + (za.x + zb.x)) + ((za.y + zb.y) + (za.z + zb.z));
+        if (!(fabsf(chk) <= 3.0e38f)) e[0].x = __int_as_float(0x7fc00000);
+        zlo[0] = z4[0].x; zlo[1] = z4[0].y; zlo[2] = z4[0].z;
+        zhi[0] = z4[1].x; zhi[1] = z4[1].y; zhi[2] = z4[1].z;
+      }
+      elo[0] = e[0].x; elo[1] = e[0].y; elo[2] = e[0].z;
+      ehi[0] = e[1].x; ehi[1] = e[1].y; ehi[2] = e[1].z;
+      const int tprb = 1 << tpr_log2;
+      const int a = blockIdx.y * tprb * VEC;
+      int b = a + tprb * VEC - 1;
+      if (b > g.n_fast - 1) b = g.n_fast - 1;
+      float pa[3], pb[3], lo[3], hi[3];
+      fast_terms<ZFAST>(c, fast_coord<ZFAST>(g, a), pa[0], pa[1], pa[2]);
+      fast_terms<ZFAST>(c, fast_coord<ZFAST>(g, b), pb[0], pb[1], pb[2]);
+#pragma unroll
+      for (int k = 0; k < 3; ++k) {
+        const float plo = fminf(pa[k], pb[k]), phi = fmaxf(pa[k], pb[k]);
+        if constexpr (ZFAST) {
+          lo[k] = elo[k] + plo;
+          hi[k] = ehi[k] + phi;
+        } else {
+          lo[k] = (plo + elo[k]) + zlo[k];
+          hi[k] = (phi + ehi[k]) + zhi[k];
+        }
+      }
+      // (a NaN planted above, or produced by the additions, fails box_is_skipped's finiteness test)
+      const bool skip = box_is_skipped(P.f[0], g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                                       reinterpret_cast<const int*>(P.f[0].dmax));
+      if (threadIdx.x == 0) blk_skip = skip;
+    }
+  }
 
   // ---- prologue 1: per-row terms of the camera transform -> shared memory ---------------
-  for (int lr = threadIdx.x; lr < rows_per_block; lr += kThreads) {
+  // (warps 1-7 when warp 0 runs the block test: 224 threads cover the <= 128 rows in one pass)
+  const int t_first = blk_test ? 32 : 0;
+  for (int lr = (int)threadIdx.x - t_first; lr < rows_per_block; lr += kThreads - t_first) {
     int r = row0 + lr;
-    if (r < n_rows) {
+    if (lr >= 0 && r < n_rows) {
       int slow = r / g.n_mid, mid = r - slow * g.n_mid;
-      float by = g.oy + (float)mid * g.vs;                         // :28
 #pragma unroll
       for (int f = 0; f < NF; ++f) {
-        const float* c = P.f[f].c;
-        float t1 = by - c[7];                                      // :34
         float4* e = tab + (lr * NF + f) * NT;
-        if constexpr (ZFAST) {
-          float bx = g.ox + (float)slow * g.vs;                    // :27
-          float t0 = bx - c[3];                                    // :33
-          e[0] = make_float4(c[0] * t0 + c[4] * t1, c[1] * t0 + c[5] * t1, c[2] * t0 + c[6] * t1, 0.0f);
-        } else {
-          float bz = g.oz + (float)(g.z0 + slow) * g.vs;           // :29 (global z)
-          float t2 = bz - c[11];                                   // :35
-          e[0] = make_float4(c[4] * t1, c[5] * t1, c[6] * t1, 0.0f);
-          e[1] = make_float4(c[8] * t2, c[9] * t2, c[10] * t2, 0.0f);
-        }
+        float4 e0, e1;
+        row_terms<ZFAST>(g, P.f[f].c, slow, mid, e0, e1);
+        e[0] = e0;
+        if constexpr (!ZFAST) e[1] = e1;
       }
     }
   }
   __syncthreads();
-
-  // ---- prologue 1b (sparse kernel): can ANY voxel of this block be touched? ---------------
-  // The computed camera coordinates of voxel k of row r are e_r + p_k (ZFAST) or (p_k + y_r) + z_r:
-  // fp32 additions, weakly monotone in each operand.  With [elo, ehi] the component-wise hull of
-  // the block's row terms and [plo, phi] that of the fast-axis terms at the two ends of the
-  // block's fast-axis window (monotone in k, as in box_is_skipped), the same additions applied to
-  // the hull ends bound every voxel's computed coordinates — in fp32, no error analysis.  One box
-  // test on that hull, identical in every thread, lets a block outside the frustum (or behind
-  // everything the frame sees) leave before the per-warp tests and the row loop.
-  if constexpr (CULL == 2 && NF == 1) {
-    if (flags & 4) {
-      bool bad = false;
-      if (threadIdx.x < kMaxRowsPerBlock) {             // whole warps: rows_per_block <= 128
-        const int lr = threadIdx.x;
-        const bool valid = lr < rows_per_block && row0 + lr < n_rows;
-        float v[4 * NT];
-#pragma unroll
-        for (int t = 0; t < NT; ++t) {
-          const float4 e = valid ? tab[lr * NT + t] : make_float4(0.f, 0.f, 0.f, 0.f);
-          v[4 * t] = e.x; v[4 * t + 1] = e.y; v[4 * t + 2] = e.z; v[4 * t + 3] = 0.0f;
-        }
-#pragma unroll
-        for (int i = 0; i < 4 * NT; ++i) {
-          if ((i & 3) == 3) continue;
-          bad = bad || (valid && !(fabsf(v[i]) <= 3.0e38f));
-          const int key = em::order_key(v[i]);
-          const int kmin = __reduce_min_sync(0xffffffffu, valid ? key : INT_MAX);
-          const int kmax = __reduce_max_sync(0xffffffffu, valid ? key : INT_MIN);
-          if ((threadIdx.x & 31) == 0) { atomicMin(&hull[2 * i], kmin); atomicMax(&hull[2 * i + 1], kmax); }
-        }
-      }
-      if (!__syncthreads_or(bad)) {
-        const int tprb = 1 << tpr_log2;
-        const int a = blockIdx.y * tprb * VEC;
-        int b = a + tprb * VEC - 1;
-        if (b > g.n_fast - 1) b = g.n_fast - 1;
-        float pa0, pa1, pa2, pb0, pb1, pb2;
-        fast_terms<ZFAST>(P.f[0].c, fast_coord<ZFAST>(g, a), pa0, pa1, pa2);
-        fast_terms<ZFAST>(P.f[0].c, fast_coord<ZFAST>(g, b), pb0, pb1, pb2);
-        float lo[3], hi[3];
-        const float plo[3] = {fminf(pa0, pb0), fminf(pa1, pb1), fminf(pa2, pb2)};
-        const float phi[3] = {fmaxf(pa0, pb0), fmaxf(pa1, pb1), fmaxf(pa2, pb2)};
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          const float e0lo = em::order_unkey(hull[2 * k]), e0hi = em::order_unkey(hull[2 * k + 1]);
-          if constexpr (ZFAST) {
-            lo[k] = e0lo + plo[k];
-            hi[k] = e0hi + phi[k];
-          } else {
-            const float e1lo = em::order_unkey(hull[2 * (4 + k)]), e1hi = em::order_unkey(hull[2 * (4 + k) + 1]);
-            lo[k] = (plo[k] + e0lo) + e1lo;
-            hi[k] = (phi[k] + e0hi) + e1hi;
-          }
-        }
-        if (box_is_skipped(P.f[0], g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
-                           reinterpret_cast<const int*>(P.f[0].dmax)))
-          return;   // block-uniform: every thread took the same decision
-      }
-    }
-  }
+  if constexpr (CULL == 2 && NF == 1)
+    if (blk_test && blk_skip) return;   // block-uniform
 
   // ---- this thread's run on the fast axis -----------------------------------------------
   const int tpr = 1 << tpr_log2;
