@@ -114,3 +114,85 @@ class ShardedVolume:
             self.lib.tsdf_comm_destroy(self.comm)
             self.comm = None
         self.vol.close()
+
+
+def plan_instances(sizes, world):
+    """Instance volumes (BASELINE config 5) shard by instance, not by z: largest
+    first, each to the rank with the fewest voxels so far (ties: lowest rank).  Deterministic, so
+    every rank computes the same plan without communication.  Returns owner[i] for every instance."""
+    load = [0] * world
+    owner = [0] * len(sizes)
+    for i in sorted(range(len(sizes)), key=lambda k: (-int(sizes[k]), k)):
+        r = min(range(world), key=lambda k: (load[k], k))
+        owner[i] = r
+        load[r] += int(sizes[i])
+    return owner
+
+
+def share_of_active(local, active, boxes=None, crops=None, masks=None):
+    """One rank's share of a keyframe's active list.  local: {global instance -> index in this
+    rank's batch}.  Returns (local indices, boxes, concatenated crops, full masks) of the active
+    instances this rank owns, in the order of `active`."""
+    keep = [k for k, g in enumerate(active) if g in local]
+    loc = np.array([local[active[k]] for k in keep], np.int32)
+    bx = cr = mk = None
+    if boxes is not None:
+        b = np.asarray(boxes, np.int32).reshape(-1, 4)
+        off = np.concatenate([[0], np.cumsum(b[:, 2].astype(np.int64) * b[:, 3])])
+        bx = np.ascontiguousarray(b[keep])
+        parts = [np.asarray(crops)[off[k]:off[k + 1]] for k in keep]
+        cr = np.ascontiguousarray(np.concatenate(parts) if parts else np.zeros(0, np.uint8), np.uint8)
+    if masks is not None:
+        mk = np.ascontiguousarray(np.asarray(masks)[keep])
+    return loc, bx, cr, mk
+
+
+class ShardedBatch:
+    """Per-object volumes of one keyframe spread over the ranks by instance.  No data-path
+    collective: a keyframe's depth / colour / masks are on every rank's host (in the off-line
+    replay of examples/label_instance_rgbd.cpp:79-110 every rank reads the same files), each rank
+    launches one batched integrate over the active instances it owns."""
+
+    def __init__(self, cfgs, rank, world, device):
+        from .volume import Batch
+        self.rank, self.world = rank, world
+        sizes = [c.dim_x * c.dim_y * c.dim_z for c in cfgs]
+        self.owner = plan_instances(sizes, world)
+        self.mine = [i for i, r in enumerate(self.owner) if r == rank]
+        self.local = {g: k for k, g in enumerate(self.mine)}
+        for i in self.mine:
+            cfgs[i].device = int(device)
+        self.batch = Batch([cfgs[i] for i in self.mine]) if self.mine else None
+
+    def split_active(self, active, boxes=None, crops=None, masks=None):
+        return share_of_active(self.local, active, boxes, crops, masks)
+
+    def integrate_boxes(self, depth, rgb, active, boxes, crops, T_wc, K=None, obs_weight=1.0, sync=False):
+        loc, bx, cr, _ = self.split_active(active, boxes, crops)
+        if len(loc):
+            self.batch.integrate_boxes(depth, rgb, loc, bx, cr, T_wc, K, obs_weight, sync)
+        return len(loc)
+
+    def integrate(self, depth, rgb, active, masks, T_wc, K=None, obs_weight=1.0, sync=False):
+        loc, _, _, mk = self.split_active(active, masks=masks)
+        if len(loc):
+            self.batch.integrate(depth, rgb, loc, mk, T_wc, K, obs_weight, sync)
+        return len(loc)
+
+    def sync(self):
+        if self.batch is not None:
+            self.batch.sync()
+
+    def voxels_written(self):
+        """This rank's count for its last launch (sum over ranks = the keyframe's total)."""
+        return self.batch.stats().voxels_written if self.batch is not None else 0
+
+    def download(self, i):
+        """Instance i (global index); only on its owner."""
+        assert i in self.local, f"instance {i} lives on rank {self.owner[i]}"
+        return self.batch.download(self.local[i])
+
+    def close(self):
+        if self.batch is not None:
+            self.batch.close()
+            self.batch = None

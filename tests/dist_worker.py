@@ -62,6 +62,38 @@ def main():
                 assert np.array_equal(rgbp, orgb)
         sv.close()
         dist.barrier()
+    # ---- instance volumes: sharded by instance, no data-path collective ----
+    n_inst, idims, ivs = 7, (32, 32, 32), 0.02
+    _, fr = synth.s_real((64, 64, 64), 0.08, n_frames=3, seed=93)
+    masks, boxes = synth.instance_masks(n_inst, seed=94)
+    origins = [o.instance_origin(fr[0][0], masks[i], synth.TUM3_K) for i in range(n_inst)]
+    cfgs = [pkg.make_config(idims, ivs, origins[i], semantics=SEM_FUSIONPY, with_color=True, vol_id=i)
+            for i in range(n_inst)]
+    sb = pkg.dist.ShardedBatch(cfgs, rank, world, local)
+    active_sets = [list(range(n_inst)), [3, 1, 6], [4, 0, 2, 5]]
+    written = 0
+    for (d, rgb, T), act in zip(fr, active_sets):
+        bx, crops = pkg.Batch.crop_masks(masks[act], boxes[act])
+        if sb.integrate_boxes(d, rgb, act, bx, crops, T, sync=True):
+            written += sb.voxels_written()
+    tot = torch.tensor([written], dtype=torch.int64, device=dev)
+    dist.all_reduce(tot)
+    want = 0
+    for i in range(n_inst):
+        p = o.params(idims, ivs, np.float32(ivs) * np.float32(5), origins[i], synth.TUM3_HW, synth.TUM3_K, np.inf, SEM_FUSIONPY)
+        t, w, c = o.new_volume(p, True)
+        for (d, rgb, T), act in zip(fr, active_sets):
+            if i in act:
+                md = (d * (masks[i] >= 128)).astype(np.float32)
+                want += o.integrate(p, T.reshape(16), md, o.pack_color(rgb), 1.0, t, w, c)
+        if sb.owner[i] == rank:
+            gt, gw, gc = sb.download(i)
+            assert np.array_equal(gw, w) and np.array_equal(gt.view(np.uint32), t.view(np.uint32)) and np.array_equal(gc, c), \
+                f"rank {rank}: instance {i} differs"
+    assert int(tot.item()) == want, (int(tot.item()), want)
+    assert sorted(i for r in range(world) for i, ow in enumerate(sb.owner) if ow == r) == list(range(n_inst))
+    sb.close()
+    dist.barrier()
     dist.destroy_process_group()
     if rank == 0:
         print("dist_worker ok", world, mode)

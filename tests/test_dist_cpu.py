@@ -40,6 +40,33 @@ def _worker(rank, world, port, q):
             parts.append((np.stack([sel] * 3, 1).astype(np.float32), np.zeros((len(sel), 3), np.uint8), sel))
         xyz, rgb, idx = pkg.dist.merge_by_index(parts)
         assert np.array_equal(idx, idx_all) and np.array_equal(xyz[:, 0], idx_all.astype(np.float32))
+        # 5. instance volumes shard by instance: same plan on every rank, every instance owned once,
+        #    loads within one largest volume of each other; a keyframe's active list, boxes and
+        #    concatenated mask crops split into per-rank shares that together cover it exactly
+        sizes = [int(x) for x in rng.integers(16, 129, 37) ** 3]
+        owner = pkg.dist.plan_instances(sizes, world)
+        t = torch.tensor(owner)
+        dist.broadcast(t, src=0)
+        assert t.tolist() == owner and set(owner) <= set(range(world))
+        loads = [sum(sz for sz, o in zip(sizes, owner) if o == r) for r in range(world)]
+        assert max(loads) - min(loads) <= max(sizes)
+        active = [int(x) for x in rng.permutation(37)[:20]]
+        boxes = rng.integers(1, 40, (20, 4)).astype(np.int32)
+        crops = np.concatenate([np.full(int(b[2]) * int(b[3]), g, np.uint8) for g, b in zip(active, boxes)])
+        seen = []
+        for r in range(world):
+            mine = [i for i, o in enumerate(owner) if o == r]
+            local = {g: k for k, g in enumerate(mine)}
+            loc, bx, cr, _ = pkg.dist.share_of_active(local, active, boxes, crops)
+            off = 0
+            for k, b in zip(loc, bx):
+                g = mine[int(k)]
+                n = int(b[2]) * int(b[3])
+                assert (cr[off:off + n] == g).all() and np.array_equal(b, boxes[active.index(g)])
+                off += n
+                seen.append(g)
+            assert off == len(cr)
+        assert sorted(seen) == sorted(active)
         q.put((rank, "ok"))
     except Exception as e:  # pragma: no cover
         q.put((rank, repr(e)))
