@@ -744,14 +744,15 @@ void balance_waves(Geometry* q, int n_rows, int slots) {
 }
 
 int device_sm_count() {
-  static int sms[64] = {0};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 0;
-  if (!sms[dev]) {
-    int n = 0;
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess) sms[dev] = n;
-  }
-  return sms[dev];
+  // every GPU of a box is the same part; queried once (thread-safe static initialisation)
+  static const int sms = [] {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      n = 0;
+    return n;
+  }();
+  return sms;
 }
 
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE>
@@ -764,10 +765,15 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   // compact tile (128 rows x 128 voxels) the block-level hull test can reject as a whole
   Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult, (o.kernel == 1 && o.compact) ? 32 : kThreads);
   if (o.kernel == 0 && o.balance) {
-    static int occ = 0;   // resident blocks per SM of this instantiation (same on every B200)
-    if (!occ && cudaOccupancyMaxActiveBlocksPerMultiprocessor(
-                    &occ, k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0>, kThreads, 0) != cudaSuccess)
-      occ = 0;
+    // resident blocks per SM of this instantiation (same on every B200); C++11 static
+    // initialisation is thread-safe: handles may be driven from different host threads
+    static const int occ = [] {
+      int n = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+              &n, k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0>, kThreads, 0) != cudaSuccess)
+        n = 0;
+      return n;
+    }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));

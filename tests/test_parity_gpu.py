@@ -616,3 +616,50 @@ def test_more_than_2_31_voxels(pkg, oracle, synth, sem):
         assert touched > 10 ** 4
         with pytest.raises(Exception):
             vol.download_range(n - 10, 11)
+
+
+def test_handles_driven_from_different_host_threads(pkg, oracle, synth):
+    """Threading contract of the boundary: each handle is single-writer, different
+    handles may be driven from different host threads (the reference's mask loop,
+    src/Engine.cpp:172, is annotated `omp parallel for`).  Four threads, four volumes of
+    different shapes and semantics, interleaved async launches (ctypes drops the GIL during the
+    calls): every volume must equal its own oracle run, and the per-thread error slots must not
+    leak into each other."""
+    import threading
+    cases = [((64, 48, 64), SEM_FUSIONPY, True, 21), ((50, 44, 38), SEM_TSDFCU, False, 22),
+             ((200, 40, 36), SEM_FUSIONPY, False, 23), ((36, 40, 132), SEM_TSDFCU, False, 24)]
+    jobs = []
+    for dims, sem, color, seed in cases:
+        origin, frames = synth.s_real(dims, 0.03, n_frames=6, seed=seed)
+        p, t, w, c, written = oracle_run(oracle, dims, 0.03, origin, frames, sem, color)
+        jobs.append((pkg.make_config(dims, 0.03, origin, semantics=sem, with_color=color), frames, color, (t, w, c), written))
+    out, errs = [None] * len(jobs), []
+    start = threading.Barrier(len(jobs))
+
+    def run(k):
+        cfg, frames, color, _, written = jobs[k]
+        try:
+            with pkg.Volume(cfg) as vol:
+                start.wait()
+                for rep in range(3):                      # same frames three times: reset in between
+                    vol.reset()
+                    for (d, rgb, T), ow in zip(frames, written):
+                        vol.integrate(d, rgb if color else None, T, sync=False)
+                    assert vol.stats().voxels_written == written[-1]
+                    if k == 0 and rep == 1:               # a failing call on this thread only
+                        with pytest.raises(Exception):
+                            vol.download_range(vol.n_local, 1)
+                        assert "range" in pkg.load().tsdf_last_error().decode()
+                out[k] = vol.download()
+        except BaseException as e:   # noqa: BLE001
+            errs.append((k, repr(e)))
+
+    threads = [threading.Thread(target=run, args=(k,)) for k in range(len(jobs))]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join(timeout=240)
+    assert not errs, errs
+    for k, (_, _, _, (t, w, c), _) in enumerate(jobs):
+        assert out[k] is not None
+        assert_volume_equal(out[k][0], out[k][1], out[k][2], t, w, c)
