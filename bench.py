@@ -467,12 +467,29 @@ def extras(pkg, line, frames, origin, vol=None):
             t0 = time.perf_counter()
             pts = v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5)   # reuses the mark pass above: emit + D2H only
             ext_full_ms = (time.perf_counter() - t0) * 1e3
+            # mesh readback (plugin SaveMesh): the first count call also allocates the scratch, so the
+            # sweep is timed on a second one after an epoch bump (re-upload of nothing = reset of the cache)
+            mesh = {}
+            try:
+                v2.mesh_count()
+                v2.upload()                       # no arrays: only invalidates the cached sweeps
+                t0 = time.perf_counter()
+                mnv, mnf = v2.mesh_count()
+                mesh_sweep_ms = (time.perf_counter() - t0) * 1e3
+                t0 = time.perf_counter()
+                v2.extract_mesh()                 # reuses the sweep: vertex + face kernels + D2H
+                mesh_emit_ms = (time.perf_counter() - t0) * 1e3
+                mesh = {"mesh_sweep_ms": mesh_sweep_ms, "mesh_emit_to_host_ms": mesh_emit_ms,
+                        "mesh_sweep_GBps": 5.5 * 512 ** 3 / (mesh_sweep_ms * 1e-3) / 1e9,
+                        "mesh_vertices": mnv, "mesh_faces": mnf}
+            except Exception as e:
+                mesh = {"mesh_error": str(e)}
         line["extra_c2"] = {"workload": "C2: 300 frames (12 distinct, fr3_office keyframe poses) into 512^3 @ 1 cm, "
                                         "scene S-real, pageable host frames through tsdf_integrate_async",
                             "value": nfr * 512 ** 3 / (ms * 1e-3) / 1e9, "unit": UNIT, "frames_per_sec": nfr / (ms * 1e-3),
                             "kernel_ms": ksum / max(kn, 1), "coverage_last_frame": wr / 512 ** 3,
                             "extract_count_ms": ext_ms, "extract_emit_to_host_ms": ext_full_ms,
-                            "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts}
+                            "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts, **mesh}
     except Exception as e:
         line["extra_c2"] = {"error": str(e)}
     # The reference's own GPU kernel (lifted verbatim, nvcc defaults) on this box, as the bar to

@@ -92,8 +92,28 @@ class TSDFfusion {
   }
 #endif
 
-  /// Headless replacement of SaveMesh (src/TSDFfusion.py.in:48-53; viewers and skimage are
-  /// unavailable on this box): surface voxels as xyz (+rgb) — returns the point count.
+  /// verts, faces, norms, colors = tsdf_vol.get_mesh() (src/TSDFfusion.py.in:52): marching cubes
+  /// on the device.  Returns the vertex count; faces holds 3 indices per triangle.
+  int64_t GetMesh(std::vector<float>& verts, std::vector<int32_t>& faces, std::vector<float>& norms,
+                  std::vector<uint8_t>& colors) {
+    int64_t nv = 0, nf = 0;
+    check(tsdf_extract_mesh(vol_, nullptr, nullptr, nullptr, 0, nullptr, 0, &nv, &nf), "mesh count");
+    verts.resize((size_t)nv * 3);
+    norms.resize((size_t)nv * 3);
+    colors.resize((size_t)nv * 3);
+    faces.resize((size_t)nf * 3);
+    if (nv)
+      check(tsdf_extract_mesh(vol_, verts.data(), norms.data(), colors.data(), nv, faces.data(), nf, &nv, &nf),
+            "tsdf_extract_mesh");
+    return nv;
+  }
+  /// SaveMesh(file_name) (src/TSDFfusion.py.in:48-53): get_mesh() + fusion.meshwrite.  The reference
+  /// ignores file_name and always writes "mesh.ply" (:53); here the name is honoured.
+  void SaveMesh(const std::string& file_name) {
+    check(tsdf_save_mesh_ply(vol_, file_name.c_str()), "tsdf_save_mesh_ply");
+  }
+
+  /// Point-cloud readback (surface voxels as xyz + rgb) beside the mesh — returns the point count.
   int64_t GetPointCloud(std::vector<float>& xyz, std::vector<uint8_t>& rgb, float tsdf_thresh = 1.2f,
                         float weight_thresh = 0.9f, int predicate = TSDF_PRED_NONZERO) {
     int64_t n = 0;

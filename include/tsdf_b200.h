@@ -185,6 +185,29 @@ int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh, float wei
 int tsdf_extract_points_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
                                float* d_xyz, uint8_t* d_rgb, int64_t* d_idx, int64_t cap,
                                int64_t* count);
+/* Triangle-mesh readback: replaces fusion.TSDFVolume.get_mesh(), called by the plugin's
+ * SaveMesh (src/TSDFfusion.py.in:48-53).  Level-0 marching cubes of the handle's tsdf array
+ * (no weight mask, as upstream), on the device: indexed mesh, one vertex per sign-crossing grid
+ * edge in ascending (storage index, axis) order, faces by ascending cell index.
+ *   verts  3*vcap floats  origin + (index + t)*voxel_size, t = a/(a-b) along the edge
+ *   norms  3*vcap floats  unit tsdf gradient (towards free space), or NULL
+ *   colors 3*vcap u8      {c0,c1,c2} of the voxel nearest to the vertex, or NULL
+ *   faces  3*fcap int32   vertex indices, triangles wound so that their normal points to free
+ *                         space (tsdf > 0)
+ * *n_verts / *n_faces always receive the counts; all four arrays NULL = sizing call (its sweep
+ * is reused by the next call while the volume is unchanged).  TSDF_E_CAPACITY if a given array
+ * is too small (nothing written).  A z-slab handle meshes its own slab; cells across a slab
+ * face belong to neither side.  Vertex/face ORDER is this library's, not skimage's.          */
+int tsdf_extract_mesh(tsdf_vol* v, float* verts, float* norms, uint8_t* colors, int64_t vcap,
+                      int32_t* faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
+/* Same, outputs stay on the device (pointers are device pointers).          */
+int tsdf_extract_mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_colors,
+                             int64_t vcap, int32_t* d_faces, int64_t fcap, int64_t* n_verts,
+                             int64_t* n_faces);
+/* fusion.meshwrite(filename, verts, faces, norms, colors) (src/TSDFfusion.py.in:53): ascii PLY
+ * with x y z nx ny nz red green blue per vertex and "3 i j k" per face.  Whole-grid handles
+ * only.                                                                                      */
+int tsdf_save_mesh_ply(tsdf_vol* v, const char* path);
 /* Byte-compatible writers: PLY header src/tsdf.cu:186-192 + float x,y,z;
  * BIN = 8-float header + tsdf array (src/tsdf.cu:116-132).  Whole-grid
  * handles only.  tsdf_load_bin restores tsdf (weights are not in the file). */

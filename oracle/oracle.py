@@ -37,7 +37,8 @@ def build(force=False):
     """Compile liboracle*.so (and oracle/_ref when /root/reference is present)."""
     need = force or not os.path.exists(os.path.join(HERE, "liboracle.so")) \
         or not os.path.exists(os.path.join(HERE, "liboracle_omp.so")) \
-        or os.path.getmtime(os.path.join(HERE, "liboracle.so")) < os.path.getmtime(os.path.join(HERE, "tsdf_oracle.c"))
+        or os.path.getmtime(os.path.join(HERE, "liboracle.so")) < max(
+            os.path.getmtime(os.path.join(HERE, "tsdf_oracle.c")), os.path.getmtime(os.path.join(HERE, "mc_table.inc")))
     if need:
         subprocess.check_call(["make", "-C", HERE, "liboracle.so", "liboracle_omp.so"],
                               stdout=subprocess.DEVNULL)
@@ -78,6 +79,11 @@ class Oracle:
         L.oracle_range_to_depth.restype = None
         L.oracle_save_bin.restype = C.c_int
         L.oracle_save_bin.argtypes = [C.c_char_p, C.POINTER(OracleParams), _f32p]
+        L.oracle_mesh.restype = C.c_int64
+        L.oracle_mesh.argtypes = [C.POINTER(OracleParams), _f32p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                  C.c_void_p, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]
+        L.oracle_save_mesh_ply.restype = C.c_int
+        L.oracle_save_mesh_ply.argtypes = [C.c_char_p, _f32p, _f32p, _u8p, C.c_int64, C.c_void_p, C.c_int64]
         L.oracle_save_ply.restype = C.c_int
         L.oracle_save_ply.argtypes = [C.c_char_p, C.POINTER(OracleParams), _f32p, _f32p, C.c_int,
                                       C.c_float, C.c_float]
@@ -161,6 +167,27 @@ class Oracle:
                                 np.float32(weight_thresh), xyz.ctypes.data, rgb.ctypes.data,
                                 idx.ctypes.data, n)
         return xyz[:n], rgb[:n], idx[:n]
+
+    def mesh(self, p, tsdf, color):
+        """Level-0 marching cubes of the slab's tsdf array (restated get_mesh(), see tsdf_oracle.c):
+        verts (nv,3) f32, faces (nf,3) i32, norms (nv,3) f32, colors (nv,3) u8."""
+        cv = None if color is None else color.ctypes.data
+        nf = C.c_int64(0)
+        nv = int(self.lib.oracle_mesh(C.byref(p), tsdf, cv, None, None, None, 0, None, 0, C.byref(nf)))
+        verts = np.zeros((max(nv, 1), 3), np.float32)
+        norms = np.zeros((max(nv, 1), 3), np.float32)
+        cols = np.zeros((max(nv, 1), 3), np.uint8)
+        faces = np.zeros((max(nf.value, 1), 3), np.int32)
+        self.lib.oracle_mesh(C.byref(p), tsdf, cv, verts.ctypes.data, norms.ctypes.data, cols.ctypes.data,
+                             nv, faces.ctypes.data, nf.value, C.byref(nf))
+        return verts[:nv], faces[:nf.value], norms[:nv], cols[:nv]
+
+    def save_mesh_ply(self, path, verts, faces, norms, colors):
+        return bool(self.lib.oracle_save_mesh_ply(
+            path.encode(), np.ascontiguousarray(verts, np.float32).reshape(-1),
+            np.ascontiguousarray(norms, np.float32).reshape(-1),
+            np.ascontiguousarray(colors, np.uint8).reshape(-1), len(verts),
+            np.ascontiguousarray(faces, np.int32).ctypes.data, len(faces)))
 
     def instance_origin(self, depth, mask, K):
         H, W = depth.shape

@@ -7,4 +7,4 @@ TSDF / TSDFfusion surface over that ABI.  Import with
 from . import capi, synth, volume, dist  # noqa: F401
 from .capi import (SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO, PRED_ABS_LT, TsdfError, load)  # noqa: F401
 from .volume import (Volume, Batch, TSDF, TSDFVolume, make_config, config_from_bounds, default_config,
-                     slab_range, device_count)  # noqa: F401
+                     slab_range, device_count, meshwrite)  # noqa: F401

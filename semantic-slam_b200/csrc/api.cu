@@ -166,7 +166,7 @@ static void free_vol(tsdf_vol* v) {
     if (s.consumed) cudaEventDestroy(s.consumed);
   }
   cudaFree(v->d_tsdf); cudaFree(v->d_weight); cudaFree(v->d_color);
-  cudaFree(v->d_written); cudaFree(v->d_scratch);
+  cudaFree(v->d_written); cudaFree(v->d_scratch); cudaFree(v->d_mesh);
   if (v->h_written) cudaFreeHost(v->h_written);
   for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1, v->ev_t0, v->ev_t1}) if (e) cudaEventDestroy(e);
   for (cudaEvent_t e : v->kev) cudaEventDestroy(e);
@@ -654,6 +654,89 @@ extern "C" int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh
   }
   cleanup();
   return rc;
+}
+
+// ---- mesh readback (plugin SaveMesh, src/TSDFfusion.py.in:48-53) -------------------------------
+extern "C" int tsdf_extract_mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_colors,
+                                        int64_t vcap, int32_t* d_faces, int64_t fcap, int64_t* n_verts,
+                                        int64_t* n_faces) {
+  REQUIRE(v && n_verts && n_faces, "null argument");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  return mesh_device(v, d_verts, d_norms, d_colors, vcap, d_faces, fcap, n_verts, n_faces);
+}
+
+extern "C" int tsdf_extract_mesh(tsdf_vol* v, float* verts, float* norms, uint8_t* colors, int64_t vcap,
+                                 int32_t* faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces) {
+  REQUIRE(v && n_verts && n_faces, "null argument");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  int64_t nv = 0, nf = 0;
+  rc = mesh_device(v, nullptr, nullptr, nullptr, 0, nullptr, 0, &nv, &nf);
+  if (rc) return rc;
+  *n_verts = nv;
+  *n_faces = nf;
+  if (!verts && !norms && !colors && !faces) return TSDF_OK;
+  if ((verts || norms || colors) && vcap < nv) {
+    tsdf_set_error("tsdf_extract_mesh: vertex capacity %lld < %lld", (long long)vcap, (long long)nv);
+    return TSDF_E_CAPACITY;
+  }
+  if (faces && fcap < nf) {
+    tsdf_set_error("tsdf_extract_mesh: face capacity %lld < %lld", (long long)fcap, (long long)nf);
+    return TSDF_E_CAPACITY;
+  }
+  float* d_v = nullptr; float* d_n = nullptr; uint8_t* d_c = nullptr; int32_t* d_f = nullptr;
+  auto cleanup = [&]() { cudaFree(d_v); cudaFree(d_n); cudaFree(d_c); cudaFree(d_f); };
+  cudaError_t e = cudaSuccess;
+  if (verts && nv) e = cudaMalloc(&d_v, (size_t)nv * 12);
+  if (e == cudaSuccess && norms && nv) e = cudaMalloc(&d_n, (size_t)nv * 12);
+  if (e == cudaSuccess && colors && nv) e = cudaMalloc(&d_c, (size_t)nv * 3);
+  if (e == cudaSuccess && faces && nf) e = cudaMalloc(&d_f, (size_t)nf * 12);
+  if (e != cudaSuccess) { cleanup(); tsdf_set_error("mesh: output alloc: %s", cudaGetErrorString(e)); return TSDF_E_NOMEM; }
+  if (d_v || d_n || d_c || d_f) {
+    rc = mesh_device(v, d_v, d_n, d_c, nv, d_f, nf, &nv, &nf);
+    if (!rc) {
+      if (d_v) e = cudaMemcpy(verts, d_v, (size_t)nv * 12, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && d_n) e = cudaMemcpy(norms, d_n, (size_t)nv * 12, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && d_c) e = cudaMemcpy(colors, d_c, (size_t)nv * 3, cudaMemcpyDeviceToHost);
+      if (e == cudaSuccess && d_f) e = cudaMemcpy(faces, d_f, (size_t)nf * 12, cudaMemcpyDeviceToHost);
+      if (e != cudaSuccess) { tsdf_set_error("mesh: D2H: %s", cudaGetErrorString(e)); rc = TSDF_E_CUDA; }
+    }
+  }
+  cleanup();
+  return rc;
+}
+
+// fusion.meshwrite: ascii PLY, "%f %f %f %f %f %f %d %d %d" per vertex, "3 %d %d %d" per face.
+extern "C" int tsdf_save_mesh_ply(tsdf_vol* v, const char* path) {
+  REQUIRE(v && path, "null argument");
+  REQUIRE(v->dzl == v->cfg.dim_z, "tsdf_save_mesh_ply needs a whole-grid handle");
+  int64_t nv = 0, nf = 0;
+  int rc = tsdf_extract_mesh(v, nullptr, nullptr, nullptr, 0, nullptr, 0, &nv, &nf);
+  if (rc) return rc;
+  std::vector<float> verts((size_t)(nv ? nv : 1) * 3), norms((size_t)(nv ? nv : 1) * 3);
+  std::vector<uint8_t> cols((size_t)(nv ? nv : 1) * 3);
+  std::vector<int32_t> faces((size_t)(nf ? nf : 1) * 3);
+  if (nv) {
+    rc = tsdf_extract_mesh(v, verts.data(), norms.data(), cols.data(), nv, faces.data(), nf, &nv, &nf);
+    if (rc) return rc;
+  }
+  FILE* fp = fopen(path, "w");
+  if (!fp) { tsdf_set_error("tsdf_save_mesh_ply: cannot open %s", path); return TSDF_E_IO; }
+  fprintf(fp, "ply\nformat ascii 1.0\nelement vertex %d\n", (int)nv);
+  fprintf(fp, "property float x\nproperty float y\nproperty float z\n");
+  fprintf(fp, "property float nx\nproperty float ny\nproperty float nz\n");
+  fprintf(fp, "property uchar red\nproperty uchar green\nproperty uchar blue\n");
+  fprintf(fp, "element face %d\nproperty list uchar int vertex_index\nend_header\n", (int)nf);
+  for (int64_t i = 0; i < nv; ++i)
+    fprintf(fp, "%f %f %f %f %f %f %d %d %d\n", verts[3 * i], verts[3 * i + 1], verts[3 * i + 2], norms[3 * i],
+            norms[3 * i + 1], norms[3 * i + 2], cols[3 * i], cols[3 * i + 1], cols[3 * i + 2]);
+  for (int64_t i = 0; i < nf; ++i) fprintf(fp, "3 %d %d %d\n", faces[3 * i], faces[3 * i + 1], faces[3 * i + 2]);
+  const bool bad = ferror(fp) != 0;
+  if (fclose(fp) != 0 || bad) { tsdf_set_error("tsdf_save_mesh_ply: write failed"); return TSDF_E_IO; }
+  return TSDF_OK;
 }
 
 // PLY: header text of src/tsdf.cu:186-192, then float x,y,z per kept voxel.

@@ -140,6 +140,13 @@ struct tsdf_vol {
   int mark_pred = 0;
   float mark_tt = 0, mark_wt = 0;
   int64_t mark_total = 0;
+  // mesh readback scratch (mesh.cu): records, case bytes and offsets of the last mark pass, reused
+  // by the call that follows a sizing call while `epoch` is unchanged
+  void* d_mesh = nullptr;
+  size_t mesh_bytes = 0;
+  bool mesh_valid = false;
+  uint64_t mesh_epoch = 0;
+  int64_t mesh_nv = 0, mesh_nf = 0;
 };
 
 inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
@@ -181,6 +188,10 @@ int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, i
 int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh, float* d_xyz,
                    uint8_t* d_rgb, int64_t* d_idx, int64_t cap, int64_t* count);
 int ensure_scratch(tsdf_vol* v, size_t bytes);
+int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st);  // off[m] = total
+// mesh.cu
+int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, int64_t vcap,
+                int32_t* d_faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
 
 // api.cpp helpers used elsewhere
 int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);

@@ -192,6 +192,12 @@ k_emit(const uint32_t* __restrict__ ballots, const int64_t* __restrict__ tile_of
 
 }  // namespace
 
+int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st) {
+  k_scan<<<1, 1024, 0, st>>>(d_cnt, m, d_off);
+  CU_CHECK(cudaGetLastError());
+  return TSDF_OK;
+}
+
 int ensure_scratch(tsdf_vol* v, size_t bytes) {
   if (v->scratch_bytes >= bytes) return TSDF_OK;
   if (v->d_scratch) cudaFree(v->d_scratch);

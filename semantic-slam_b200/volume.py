@@ -242,6 +242,28 @@ class Volume:
         assert cnt.value == n
         return xyz[:n], rgb[:n], idx[:n]
 
+    def mesh_count(self):
+        nv, nf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_extract_mesh(self.h, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
+        return nv.value, nf.value
+
+    def extract_mesh(self):
+        """Level-0 marching cubes on the device: verts (nv,3) f32, faces (nf,3) i32, norms (nv,3) f32,
+        colors (nv,3) u8 — the tuple order of fusion.TSDFVolume.get_mesh()."""
+        nv, nf = self.mesh_count()
+        verts = np.zeros((max(nv, 1), 3), np.float32)
+        norms = np.zeros((max(nv, 1), 3), np.float32)
+        cols = np.zeros((max(nv, 1), 3), np.uint8)
+        faces = np.zeros((max(nf, 1), 3), np.int32)
+        cv, cf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_extract_mesh(self.h, ptr(verts), ptr(norms), ptr(cols), nv, ptr(faces), nf,
+                                         C.byref(cv), C.byref(cf)))
+        assert (cv.value, cf.value) == (nv, nf)
+        return verts[:nv], faces[:nf], norms[:nv], cols[:nv]
+
+    def save_mesh_ply(self, path):
+        check(self.lib.tsdf_save_mesh_ply(self.h, path.encode()))
+
     def save_ply(self, path, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
         check(self.lib.tsdf_save_ply(self.h, path.encode(), pred, np.float32(tsdf_thresh), np.float32(weight_thresh)))
 
@@ -403,5 +425,27 @@ class TSDFVolume:
         xyz, rgb, _ = self.vol.extract_points(pred, tsdf_thresh, weight_thresh)
         return xyz, rgb
 
+    def get_mesh(self):
+        """src/TSDFfusion.py.in:52 — verts, faces, norms, colors = tsdf_vol.get_mesh(); marching cubes
+        runs on the device (csrc/mesh.cu), vertex/face order is this library's."""
+        return self.vol.extract_mesh()
+
     def close(self):
         self.vol.close()
+
+
+def meshwrite(filename, verts, faces, norms, colors):
+    """fusion.meshwrite (src/TSDFfusion.py.in:53): ascii PLY of a mesh already on the host.  Pure file
+    formatting, no voxel is computed here; Volume.save_mesh_ply writes the same bytes from the C ABI."""
+    with open(filename, "w") as f:
+        f.write("ply\nformat ascii 1.0\nelement vertex %d\n" % verts.shape[0])
+        f.write("property float x\nproperty float y\nproperty float z\n")
+        f.write("property float nx\nproperty float ny\nproperty float nz\n")
+        f.write("property uchar red\nproperty uchar green\nproperty uchar blue\n")
+        f.write("element face %d\nproperty list uchar int vertex_index\nend_header\n" % faces.shape[0])
+        for i in range(verts.shape[0]):
+            f.write("%f %f %f %f %f %f %d %d %d\n" % (verts[i, 0], verts[i, 1], verts[i, 2], norms[i, 0],
+                                                     norms[i, 1], norms[i, 2], colors[i, 0], colors[i, 1],
+                                                     colors[i, 2]))
+        for i in range(faces.shape[0]):
+            f.write("3 %d %d %d\n" % (faces[i, 0], faces[i, 1], faces[i, 2]))
