@@ -16,7 +16,8 @@
 // usage: replay_rgbd <sequence.bin> <out_dir> [tsdf|fusion|both] [--raw]
 //   tsdf   -> <out_dir>/tsdf<id>.ply, tsdf<id>.bin (written by ~TSDF, src/tsdf.cu:107-132),
 //             weights.f32 (the public mirror voxel_grid_weight)
-//   fusion -> <out_dir>/fusion_tsdf.f32, fusion_color.f32, fusion_points.ply
+//   fusion -> <out_dir>/fusion_tsdf.f32, fusion_color.f32, fusion_points.ply, fusion_mesh.ply
+//             (SaveMesh of the plugin, src/TSDFfusion.py.in:48-53)
 //   --raw  -> hand the u16 image to tsdf_integrate_raw_async (subsampling + scaling on the GPU)
 // exit codes: 0 ok, 1 usage / file error, 2 library error (e.g. no CUDA device: no CPU fallback)
 #include <unistd.h>
@@ -148,6 +149,7 @@ int main(int argc, char** argv) {
       dump("fusion_tsdf.f32", t.data(), t.size());
       dump("fusion_color.f32", c.data(), c.size());
       fusion.SavePointCloud("fusion_points.ply");
+      fusion.SaveMesh("fusion_mesh.ply");  // src/TSDFfusion.py.in:48-53
     }
   } catch (const std::exception& e) {
     fprintf(stderr, "replay_rgbd: %s\n", e.what());

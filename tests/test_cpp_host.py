@@ -105,6 +105,10 @@ def test_cpp_replay_matches_oracle(replay_bin, synth, oracle, tmp_path, raw):
     assert np.array_equal(np.fromfile(tmp_path / "fusion_color.f32", np.float32), c2)
     assert oracle.save_ply(str(tmp_path / "o2.ply"), p2, t2, w2)
     assert (tmp_path / "o2.ply").read_bytes() == (tmp_path / "fusion_points.ply").read_bytes()
+    # SaveMesh (src/TSDFfusion.py.in:48-53): marching cubes + meshwrite, against the oracle's bytes
+    mv, mf, mn, mc = oracle.mesh(p2, t2, c2)
+    assert len(mf) > 100 and oracle.save_mesh_ply(str(tmp_path / "o2_mesh.ply"), mv, mf, mn, mc)
+    assert (tmp_path / "o2_mesh.ply").read_bytes() == (tmp_path / "fusion_mesh.ply").read_bytes()
 
 
 @pytest.fixture(scope="module")
