@@ -188,7 +188,8 @@ int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, i
 int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh, float* d_xyz,
                    uint8_t* d_rgb, int64_t* d_idx, int64_t cap, int64_t* count);
 int ensure_scratch(tsdf_vol* v, size_t bytes);
-int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st);  // off[m] = total
+int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st,  // off[m] = total
+                const uint32_t* d_cnt_b = nullptr, int64_t* d_off_b = nullptr);       // second pair, same m
 // mesh.cu
 int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, int64_t vcap,
                 int32_t* d_faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);

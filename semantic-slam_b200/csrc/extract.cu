@@ -73,8 +73,11 @@ k_mark(const float* __restrict__ tsdf, const float* __restrict__ weight, int64_t
 // Exclusive scan of m uint32 counts into int64 offsets; offsets[m] = total.  One block of
 // 1024 threads walks the array in coalesced 4096-entry tiles (uint4 per thread), scans each
 // tile with warp shuffles and carries the running total (<= 131072 entries at 1024^3).
+// A second (count, offset) pair of the same length rides in block 1 of the same launch (mesh.cu).
 __global__ void __launch_bounds__(1024)
-k_scan(const uint32_t* __restrict__ cnt, int64_t m, int64_t* __restrict__ off) {
+k_scan(const uint32_t* __restrict__ cnt, int64_t m, int64_t* __restrict__ off,
+       const uint32_t* __restrict__ cnt_b, int64_t* __restrict__ off_b) {
+  if (blockIdx.x == 1) { cnt = cnt_b; off = off_b; }
   __shared__ int64_t s_warp[32];
   __shared__ int64_t s_carry;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -192,8 +195,9 @@ k_emit(const uint32_t* __restrict__ ballots, const int64_t* __restrict__ tile_of
 
 }  // namespace
 
-int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st) {
-  k_scan<<<1, 1024, 0, st>>>(d_cnt, m, d_off);
+int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st,
+                const uint32_t* d_cnt_b, int64_t* d_off_b) {
+  k_scan<<<d_cnt_b ? 2 : 1, 1024, 0, st>>>(d_cnt, m, d_off, d_cnt_b, d_off_b);
   CU_CHECK(cudaGetLastError());
   return TSDF_OK;
 }
@@ -235,7 +239,7 @@ int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_t
     k_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(v->d_tsdf, v->d_weight, n, predicate, tsdf_thresh,
                                                    weight_thresh, d_bal, d_cnt);
     CU_CHECK(cudaGetLastError());
-    k_scan<<<1, 1024, 0, st>>>(d_cnt, n_tiles, d_off);
+    k_scan<<<1, 1024, 0, st>>>(d_cnt, n_tiles, d_off, nullptr, nullptr);
     CU_CHECK(cudaGetLastError());
     CU_CHECK(cudaMemcpyAsync(&total, d_off + n_tiles, 8, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaStreamSynchronize(st));

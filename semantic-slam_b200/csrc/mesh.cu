@@ -43,6 +43,8 @@ struct MeshP {
   float o[3], vs;
   const float* t;
   const float* color;
+  // i / n_fast and row / n_mid as multiply-shift, exact for dividends below 2^31 (k_mc_mark4)
+  uint32_t magic_f, shift_f, magic_m, shift_m;
 };
 
 __device__ __forceinline__ void decode(const MeshP& p, int64_t i, int co[3]) {
@@ -113,6 +115,274 @@ k_mc_mark(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
   __syncthreads();
   if (warp == 0) {
     // exclusive scan of the 64 group vertex counts: lane owns groups 2*lane, 2*lane + 1
+    const uint32_t c0 = s_vc[2 * lane], c1 = s_vc[2 * lane + 1];
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const uint32_t excl = incl - (c0 + c1);
+    const int64_t g0 = tile * kGroupsPerTile + 2 * lane;
+    recs[g0] = make_uint4(s_b[0][2 * lane], s_b[1][2 * lane], s_b[2][2 * lane], excl);
+    recs[g0 + 1] = make_uint4(s_b[0][2 * lane + 1], s_b[1][2 * lane + 1], s_b[2][2 * lane + 1], excl + c0);
+    const uint32_t tt = __reduce_add_sync(0xffffffffu, s_tc[2 * lane] + s_tc[2 * lane + 1]);
+    if (lane == 31) tile_verts[tile] = incl;
+    if (lane == 0) tile_tris[tile] = tt;
+  }
+}
+
+// The same pass for fast axes that are a multiple of 4 voxels: a thread owns 4 consecutive voxels
+// (four LDG.128 — its own run and the runs one step along mid, slow and mid+slow — instead of 32
+// scalar loads; the fifth value along the fast axis comes from the next lane by shuffle, lane 31
+// loads it) and stores its four case bytes as one word.  Everything after the 20 compares is
+// integer bit arithmetic on 5-bit row masks (the first form, with per-voxel booleans, ballots and
+// selects, was ALU-bound at 83 % pipe utilisation: profiles/r1_v9_mesh_mark4_v1.txt):
+//   edges   (m0 ^ m0>>1), (m0 ^ m_mid), (m0 ^ m_slow)            one nibble per axis per thread
+//   cases   4x4 bit transpose by multiplication: S(m) = (m * 0x00204081) & 0x01010101 puts bit j
+//           of m at bit 8j; the four rows land at their corner positions, the run shifted by one
+//           voxel supplies the other four corners
+//   record  a run leaves its three nibbles and its triangle count in one shared-memory word; after
+//           the block barrier 64 threads assemble the 64 groups' record words from eight runs each
+//           (redux.sync under per-group masks compiles to a loop over the masks: measured slower)
+//           — records, offsets and the two emit kernels are the scalar pass's.
+// Coordinates come from a multiply-shift division (exact for indices below 2^31; host-made magic).
+constexpr uint32_t kMaskBytes = 0x01010101u;
+__device__ __forceinline__ uint32_t prmt(uint32_t a, uint32_t b, uint32_t sel) {
+  uint32_t d;
+  asm("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel));
+  return d;
+}
+// bytes {s(u), s(v), s(u), s(v)}, s(x) = 0xff if x < 0 else 0.  x + 0.0f is x with -0.0 turned into +0.0
+// and a NaN into the canonical (positive) one, so the sign bit of the sum IS (x < 0); prmt's
+// selector bit 3 replicates a byte's sign over the target byte.  The adds run on the FMA pipe.
+__device__ __forceinline__ uint32_t sign_bytes2(float u, float v) {
+  return prmt(__float_as_uint(__fadd_rn(u, 0.0f)), __float_as_uint(__fadd_rn(v, 0.0f)), 0xfbfbu);
+}
+
+template <bool ZFAST>
+__global__ void __launch_bounds__(kThreads)
+k_mc_mark4(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
+           uint32_t* __restrict__ tile_verts, uint32_t* __restrict__ tile_tris) {
+  // per 4-voxel run: byte j bits 0..2 = x / y / z edge of voxel 4*run + j; triangles in bits 3..7 of byte 0
+  __shared__ __align__(16) uint32_t s_e[kTileVox / 4];
+  __shared__ uint32_t s_b[3][kGroupsPerTile];
+  __shared__ uint32_t s_vc[kGroupsPerTile], s_tc[kGroupsPerTile];
+  __shared__ uint8_t s_ntri[256];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t tile = blockIdx.x;
+  s_ntri[threadIdx.x] = d_mc_table[threadIdx.x][0];
+  __syncthreads();
+  const int64_t st_m = p.n_fast, st_s = (int64_t)p.n_fast * p.n_mid;
+  // corner c = dx + 2*dy + 4*dz: bit positions added by one step along the fast / slow axis
+  constexpr int kF = ZFAST ? 4 : 1, kS = ZFAST ? 1 : 4;
+  const int n_slow = ZFAST ? p.dim[0] : p.dim[2];
+#pragma unroll 1
+  for (int it = 0; it < kIters / 4; ++it) {
+    const int run = (it * kWarps + warp) * 32 + lane;          // 4-voxel run of the tile (512 per tile)
+    const int64_t i0 = tile * kTileVox + 4 * run;
+    const bool live = i0 < p.n;                                // n % 4 == 0: all four voxels or none
+    const int64_t ic = live ? i0 : 0;                          // dead lanes read voxel 0 and write nothing
+    uint32_t f, m, s;
+    if (p.n <= 0x7fffffffLL) {
+      const uint32_t u = (uint32_t)ic;
+      const uint32_t row = (uint32_t)(((uint64_t)u * p.magic_f) >> p.shift_f);
+      f = u - row * (uint32_t)p.n_fast;
+      s = (uint32_t)(((uint64_t)row * p.magic_m) >> p.shift_m);
+      m = row - s * (uint32_t)p.n_mid;
+    } else {
+      const int64_t row = ic / p.n_fast;
+      f = (uint32_t)(ic - row * p.n_fast);
+      s = (uint32_t)(row / p.n_mid);
+      m = (uint32_t)(row - (int64_t)s * p.n_mid);
+    }
+    // the run has a neighbour run along fast / mid / slow; a missing neighbour row aliases the run's
+    // own row, which makes its edge nibble (m0 ^ m_row) zero without a select
+    const bool hf4 = live && (int)f + 4 < p.n_fast, hm = live && (int)m + 1 < p.n_mid,
+               hs = live && (int)s + 1 < n_slow;
+    const float* q[4];
+    q[0] = p.t + ic;
+    q[1] = q[0] + (hm ? st_m : 0);
+    q[2] = q[0] + (hs ? st_s : 0);
+    q[3] = q[2] + (hm ? st_m : 0);
+    float4 a[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) a[k] = __ldg(reinterpret_cast<const float4*>(q[k]));
+    // S[k]: byte j = 0xff if voxel j of row k is inside, H[k]: the same one voxel further along the run
+    uint32_t S[4], H[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float nx = __shfl_down_sync(0xffffffffu, a[k].x, 1);
+      if (lane == 31) nx = __ldg(q[k] + (hf4 ? 4 : 0));
+      const uint32_t p01 = sign_bytes2(a[k].x, a[k].y), p23 = sign_bytes2(a[k].z, a[k].w);
+      S[k] = prmt(p01, p23, 0x5410u);
+      H[k] = prmt(S[k], sign_bytes2(nx, nx), 0x4321u);
+    }
+    constexpr uint32_t kM = 0x01010101u;
+    // edge bits of voxel j at byte j: x -> bit 0, y -> bit 1, z -> bit 2 (a missing neighbour row is the
+    // run's own row: xor = 0); the fast-axis edge of voxel 3 needs the next run
+    const uint32_t ef = (S[0] ^ H[0]) & (hf4 ? 0xffffffffu : (live ? 0x00ffffffu : 0u));
+    const uint32_t eb = (ef & (kM << (ZFAST ? 2 : 0))) | ((S[0] ^ S[1]) & (kM << 1)) |
+                        ((S[0] ^ S[2]) & (kM << (ZFAST ? 0 : 2)));
+    // case bytes: a row's inside byte masks land on its corner's bit (corner c = dx + 2*dy + 4*dz)
+    const uint32_t cs4 = ((S[0] & kM) | (S[1] & (kM << 2)) | (S[2] & (kM << kS)) | (S[3] & (kM << (2 + kS))) |
+                          (H[0] & (kM << kF)) | (H[1] & (kM << (kF + 2))) | (H[2] & (kM << (kF + kS))) |
+                          (H[3] & (kM << (kF + kS + 2)))) &
+                         ((hm && hs) ? (hf4 ? 0xffffffffu : 0x00ffffffu) : 0u);
+    if (live) *reinterpret_cast<uint32_t*>(cases + i0) = cs4;
+    uint32_t nt = 0;
+    if (cs4 != 0u && cs4 != 0xffffffffu)                       // all-outside / all-inside cells: no triangle
+      nt = (uint32_t)s_ntri[cs4 & 255u] + s_ntri[(cs4 >> 8) & 255u] + s_ntri[(cs4 >> 16) & 255u] + s_ntri[cs4 >> 24];
+    s_e[run] = eb | nt << 3;                                    // nt <= 20: bits 3..7 of byte 0
+  }
+  __syncthreads();
+  {
+    // the eight runs of a 32-voxel group -> its record words: thread = (group, part), parts 0..2 gather
+    // the x / y / z edge bits (bit 8j + part of run k -> bit 4k + j), part 3 sums the triangle counts
+    const int g = threadIdx.x >> 2, part = threadIdx.x & 3;
+    const uint4 e0 = *reinterpret_cast<const uint4*>(&s_e[8 * g]), e1 = *reinterpret_cast<const uint4*>(&s_e[8 * g + 4]);
+    const uint32_t e[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+    uint32_t w = 0;
+    if (part < 3) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) w |= ((((e[k] >> part) & kMaskBytes) * 0x10204080u) >> 28) << (4 * k);
+      s_b[part][g] = w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) w += (e[k] >> 3) & 31u;
+      s_tc[g] = w;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < kGroupsPerTile)
+    s_vc[threadIdx.x] = __popc(s_b[0][threadIdx.x]) + __popc(s_b[1][threadIdx.x]) + __popc(s_b[2][threadIdx.x]);
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t c0 = s_vc[2 * lane], c1 = s_vc[2 * lane + 1];
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    const uint32_t excl = incl - (c0 + c1);
+    const int64_t g0 = tile * kGroupsPerTile + 2 * lane;
+    recs[g0] = make_uint4(s_b[0][2 * lane], s_b[1][2 * lane], s_b[2][2 * lane], excl);
+    recs[g0 + 1] = make_uint4(s_b[0][2 * lane + 1], s_b[1][2 * lane + 1], s_b[2][2 * lane + 1], excl + c0);
+    const uint32_t tt = __reduce_add_sync(0xffffffffu, s_tc[2 * lane] + s_tc[2 * lane + 1]);
+    if (lane == 31) tile_verts[tile] = incl;
+    if (lane == 0) tile_tris[tile] = tt;
+  }
+}
+
+// Fast axes that are a multiple of 8 voxels: a thread owns 8 consecutive voxels, a block's 256 threads
+// own the tile's 2048 voxels in one pass (no loop), and the four threads of a 32-voxel group build
+// its record words with two xor-shuffles per word instead of a pass through shared memory.  Same
+// arithmetic as k_mc_mark4 on two words per row.
+template <bool ZFAST>
+__global__ void __launch_bounds__(kThreads)
+k_mc_mark8(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
+           uint32_t* __restrict__ tile_verts, uint32_t* __restrict__ tile_tris) {
+  __shared__ uint32_t s_b[3][kGroupsPerTile];
+  __shared__ uint32_t s_vc[kGroupsPerTile], s_tc[kGroupsPerTile];
+  __shared__ uint8_t s_ntri[256];
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = blockIdx.x;
+  s_ntri[threadIdx.x] = d_mc_table[threadIdx.x][0];
+  const int64_t st_m = p.n_fast, st_s = (int64_t)p.n_fast * p.n_mid;
+  constexpr int kF = ZFAST ? 4 : 1, kS = ZFAST ? 1 : 4;
+  constexpr uint32_t kM = kMaskBytes;
+  const int n_slow = ZFAST ? p.dim[0] : p.dim[2];
+  const int64_t i0 = tile * kTileVox + 8 * threadIdx.x;
+  const bool live = i0 < p.n;                                  // n % 8 == 0: all eight voxels or none
+  const int64_t ic = live ? i0 : 0;                            // dead threads read voxel 0 and write nothing
+  uint32_t f, m, s;
+  if (p.n <= 0x7fffffffLL) {
+    const uint32_t u = (uint32_t)ic;
+    const uint32_t row = (uint32_t)(((uint64_t)u * p.magic_f) >> p.shift_f);
+    f = u - row * (uint32_t)p.n_fast;
+    s = (uint32_t)(((uint64_t)row * p.magic_m) >> p.shift_m);
+    m = row - s * (uint32_t)p.n_mid;
+  } else {
+    const int64_t row = ic / p.n_fast;
+    f = (uint32_t)(ic - row * p.n_fast);
+    s = (uint32_t)(row / p.n_mid);
+    m = (uint32_t)(row - (int64_t)s * p.n_mid);
+  }
+  const bool hf8 = live && (int)f + 8 < p.n_fast, hm = live && (int)m + 1 < p.n_mid, hs = live && (int)s + 1 < n_slow;
+  const float* q[4];
+  q[0] = p.t + ic;
+  q[1] = q[0] + (hm ? st_m : 0);
+  q[2] = q[0] + (hs ? st_s : 0);
+  q[3] = q[2] + (hm ? st_m : 0);
+  // one 256-bit load per row: a warp's request is 1 KB of consecutive voxels, every sector used whole
+  // (two LDG.128 per thread are 32-byte-strided across lanes: twice the L1 wavefronts, the first form
+  // of this kernel was bound by them — l1tex throughput 90 %, profiles/r1_v9_mesh_mark8_v1.txt)
+  float4 a[4], b[4];
+  float nx[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    asm volatile("ld.global.nc.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+                 : "=f"(a[k].x), "=f"(a[k].y), "=f"(a[k].z), "=f"(a[k].w), "=f"(b[k].x), "=f"(b[k].y),
+                   "=f"(b[k].z), "=f"(b[k].w)
+                 : "l"(q[k]));
+  }
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {  // the ninth value of the run: the next lane's first, lane 31 loads it
+    nx[k] = __shfl_down_sync(0xffffffffu, a[k].x, 1);
+    if (lane == 31) nx[k] = __ldg(q[k] + (hf8 ? 8 : 0));
+  }
+  // SA/SB[k]: byte j = 0xff if voxel j / 4 + j of row k is inside; HA/HB: one voxel further along the run
+  uint32_t SA[4], SB[4], HA[4], HB[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    SA[k] = prmt(sign_bytes2(a[k].x, a[k].y), sign_bytes2(a[k].z, a[k].w), 0x5410u);
+    SB[k] = prmt(sign_bytes2(b[k].x, b[k].y), sign_bytes2(b[k].z, b[k].w), 0x5410u);
+    HA[k] = prmt(SA[k], SB[k], 0x4321u);
+    HB[k] = prmt(SB[k], sign_bytes2(nx[k], nx[k]), 0x4321u);
+  }
+  __syncthreads();                                             // s_ntri
+  const uint32_t cell = (hm && hs) ? 0xffffffffu : 0u;
+  const uint32_t last = hf8 ? 0xffffffffu : (live ? 0x00ffffffu : 0u);  // voxel 7 has no fast neighbour at a row end
+  // edge bits of voxel j at byte j: x -> bit 0, y -> bit 1, z -> bit 2
+  const uint32_t ea = ((SA[0] ^ HA[0]) & (live ? kM << (ZFAST ? 2 : 0) : 0u)) | ((SA[0] ^ SA[1]) & (kM << 1)) |
+                      ((SA[0] ^ SA[2]) & (kM << (ZFAST ? 0 : 2)));
+  const uint32_t eb = ((SB[0] ^ HB[0]) & last & (kM << (ZFAST ? 2 : 0))) | ((SB[0] ^ SB[1]) & (kM << 1)) |
+                      ((SB[0] ^ SB[2]) & (kM << (ZFAST ? 0 : 2)));
+  const uint32_t ca = ((SA[0] & kM) | (SA[1] & (kM << 2)) | (SA[2] & (kM << kS)) | (SA[3] & (kM << (2 + kS))) |
+                       (HA[0] & (kM << kF)) | (HA[1] & (kM << (kF + 2))) | (HA[2] & (kM << (kF + kS))) |
+                       (HA[3] & (kM << (kF + kS + 2)))) & cell;
+  const uint32_t cb = ((SB[0] & kM) | (SB[1] & (kM << 2)) | (SB[2] & (kM << kS)) | (SB[3] & (kM << (2 + kS))) |
+                       (HB[0] & (kM << kF)) | (HB[1] & (kM << (kF + 2))) | (HB[2] & (kM << (kF + kS))) |
+                       (HB[3] & (kM << (kF + kS + 2)))) & cell & (hf8 ? 0xffffffffu : 0x00ffffffu);
+  if (live) *reinterpret_cast<uint2*>(cases + i0) = make_uint2(ca, cb);
+  uint32_t nt = 0;
+  if (ca != 0u && ca != 0xffffffffu)                           // all-outside / all-inside cells: no triangle
+    nt = (uint32_t)s_ntri[ca & 255u] + s_ntri[(ca >> 8) & 255u] + s_ntri[(ca >> 16) & 255u] + s_ntri[ca >> 24];
+  if (cb != 0u && cb != 0xffffffffu)
+    nt += (uint32_t)s_ntri[cb & 255u] + s_ntri[(cb >> 8) & 255u] + s_ntri[(cb >> 16) & 255u] + s_ntri[cb >> 24];
+  // this thread's byte of each record word (bit j <-> voxel j of the run), dealt to its place in the
+  // group's word and OR-ed over the group's four lanes
+  const int sh = 8 * (lane & 3);
+  uint32_t w[3];
+#pragma unroll
+  for (int ax = 0; ax < 3; ++ax) {
+    const uint32_t byte = ((((ea >> ax) & kM) * 0x10204080u) >> 28) | ((((eb >> ax) & kM) * 0x10204080u) >> 28) << 4;
+    uint32_t v = byte << sh;
+    v |= __shfl_xor_sync(0xffffffffu, v, 1);
+    v |= __shfl_xor_sync(0xffffffffu, v, 2);
+    w[ax] = v;
+  }
+  nt += __shfl_xor_sync(0xffffffffu, nt, 1);
+  nt += __shfl_xor_sync(0xffffffffu, nt, 2);
+  if ((lane & 3) == 0) {
+    const int g = threadIdx.x >> 2;
+    s_b[0][g] = w[0]; s_b[1][g] = w[1]; s_b[2][g] = w[2];
+    s_vc[g] = __popc(w[0]) + __popc(w[1]) + __popc(w[2]);
+    s_tc[g] = nt;
+  }
+  __syncthreads();
+  if (threadIdx.x < 32) {
     const uint32_t c0 = s_vc[2 * lane], c1 = s_vc[2 * lane + 1];
     uint32_t incl = c0 + c1;
 #pragma unroll
@@ -270,6 +540,182 @@ k_mc_faces(MeshP p, const uint4* __restrict__ recs, const uint8_t* __restrict__ 
   }
 }
 
+// ---- emit kernels, compacted form ------------------------------------------------------------------
+// The first forms above give every voxel of a tile a thread and let the few that carry a vertex (or
+// a triangle) work alone in their warp: 28 % of the warps active, latency-bound.  Here the block
+// first lists the voxels that have work (from the records for vertices, from the case bytes for
+// triangles) and then deals the list out to all 256 threads.
+
+__device__ __forceinline__ int select_bit(uint32_t m, int k) {  // position of the k-th (0-based) set bit
+  int pos = 0, c;
+  c = __popc(m & 0xffffu); if (k >= c) { k -= c; pos += 16; m >>= 16; }
+  c = __popc(m & 0xffu);   if (k >= c) { k -= c; pos += 8;  m >>= 8; }
+  c = __popc(m & 0xfu);    if (k >= c) { k -= c; pos += 4;  m >>= 4; }
+  c = __popc(m & 0x3u);    if (k >= c) { k -= c; pos += 2;  m >>= 2; }
+  c = (int)(m & 1u);       if (k >= c) { pos += 1; }
+  return pos;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_mc_verts2(MeshP p, const uint4* __restrict__ recs, const int64_t* __restrict__ tile_off,
+            float* __restrict__ verts, float* __restrict__ norms, uint8_t* __restrict__ cols) {
+  __shared__ uint4 s_rec[kGroupsPerTile];
+  __shared__ uint32_t s_first[kGroupsPerTile + 1];  // vertex-bearing voxels before group g
+  const int lane = threadIdx.x & 31;
+  const int64_t tile = blockIdx.x;
+  const int64_t base = tile_off[tile];
+  if (tile_off[tile + 1] == base) return;  // no vertex in this tile (block-uniform)
+  if (threadIdx.x < 32) {
+    const uint4 r0 = recs[tile * kGroupsPerTile + 2 * lane], r1 = recs[tile * kGroupsPerTile + 2 * lane + 1];
+    s_rec[2 * lane] = r0; s_rec[2 * lane + 1] = r1;
+    const uint32_t c0 = __popc(r0.x | r0.y | r0.z), c1 = __popc(r1.x | r1.y | r1.z);
+    uint32_t incl = c0 + c1;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+      if (lane >= o) incl += v;
+    }
+    s_first[2 * lane] = incl - c0 - c1;
+    s_first[2 * lane + 1] = incl - c1;
+    if (lane == 31) s_first[kGroupsPerTile] = incl;
+  }
+  __syncthreads();
+  const uint32_t total = s_first[kGroupsPerTile];
+  for (uint32_t idx = threadIdx.x; idx < total; idx += kThreads) {
+    int g = 0;  // largest g with s_first[g] <= idx
+#pragma unroll
+    for (int step = kGroupsPerTile / 2; step > 0; step >>= 1)
+      if (s_first[g + step] <= idx) g += step;
+    const uint4 r = s_rec[g];
+    const int vl = select_bit(r.x | r.y | r.z, (int)(idx - s_first[g]));
+    const uint32_t lt = (1u << vl) - 1u;
+    const uint32_t bits[3] = {(r.x >> vl) & 1u, (r.y >> vl) & 1u, (r.z >> vl) & 1u};
+    const int64_t i = tile * kTileVox + (int64_t)g * 32 + vl;
+    int64_t pos = base + r.w + __popc(r.x & lt) + __popc(r.y & lt) + __popc(r.z & lt);
+    int co[3];
+    decode(p, i, co);
+    const float va = __ldg(p.t + i);
+    float g0[3];
+    if (norms) grad_at(p, i, co, g0);
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+      if (!bits[a]) continue;
+      const float vb = __ldg(p.t + i + p.st[a]);
+      const float t = __fdiv_rn(va, __fsub_rn(va, vb));
+      if (verts) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          const float gk = (float)(co[k] + p.goff[k]);
+          verts[3 * pos + k] = __fadd_rn(p.o[k], __fmul_rn(k == a ? __fadd_rn(gk, t) : gk, p.vs));
+        }
+      }
+      if (cols) {
+        const int gi = co[a] + p.goff[a];
+        int k = (int)rintf(__fadd_rn((float)gi, t));  // np.round: half to even
+        k = k < gi ? gi : (k > gi + 1 ? gi + 1 : k);
+        const uint32_t cc = p.color ? (uint32_t)__ldg(p.color + i + (int64_t)(k - gi) * p.st[a]) : 0u;
+        cols[3 * pos + 0] = (uint8_t)(cc & 255u);
+        cols[3 * pos + 1] = (uint8_t)((cc >> 8) & 255u);
+        cols[3 * pos + 2] = (uint8_t)((cc >> 16) & 255u);
+      }
+      if (norms) {
+        int c1[3] = {co[0], co[1], co[2]};
+        c1[a] += 1;
+        float g1[3], nn[3];
+        grad_at(p, i + p.st[a], c1, g1);
+#pragma unroll
+        for (int k = 0; k < 3; ++k) nn[k] = __fadd_rn(g0[k], __fmul_rn(t, __fsub_rn(g1[k], g0[k])));
+        const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(nn[0], nn[0]), __fmul_rn(nn[1], nn[1])),
+                                               __fmul_rn(nn[2], nn[2])));
+#pragma unroll
+        for (int k = 0; k < 3; ++k) norms[3 * pos + k] = len > 0.0f ? __fdiv_rn(nn[k], len) : 0.0f;
+      }
+      ++pos;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_mc_faces2(MeshP p, const uint4* __restrict__ recs, const uint8_t* __restrict__ cases,
+            const int64_t* __restrict__ vert_off, const int64_t* __restrict__ tri_off,
+            int32_t* __restrict__ faces) {
+  __shared__ uint32_t s_tab[256 * 4];       // the table, 16 bytes per case
+  __shared__ uint32_t s_list[kTileVox];     // cells with triangles: local index | first triangle << 11
+  __shared__ uint32_t s_warp[kWarps];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t tile = blockIdx.x;
+  const int64_t base = tri_off[tile];
+  if (tri_off[tile + 1] == base) return;  // no triangle in this tile (block-uniform)
+  {
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(&d_mc_table[0][0]);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) s_tab[threadIdx.x + k * kThreads] = src[threadIdx.x + k * kThreads];
+  }
+  __syncthreads();
+  const uint8_t* tab = reinterpret_cast<const uint8_t*>(s_tab);
+  // a thread lists its 8 consecutive cells; packed block scan: triangles in the low half, cells in the high
+  const int64_t c0 = tile * kTileVox + 8 * threadIdx.x;
+  uint2 cb = make_uint2(0u, 0u);
+  if (c0 + 8 <= p.n) cb = *reinterpret_cast<const uint2*>(cases + c0);
+  else
+    for (int k = 0; k < 8; ++k)
+      if (c0 + k < p.n) (k < 4 ? cb.x : cb.y) |= (uint32_t)cases[c0 + k] << (8 * (k & 3));
+  uint32_t mine = 0;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t nt = tab[(((k < 4 ? cb.x : cb.y) >> (8 * (k & 3))) & 255u) * 16];
+    mine += nt + (nt ? 65536u : 0u);
+  }
+  uint32_t incl = mine;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) s_warp[warp] = incl;
+  __syncthreads();
+  uint32_t run = incl - mine, n_cells = 0;
+#pragma unroll
+  for (int w = 0; w < kWarps; ++w) {
+    if (w < warp) run += s_warp[w];
+    n_cells += s_warp[w] >> 16;
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const uint32_t nt = tab[(((k < 4 ? cb.x : cb.y) >> (8 * (k & 3))) & 255u) * 16];
+    if (nt) {
+      s_list[run >> 16] = (uint32_t)(8 * threadIdx.x + k) | (run & 0xffffu) << 11;
+      run += nt + 65536u;
+    }
+  }
+  __syncthreads();
+  for (uint32_t idx = threadIdx.x; idx < n_cells; idx += kThreads) {
+    const uint32_t e0 = s_list[idx], local = e0 & 2047u;
+    const int64_t i = tile * kTileVox + local;
+    const uint8_t* row = tab + (uint32_t)cases[i] * 16;
+    const uint32_t nt = row[0];
+    int64_t f = base + (e0 >> 11);
+    for (uint32_t k = 0; k < nt; ++k, ++f) {
+#pragma unroll
+      for (int j = 0; j < 3; ++j) {
+        const uint32_t e = row[1 + 3 * k + j], a = e >> 2, q = e & 3u;
+        // the two fixed coordinates of edge e, in axis order (tools/gen_mc_table.py)
+        const uint32_t d0 = a == 0 ? 0u : (q & 1u);
+        const uint32_t d1 = a == 1 ? 0u : (a == 0 ? (q & 1u) : (q >> 1));
+        const uint32_t d2 = a == 2 ? 0u : (q >> 1);
+        const int64_t u = i + d0 * p.st[0] + d1 * p.st[1] + d2 * p.st[2];
+        const int64_t gu = u >> 5;
+        const uint32_t lu = (uint32_t)(u & 31), ltu = (1u << lu) - 1u;
+        const uint4 r = recs[gu];
+        int64_t id = vert_off[gu / kGroupsPerTile] + r.w + __popc(r.x & ltu) + __popc(r.y & ltu) + __popc(r.z & ltu);
+        if (a > 0) id += (r.x >> lu) & 1u;
+        if (a > 1) id += (r.y >> lu) & 1u;
+        faces[3 * f + j] = (int32_t)id;
+      }
+    }
+  }
+}
+
 void fill_mesh_params(const tsdf_vol* v, MeshP* p) {
   const tsdf_config& c = v->cfg;
   p->n = v->n_local;
@@ -287,6 +733,15 @@ void fill_mesh_params(const tsdf_vol* v, MeshP* p) {
   p->vs = c.voxel_size;
   p->t = v->d_tsdf;
   p->color = v->d_color;
+  // Granlund-Montgomery: s = ceil(log2 d), M = ceil(2^(31+s) / d) < 2^32, n / d = (n * M) >> (31 + s)
+  auto magic = [](uint32_t d, uint32_t* M, uint32_t* sh) {
+    uint32_t s = 0;
+    while ((1ull << s) < d) ++s;
+    *M = (uint32_t)(((1ull << (31 + s)) + d - 1) / d);
+    *sh = 31 + s;
+  };
+  magic((uint32_t)p->n_fast, &p->magic_f, &p->shift_f);
+  magic((uint32_t)p->n_mid, &p->magic_m, &p->shift_m);
 }
 
 }  // namespace
@@ -323,11 +778,22 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
   fill_mesh_params(v, &p);
   if (!(v->mesh_valid && v->mesh_epoch == v->epoch)) {
     v->mesh_valid = false;
-    k_mc_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
+    // bit 16 of the A/B variant forces the scalar pass (tools/variants.py, tests)
+    const bool vec4 = p.n_fast % 4 == 0 && (v->variant & 65536) == 0;
+    const bool vec8 = vec4 && p.n_fast % 8 == 0 && (v->variant & 262144) == 0;  // bit 18: 4-wide sweep
+    if (vec8 && p.zfast)
+      k_mc_mark8<true><<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
+    else if (vec8)
+      k_mc_mark8<false><<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
+    else if (vec4 && p.zfast)
+      k_mc_mark4<true><<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
+    else if (vec4)
+      k_mc_mark4<false><<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
+    else
+      k_mc_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
     CU_CHECK(cudaGetLastError());
-    int rc = launch_scan(d_vcnt, n_tiles, d_voff, st);
+    int rc = launch_scan(d_vcnt, n_tiles, d_voff, st, d_tcnt, d_toff);  // both scans in one launch
     if (rc) return rc;
-    if ((rc = launch_scan(d_tcnt, n_tiles, d_toff, st))) return rc;
     int64_t tot[2] = {0, 0};
     CU_CHECK(cudaMemcpyAsync(&tot[0], d_voff + n_tiles, 8, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaMemcpyAsync(&tot[1], d_toff + n_tiles, 8, cudaMemcpyDeviceToHost, st));
@@ -352,11 +818,17 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
     return TSDF_E_CAPACITY;
   }
   if (nv && (d_verts || d_norms || d_cols)) {
-    k_mc_verts<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_verts, d_norms, d_cols);
+    if (v->variant & 131072)  // bit 17: the uncompacted emit kernels (A/B)
+      k_mc_verts<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_verts, d_norms, d_cols);
+    else
+      k_mc_verts2<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_verts, d_norms, d_cols);
     CU_CHECK(cudaGetLastError());
   }
   if (nf && d_faces) {
-    k_mc_faces<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_faces);
+    if (v->variant & 131072)
+      k_mc_faces<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_faces);
+    else
+      k_mc_faces2<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_faces);
     CU_CHECK(cudaGetLastError());
   }
   CU_CHECK(cudaStreamSynchronize(st));

@@ -245,3 +245,24 @@ def test_gpu_mesh_capacity_and_device_outputs(pkg):
         full = vol.extract_mesh()
         assert np.array_equal(full[1], faces) and np.array_equal(bits(full[0]), bits(verts))
         assert full[3].max() == 0                                      # no colour array: zeros
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sem", [SEM_FUSIONPY, SEM_TSDFCU])
+def test_gpu_mesh_scalar_and_vector_sweeps_agree(pkg, oracle, sem):
+    """Fast axes that are a multiple of 8 / of 4 take k_mc_mark8 / k_mc_mark4 (a thread owns 8 / 4 voxels);
+    variant bit 16 forces the scalar sweep, bit 18 the 4-wide one.  Both must give the oracle's mesh — also where a 128-voxel
+    chunk straddles rows (fast axis 36) and where the volume ends inside a tile."""
+    for dims in ((36, 20, 36), (128, 12, 256), (8, 8, 8), (4, 4, 4), (132, 9, 68)):
+        rng = np.random.default_rng(sum(dims))
+        t = rng.standard_normal(dims).astype(np.float32)
+        col = rng.integers(0, 1 << 24, dims).astype(np.float32)
+        want = oracle_mesh(oracle, t, sem, col)
+        cfg = pkg.make_config(dims, VS, (0, 0, 0), semantics=sem, with_color=True)
+        with pkg.Volume(cfg) as vol:
+            vol.upload(tsdf=to_storage(t, sem), color=to_storage(col, sem))
+            assert_same_mesh(vol.extract_mesh(), want)
+            for variant in (65536, 131072, 262144):        # scalar sweep; uncompacted emit kernels; 4-wide sweep
+                vol.set_variant(variant)
+                vol.upload()                               # invalidate the cached sweep
+                assert_same_mesh(vol.extract_mesh(), want)
