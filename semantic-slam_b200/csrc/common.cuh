@@ -147,6 +147,7 @@ struct tsdf_vol {
   bool mesh_valid = false;
   uint64_t mesh_epoch = 0;
   int64_t mesh_nv = 0, mesh_nf = 0;
+  uint32_t mesh_vtiles = 0, mesh_ftiles = 0;  // tiles that hold vertices / triangles
 };
 
 inline size_t frame_pixels(const tsdf_config& c) { return (size_t)c.im_h * c.im_w; }
@@ -188,8 +189,12 @@ int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, i
 int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh, float* d_xyz,
                    uint8_t* d_rgb, int64_t* d_idx, int64_t cap, int64_t* count);
 int ensure_scratch(tsdf_vol* v, size_t bytes);
-int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, cudaStream_t st,  // off[m] = total
-                const uint32_t* d_cnt_b = nullptr, int64_t* d_off_b = nullptr);       // second pair, same m
+int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, int64_t* d_tot, cudaStream_t st,  // off[m] = total
+                const uint32_t* d_cnt_b = nullptr, int64_t* d_off_b = nullptr,                   // second triple,
+                int64_t* d_tot_b = nullptr,                                                       // same m
+                uint32_t* d_list = nullptr, uint32_t* d_list_b = nullptr,  // optional: indices of the non-zero counts
+                uint32_t* d_nlist2 = nullptr);                             // their two lengths (zeroed by the caller)
+size_t scan_scratch_bytes(int64_t m);  // size of one d_tot
 // mesh.cu
 int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, int64_t vcap,
                 int32_t* d_faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);

@@ -9,11 +9,12 @@
 // Indexed mesh, every vertex emitted once:
 //   vertex   one per grid edge (voxel i, axis a) whose two voxels differ in (tsdf < 0);
 //            id = rank of (i, a) in ascending (storage index, axis) order
-//   k_mc_mark   one thread per voxel, 8 corner loads (coalesced along the fast axis, the seven
-//               neighbours come from L1/L2): three edge ballots per 32-voxel group, the cell's
-//               8-bit case, per-tile vertex and triangle counts; one 16-byte record per group
-//               {ballot_x, ballot_y, ballot_z, vertices before this group in its tile}
-//   k_scan      (extract.cu) exclusive scans of the two tile-count arrays
+//   k_mc_mark*  the only sweep: three edge ballots per 32-voxel group, the cell's 8-bit case, per-tile
+//               vertex and triangle counts; one 16-byte record per group {ballot_x, ballot_y,
+//               ballot_z, vertices before this group in its tile}.  k_mc_mark8 / k_mc_mark4: a thread
+//               owns 8 / 4 voxels of a fast axis that is a multiple of 8 / 4 (vector loads, bit
+//               arithmetic on sign bytes); k_mc_mark: one thread per voxel, any shape
+//   k_scan_*    (extract.cu) exclusive scans of the two tile-count arrays, 4096 entries per block
 //   k_mc_verts  rank = tile offset + record prefix + popc of lower ballot bits; writes position
 //               (t = a/(a-b) along the edge), gradient normal, colour of the nearer voxel
 //   k_mc_faces  per cell: triangles of mc_table.inc; a vertex id is ONE 16-byte record load + popc
@@ -285,10 +286,8 @@ k_mc_mark8(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
            uint32_t* __restrict__ tile_verts, uint32_t* __restrict__ tile_tris) {
   __shared__ uint32_t s_b[3][kGroupsPerTile];
   __shared__ uint32_t s_vc[kGroupsPerTile], s_tc[kGroupsPerTile];
-  __shared__ uint8_t s_ntri[256];
   const int lane = threadIdx.x & 31;
   const int64_t tile = blockIdx.x;
-  s_ntri[threadIdx.x] = d_mc_table[threadIdx.x][0];
   const int64_t st_m = p.n_fast, st_s = (int64_t)p.n_fast * p.n_mid;
   constexpr int kF = ZFAST ? 4 : 1, kS = ZFAST ? 1 : 4;
   constexpr uint32_t kM = kMaskBytes;
@@ -341,7 +340,6 @@ k_mc_mark8(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
     HA[k] = prmt(SA[k], SB[k], 0x4321u);
     HB[k] = prmt(SB[k], sign_bytes2(nx[k], nx[k]), 0x4321u);
   }
-  __syncthreads();                                             // s_ntri
   const uint32_t cell = (hm && hs) ? 0xffffffffu : 0u;
   const uint32_t last = hf8 ? 0xffffffffu : (live ? 0x00ffffffu : 0u);  // voxel 7 has no fast neighbour at a row end
   // edge bits of voxel j at byte j: x -> bit 0, y -> bit 1, z -> bit 2
@@ -357,10 +355,12 @@ k_mc_mark8(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
                        (HB[3] & (kM << (kF + kS + 2)))) & cell & (hf8 ? 0xffffffffu : 0x00ffffffu);
   if (live) *reinterpret_cast<uint2*>(cases + i0) = make_uint2(ca, cb);
   uint32_t nt = 0;
-  if (ca != 0u && ca != 0xffffffffu)                           // all-outside / all-inside cells: no triangle
-    nt = (uint32_t)s_ntri[ca & 255u] + s_ntri[(ca >> 8) & 255u] + s_ntri[(ca >> 16) & 255u] + s_ntri[ca >> 24];
+  if (ca != 0u && ca != 0xffffffffu)  // all-outside / all-inside cells have no triangle; the rest look the table up (L1)
+    nt = (uint32_t)d_mc_table[ca & 255u][0] + d_mc_table[(ca >> 8) & 255u][0] + d_mc_table[(ca >> 16) & 255u][0] +
+         d_mc_table[ca >> 24][0];
   if (cb != 0u && cb != 0xffffffffu)
-    nt += (uint32_t)s_ntri[cb & 255u] + s_ntri[(cb >> 8) & 255u] + s_ntri[(cb >> 16) & 255u] + s_ntri[cb >> 24];
+    nt += (uint32_t)d_mc_table[cb & 255u][0] + d_mc_table[(cb >> 8) & 255u][0] + d_mc_table[(cb >> 16) & 255u][0] +
+          d_mc_table[cb >> 24][0];
   // this thread's byte of each record word (bit j <-> voxel j of the run), dealt to its place in the
   // group's word and OR-ed over the group's four lanes
   const int sh = 8 * (lane & 3);
@@ -413,138 +413,12 @@ __device__ __forceinline__ void grad_at(const MeshP& p, int64_t u, const int co[
   }
 }
 
-__global__ void __launch_bounds__(kThreads)
-k_mc_verts(MeshP p, const uint4* __restrict__ recs, const int64_t* __restrict__ tile_off,
-           float* __restrict__ verts, float* __restrict__ norms, uint8_t* __restrict__ cols) {
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t tile = blockIdx.x;
-  const int64_t base = tile_off[tile];
-  if (tile_off[tile + 1] == base) return;  // no vertex in this tile (block-uniform)
-  const uint32_t lt = (1u << lane) - 1u;
-#pragma unroll 1
-  for (int it = 0; it < kIters; ++it) {
-    const int g = it * kWarps + warp;
-    const uint4 r = recs[tile * kGroupsPerTile + g];
-    if (!(r.x | r.y | r.z)) continue;
-    const uint32_t bits[3] = {(r.x >> lane) & 1u, (r.y >> lane) & 1u, (r.z >> lane) & 1u};
-    if (!(bits[0] | bits[1] | bits[2])) continue;
-    const int64_t i = tile * kTileVox + (int64_t)g * 32 + lane;
-    int64_t pos = base + r.w + __popc(r.x & lt) + __popc(r.y & lt) + __popc(r.z & lt);
-    int co[3];
-    decode(p, i, co);
-    const float va = __ldg(p.t + i);
-    float g0[3];
-    if (norms) grad_at(p, i, co, g0);
-#pragma unroll
-    for (int a = 0; a < 3; ++a) {
-      if (!bits[a]) continue;
-      const float vb = __ldg(p.t + i + p.st[a]);
-      const float t = __fdiv_rn(va, __fsub_rn(va, vb));
-      if (verts) {
-#pragma unroll
-        for (int k = 0; k < 3; ++k) {
-          const float gk = (float)(co[k] + p.goff[k]);
-          verts[3 * pos + k] = __fadd_rn(p.o[k], __fmul_rn(k == a ? __fadd_rn(gk, t) : gk, p.vs));
-        }
-      }
-      if (cols) {
-        const int gi = co[a] + p.goff[a];
-        int k = (int)rintf(__fadd_rn((float)gi, t));  // np.round: half to even
-        k = k < gi ? gi : (k > gi + 1 ? gi + 1 : k);
-        const uint32_t cc = p.color ? (uint32_t)__ldg(p.color + i + (int64_t)(k - gi) * p.st[a]) : 0u;
-        cols[3 * pos + 0] = (uint8_t)(cc & 255u);
-        cols[3 * pos + 1] = (uint8_t)((cc >> 8) & 255u);
-        cols[3 * pos + 2] = (uint8_t)((cc >> 16) & 255u);
-      }
-      if (norms) {
-        int c1[3] = {co[0], co[1], co[2]};
-        c1[a] += 1;
-        float g1[3], nn[3];
-        grad_at(p, i + p.st[a], c1, g1);
-#pragma unroll
-        for (int k = 0; k < 3; ++k) nn[k] = __fadd_rn(g0[k], __fmul_rn(t, __fsub_rn(g1[k], g0[k])));
-        const float len = __fsqrt_rn(__fadd_rn(__fadd_rn(__fmul_rn(nn[0], nn[0]), __fmul_rn(nn[1], nn[1])),
-                                               __fmul_rn(nn[2], nn[2])));
-#pragma unroll
-        for (int k = 0; k < 3; ++k) norms[3 * pos + k] = len > 0.0f ? __fdiv_rn(nn[k], len) : 0.0f;
-      }
-      ++pos;
-    }
-  }
-}
-
-__global__ void __launch_bounds__(kThreads)
-k_mc_faces(MeshP p, const uint4* __restrict__ recs, const uint8_t* __restrict__ cases,
-           const int64_t* __restrict__ vert_off, const int64_t* __restrict__ tri_off,
-           int32_t* __restrict__ faces) {
-  __shared__ uint32_t s_tab[256 * 4];     // the table, 16 bytes per case
-  __shared__ uint32_t s_goff[kGroupsPerTile + 1];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t tile = blockIdx.x;
-  const int64_t base = tri_off[tile];
-  if (tri_off[tile + 1] == base) return;  // no triangle in this tile (block-uniform)
-  {
-    const uint32_t* src = reinterpret_cast<const uint32_t*>(&d_mc_table[0][0]);
-#pragma unroll
-    for (int k = 0; k < 4; ++k) s_tab[threadIdx.x + k * kThreads] = src[threadIdx.x + k * kThreads];
-  }
-  __syncthreads();
-  const uint8_t* tab = reinterpret_cast<const uint8_t*>(s_tab);
-  uint32_t my_case[kIters];
-#pragma unroll
-  for (int it = 0; it < kIters; ++it) {
-    const int g = it * kWarps + warp;
-    const int64_t i = tile * kTileVox + (int64_t)g * 32 + lane;
-    my_case[it] = i < p.n ? (uint32_t)cases[i] : 0u;
-    const uint32_t nt = __reduce_add_sync(0xffffffffu, (uint32_t)tab[my_case[it] * 16]);
-    if (lane == 0) s_goff[g + 1] = nt;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    s_goff[0] = 0;
-    for (int g = 1; g <= kGroupsPerTile; ++g) s_goff[g] += s_goff[g - 1];
-  }
-  __syncthreads();
-#pragma unroll
-  for (int it = 0; it < kIters; ++it) {
-    const int g = it * kWarps + warp;
-    if (s_goff[g + 1] == s_goff[g]) continue;  // warp-uniform
-    const uint8_t* row = tab + my_case[it] * 16;
-    const uint32_t nt = row[0];
-    uint32_t incl = nt;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-      const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-      if (lane >= o) incl += v;
-    }
-    const int64_t i = tile * kTileVox + (int64_t)g * 32 + lane;
-    int64_t f = base + s_goff[g] + (incl - nt);
-    for (uint32_t k = 0; k < nt; ++k, ++f) {
-#pragma unroll
-      for (int j = 0; j < 3; ++j) {
-        const uint32_t e = row[1 + 3 * k + j], a = e >> 2, q = e & 3u;
-        // the two fixed coordinates of edge e, in axis order (tools/gen_mc_table.py)
-        const uint32_t d0 = a == 0 ? 0u : (q & 1u);
-        const uint32_t d1 = a == 1 ? 0u : (a == 0 ? (q & 1u) : (q >> 1));
-        const uint32_t d2 = a == 2 ? 0u : (q >> 1);
-        const int64_t u = i + d0 * p.st[0] + d1 * p.st[1] + d2 * p.st[2];
-        const int64_t gu = u >> 5;
-        const uint32_t lu = (uint32_t)(u & 31), ltu = (1u << lu) - 1u;
-        const uint4 r = recs[gu];
-        int64_t id = vert_off[gu / kGroupsPerTile] + r.w + __popc(r.x & ltu) + __popc(r.y & ltu) + __popc(r.z & ltu);
-        if (a > 0) id += (r.x >> lu) & 1u;
-        if (a > 1) id += (r.y >> lu) & 1u;
-        faces[3 * f + j] = (int32_t)id;
-      }
-    }
-  }
-}
-
-// ---- emit kernels, compacted form ------------------------------------------------------------------
-// The first forms above give every voxel of a tile a thread and let the few that carry a vertex (or
-// a triangle) work alone in their warp: 28 % of the warps active, latency-bound.  Here the block
-// first lists the voxels that have work (from the records for vertices, from the case bytes for
-// triangles) and then deals the list out to all 256 threads.
+// ---- emit kernels ------------------------------------------------------------------------------------
+// The first forms gave every voxel of a tile a thread and let the few that carry a vertex (or a
+// triangle) work alone in their warp: 28 % of the warps active, latency-bound (512^3 S-real: 0.68 +
+// 0.43 ms, profiles/r1_v9_mesh_kernels_ncu.jsonl).  Here the block first lists the voxels that have
+// work (from the records for vertices, from the case bytes for triangles) and then deals the list
+// out to all 256 threads (0.17 + 0.19 ms).
 
 __device__ __forceinline__ int select_bit(uint32_t m, int k) {  // position of the k-th (0-based) set bit
   int pos = 0, c;
@@ -557,14 +431,14 @@ __device__ __forceinline__ int select_bit(uint32_t m, int k) {  // position of t
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_mc_verts2(MeshP p, const uint4* __restrict__ recs, const int64_t* __restrict__ tile_off,
-            float* __restrict__ verts, float* __restrict__ norms, uint8_t* __restrict__ cols) {
+k_mc_verts(MeshP p, const uint4* __restrict__ recs, const int64_t* __restrict__ tile_off,
+           const uint32_t* __restrict__ tiles, float* __restrict__ verts, float* __restrict__ norms,
+           uint8_t* __restrict__ cols) {
   __shared__ uint4 s_rec[kGroupsPerTile];
   __shared__ uint32_t s_first[kGroupsPerTile + 1];  // vertex-bearing voxels before group g
   const int lane = threadIdx.x & 31;
-  const int64_t tile = blockIdx.x;
+  const int64_t tile = tiles[blockIdx.x];  // one block per tile that holds vertices (list made by the scan)
   const int64_t base = tile_off[tile];
-  if (tile_off[tile + 1] == base) return;  // no vertex in this tile (block-uniform)
   if (threadIdx.x < 32) {
     const uint4 r0 = recs[tile * kGroupsPerTile + 2 * lane], r1 = recs[tile * kGroupsPerTile + 2 * lane + 1];
     s_rec[2 * lane] = r0; s_rec[2 * lane + 1] = r1;
@@ -636,16 +510,15 @@ k_mc_verts2(MeshP p, const uint4* __restrict__ recs, const int64_t* __restrict__
 }
 
 __global__ void __launch_bounds__(kThreads)
-k_mc_faces2(MeshP p, const uint4* __restrict__ recs, const uint8_t* __restrict__ cases,
-            const int64_t* __restrict__ vert_off, const int64_t* __restrict__ tri_off,
-            int32_t* __restrict__ faces) {
+k_mc_faces(MeshP p, const uint4* __restrict__ recs, const uint8_t* __restrict__ cases,
+           const int64_t* __restrict__ vert_off, const int64_t* __restrict__ tri_off,
+           const uint32_t* __restrict__ tiles, int32_t* __restrict__ faces) {
   __shared__ uint32_t s_tab[256 * 4];       // the table, 16 bytes per case
   __shared__ uint32_t s_list[kTileVox];     // cells with triangles: local index | first triangle << 11
   __shared__ uint32_t s_warp[kWarps];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t tile = blockIdx.x;
+  const int64_t tile = tiles[blockIdx.x];  // one block per tile that holds triangles
   const int64_t base = tri_off[tile];
-  if (tri_off[tile + 1] == base) return;  // no triangle in this tile (block-uniform)
   {
     const uint32_t* src = reinterpret_cast<const uint32_t*>(&d_mc_table[0][0]);
 #pragma unroll
@@ -754,12 +627,14 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
   const int64_t n = v->n_local;
   const int64_t n_tiles = (n + kTileVox - 1) / kTileVox;
   // scratch: [vert_off i64 (T+1)] [tri_off i64 (T+1)] [tile_verts u32 T] [tile_tris u32 T]
-  //          [records uint4 64*T] [cases u8 2048*T]
+  //          [records uint4 64*T] [cases u8 2048*T] [scan block totals x2] [vertex tile list u32 T]
+  //          [triangle tile list u32 T] [the two list lengths]
   const size_t off_b = ((size_t)(n_tiles + 1) * 8 + 255) & ~(size_t)255;
   const size_t cnt_b = ((size_t)n_tiles * 4 + 255) & ~(size_t)255;
   const size_t rec_b = (size_t)n_tiles * kGroupsPerTile * 16;
   const size_t cas_b = (size_t)n_tiles * kTileVox;
-  const size_t need = 2 * off_b + 2 * cnt_b + rec_b + cas_b;
+  const size_t tot_b = scan_scratch_bytes(n_tiles);
+  const size_t need = 2 * off_b + 2 * cnt_b + rec_b + cas_b + 2 * tot_b + 2 * cnt_b + 256;
   if (v->mesh_bytes < need) {
     if (v->d_mesh) cudaFree(v->d_mesh);
     v->d_mesh = nullptr; v->mesh_bytes = 0; v->mesh_valid = false;
@@ -773,6 +648,12 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
   uint32_t* d_tcnt = reinterpret_cast<uint32_t*>(s + 2 * off_b + cnt_b);
   uint4* d_recs = reinterpret_cast<uint4*>(s + 2 * off_b + 2 * cnt_b);
   uint8_t* d_cases = reinterpret_cast<uint8_t*>(s + 2 * off_b + 2 * cnt_b + rec_b);
+  int64_t* d_vtot = reinterpret_cast<int64_t*>(s + 2 * off_b + 2 * cnt_b + rec_b + cas_b);
+  int64_t* d_ttot = reinterpret_cast<int64_t*>(s + 2 * off_b + 2 * cnt_b + rec_b + cas_b + tot_b);
+  char* s2 = s + 2 * off_b + 2 * cnt_b + rec_b + cas_b + 2 * tot_b;
+  uint32_t* d_vlist = reinterpret_cast<uint32_t*>(s2);             // tiles that hold vertices
+  uint32_t* d_flist = reinterpret_cast<uint32_t*>(s2 + cnt_b);     // tiles that hold triangles
+  uint32_t* d_nlist = reinterpret_cast<uint32_t*>(s2 + 2 * cnt_b); // their two counts
   cudaStream_t st = v->s_compute;
   MeshP p;
   fill_mesh_params(v, &p);
@@ -792,14 +673,19 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
     else
       k_mc_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
     CU_CHECK(cudaGetLastError());
-    int rc = launch_scan(d_vcnt, n_tiles, d_voff, st, d_tcnt, d_toff);  // both scans in one launch
+    CU_CHECK(cudaMemsetAsync(d_nlist, 0, 8, st));
+    int rc = launch_scan(d_vcnt, n_tiles, d_voff, d_vtot, st, d_tcnt, d_toff, d_ttot,  // both arrays per launch
+                         d_vlist, d_flist, d_nlist);
     if (rc) return rc;
     int64_t tot[2] = {0, 0};
+    uint32_t nl[2] = {0, 0};
     CU_CHECK(cudaMemcpyAsync(&tot[0], d_voff + n_tiles, 8, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaMemcpyAsync(&tot[1], d_toff + n_tiles, 8, cudaMemcpyDeviceToHost, st));
+    CU_CHECK(cudaMemcpyAsync(nl, d_nlist, 8, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaStreamSynchronize(st));
     v->mesh_valid = true; v->mesh_epoch = v->epoch;
     v->mesh_nv = tot[0]; v->mesh_nf = tot[1];
+    v->mesh_vtiles = nl[0]; v->mesh_ftiles = nl[1];
   }
   const int64_t nv = v->mesh_nv, nf = v->mesh_nf;
   if (n_verts) *n_verts = nv;
@@ -818,17 +704,11 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
     return TSDF_E_CAPACITY;
   }
   if (nv && (d_verts || d_norms || d_cols)) {
-    if (v->variant & 131072)  // bit 17: the uncompacted emit kernels (A/B)
-      k_mc_verts<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_verts, d_norms, d_cols);
-    else
-      k_mc_verts2<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_verts, d_norms, d_cols);
+    k_mc_verts<<<v->mesh_vtiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_vlist, d_verts, d_norms, d_cols);
     CU_CHECK(cudaGetLastError());
   }
   if (nf && d_faces) {
-    if (v->variant & 131072)
-      k_mc_faces<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_faces);
-    else
-      k_mc_faces2<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_faces);
+    k_mc_faces<<<v->mesh_ftiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_flist, d_faces);
     CU_CHECK(cudaGetLastError());
   }
   CU_CHECK(cudaStreamSynchronize(st));

@@ -262,7 +262,31 @@ def test_gpu_mesh_scalar_and_vector_sweeps_agree(pkg, oracle, sem):
         with pkg.Volume(cfg) as vol:
             vol.upload(tsdf=to_storage(t, sem), color=to_storage(col, sem))
             assert_same_mesh(vol.extract_mesh(), want)
-            for variant in (65536, 131072, 262144):        # scalar sweep; uncompacted emit kernels; 4-wide sweep
+            for variant in (65536, 262144):                # scalar sweep; 4-wide sweep
                 vol.set_variant(variant)
                 vol.upload()                               # invalidate the cached sweep
                 assert_same_mesh(vol.extract_mesh(), want)
+
+
+@pytest.mark.gpu
+def test_gpu_scans_over_many_tiles(pkg, oracle):
+    """42 M voxels: 20480 mesh tiles and 5120 extraction tiles, i.e. several 4096-entry iterations of the
+    one-block scan (register carry, prefetched counts, double-buffered warp totals) behind both the
+    point extraction and the mesh; sparse content so that the oracle's outputs stay small."""
+    dims = (512, 512, 160)
+    rng = np.random.default_rng(0xB200 + 9)
+    t = np.ones(dims, np.float32)
+    hit = rng.random(dims) < 0.01
+    t[hit] = rng.standard_normal(int(hit.sum())).astype(np.float32)
+    w = hit.astype(np.float32) * 2
+    cfg = pkg.make_config(dims, VS, (0, 0, 0), semantics=pkg.SEM_FUSIONPY, with_color=False)
+    p = oracle.params(dims, VS, 5 * VS, (0, 0, 0), (480, 640), K_ID, np.inf, SEM_FUSIONPY)
+    with pkg.Volume(cfg) as vol:
+        vol.upload(tsdf=t.reshape(-1), weight=w.reshape(-1))
+        gxyz, _, gidx = vol.extract_points()
+        got = vol.extract_mesh()
+    oxyz, _, oidx = oracle.extract(p, t.reshape(-1), w.reshape(-1), None)
+    assert len(oidx) > 300000 and np.array_equal(gidx, oidx) and np.array_equal(bits(gxyz), bits(oxyz))
+    want = oracle.mesh(p, t.reshape(-1), None)
+    assert len(want[0]) > 1000000
+    assert_same_mesh(got, want)

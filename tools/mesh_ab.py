@@ -1,7 +1,6 @@
 """Mesh readback timing: the sweep (k_mc_mark* + two scans + counts to the host)
-and the emit kernels, device time by CUDA events on the library's compute stream, scalar pass
-(variant bit 16) against the vectorised one and the uncompacted emit kernels (bit 17) against the
-compacted ones, round-robin.
+and the emit kernels, device time by CUDA events on the library's compute stream, the 8-wide
+sweep against the 4-wide one (variant bit 18) and the scalar one (bit 16), round-robin.
 usage: python tools/mesh_ab.py <scene: real|sphere> <dim> [cu]
   real   = S-real fused from 8 fr3_office keyframes (C2-like); sphere = analytic sphere uploaded
   cu     = class-TSDF storage order (x fast) instead of the plugin's (z fast)"""
@@ -22,7 +21,7 @@ else:
 cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=(sem == pkg.SEM_FUSIONPY),
                       max_depth=6.0 if sem == pkg.SEM_TSDFCU else None)
 lib = pkg.load()
-VARIANTS = ((0, "default"), (262144, "sweep_4_wide"), (65536, "scalar_sweep"), (131072, "uncompacted_emit"))
+VARIANTS = ((0, "default"), (262144, "sweep_4_wide"), (65536, "scalar_sweep"))
 res = {v: {"sweep": [], "emit": []} for v, _ in VARIANTS}
 with pkg.Volume(cfg) as vol:
     if frames:
