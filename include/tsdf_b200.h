@@ -250,6 +250,10 @@ int tsdf_batch_download(tsdf_batch* b, int instance, float* tsdf, float* weight,
 int tsdf_batch_extract_points(tsdf_batch* b, int instance, int predicate, float tsdf_thresh,
                               float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx,
                               int64_t cap, int64_t* count);
+/* Mesh of one instance volume (tsdf_extract_mesh on it): the per-object surface of Engine/Object. */
+int tsdf_batch_extract_mesh(tsdf_batch* b, int instance, float* verts, float* norms, uint8_t* colors,
+                            int64_t vcap, int32_t* faces, int64_t fcap, int64_t* n_verts,
+                            int64_t* n_faces);
 
 /* ---- multi-GPU: z-slabs + NCCL -------------------------------- */
 /* One tsdf_comm per rank (one process per GPU, or G handles in one process).

@@ -84,6 +84,7 @@ SIGNATURES = {
     "tsdf_batch_get_stats": (_I, [_VP, C.POINTER(Stats)]),
     "tsdf_batch_download": (_I, [_VP, _I, _VP, _VP, _VP]),
     "tsdf_batch_extract_points": (_I, [_VP, _I, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
+    "tsdf_batch_extract_mesh": (_I, [_VP, _I, _VP, _VP, _VP, _I64, _VP, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
     "tsdf_comm_unique_id": (_I, [_VP]),
     "tsdf_comm_create": (_I, [_VP, _I, _I, _I, C.POINTER(_VP)]),
     "tsdf_comm_destroy": (_I, [_VP]),

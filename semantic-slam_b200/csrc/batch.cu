@@ -268,3 +268,12 @@ extern "C" int tsdf_batch_extract_points(tsdf_batch* b, int instance, int predic
   if (rc) return rc;
   return tsdf_extract_points(b->vols[instance], predicate, tsdf_thresh, weight_thresh, xyz, rgb, idx, cap, count);
 }
+
+extern "C" int tsdf_batch_extract_mesh(tsdf_batch* b, int instance, float* verts, float* norms, uint8_t* colors,
+                                       int64_t vcap, int32_t* faces, int64_t fcap, int64_t* n_verts,
+                                       int64_t* n_faces) {
+  REQUIRE(b && instance >= 0 && instance < b->n, "bad argument");
+  int rc = tsdf_batch_sync(b);
+  if (rc) return rc;
+  return tsdf_extract_mesh(b->vols[instance], verts, norms, colors, vcap, faces, fcap, n_verts, n_faces);
+}

@@ -350,6 +350,18 @@ class Batch:
         check(self.lib.tsdf_batch_download(self.h, int(i), ptr(t), ptr(w), ptr(c)))
         return t, w, c
 
+    def extract_mesh(self, i):
+        """verts, faces, norms, colors of instance i (tsdf_batch_extract_mesh)."""
+        nv, nf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_batch_extract_mesh(self.h, int(i), None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
+        verts = np.zeros((max(nv.value, 1), 3), np.float32)
+        norms = np.zeros((max(nv.value, 1), 3), np.float32)
+        cols = np.zeros((max(nv.value, 1), 3), np.uint8)
+        faces = np.zeros((max(nf.value, 1), 3), np.int32)
+        check(self.lib.tsdf_batch_extract_mesh(self.h, int(i), ptr(verts), ptr(norms), ptr(cols), nv.value, ptr(faces),
+                                               nf.value, C.byref(nv), C.byref(nf)))
+        return verts[:nv.value], faces[:nf.value], norms[:nv.value], cols[:nv.value]
+
 
 class TSDF:
     """Mirror of the reference's `class TSDF` (include/tsdf.hpp:22-98).

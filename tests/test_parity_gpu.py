@@ -428,6 +428,10 @@ def test_batched_instances_cropped_masks_equal_full_masks(pkg, oracle, synth):
                     md = (d * (masks[i] >= 128)).astype(np.float32)
                     oracle.integrate(p, T.reshape(16), md, oracle.pack_color(rgb), 1.0, t, w, c)
             assert_volume_equal(ct, cw, cc, t, w, c)
+            # per-object mesh (tsdf_batch_extract_mesh) of the same instance volume
+            gm, om = crop.extract_mesh(i), oracle.mesh(p, t, c)
+            assert np.array_equal(gm[1], om[1]) and np.array_equal(bits(gm[0]), bits(om[0]))
+            assert np.array_equal(bits(gm[2]), bits(om[2])) and np.array_equal(gm[3], om[3])
 
 
 def test_full_size_properties_c1(pkg, synth):
