@@ -482,6 +482,23 @@ def extras(pkg, line, frames, origin, vol=None):
                 mesh = {"mesh_sweep_ms": mesh_sweep_ms, "mesh_emit_to_host_ms": mesh_emit_ms,
                         "mesh_sweep_GBps": 5.5 * 512 ** 3 / (mesh_sweep_ms * 1e-3) / 1e9,
                         "mesh_vertices": mnv, "mesh_faces": mnf}
+                # reported CPU baseline of the same readback: the oracle's marching cubes (one host
+                # thread) on the same 512^3 volume, counting pass only (what mesh_sweep_ms does)
+                try:
+                    import ctypes as _C
+                    from oracle.oracle import Oracle
+                    orc = Oracle()
+                    t2 = v2.download()[0]
+                    p2 = orc.params(dims, vs, cfg.trunc_margin, o2, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth,
+                                    pkg.SEM_FUSIONPY)
+                    nf_c = _C.c_int64(0)
+                    t0 = time.perf_counter()
+                    nv_c = int(orc.lib.oracle_mesh(_C.byref(p2), t2, None, None, None, None, 0, None, 0, _C.byref(nf_c)))
+                    mesh["mesh_cpu_oracle_count_ms"] = (time.perf_counter() - t0) * 1e3
+                    mesh["mesh_cpu_oracle_agrees"] = bool((nv_c, nf_c.value) == (mnv, mnf))
+                    del t2
+                except Exception as e:
+                    mesh["mesh_cpu_oracle_error"] = str(e)
             except Exception as e:
                 mesh = {"mesh_error": str(e)}
         line["extra_c2"] = {"workload": "C2: 300 frames (12 distinct, fr3_office keyframe poses) into 512^3 @ 1 cm, "

@@ -17,6 +17,10 @@
  *                 andyzeng/tsdf-fusion-python (no pinned version; call site
  *                 src/TSDFfusion.py.in:43).  Its source is not available offline:
  *                 PARITY UNPINNED for the colour/obs_weight extension.
+ *   mesh        : oracle_mesh restates the skimage-independent parts of the same third-party
+ *                 get_mesh()/meshwrite (src/TSDFfusion.py.in:48-53); skimage itself is absent and
+ *                 un-pinned: PARITY UNPINNED, vertex/face order is this repository's definition,
+ *                 validated through the properties in tests/test_mesh.py.
  *
  * Arithmetic discipline: every operation is one IEEE-754 fp32 round-to-nearest-even op in
  * the source order of the reference, with NO fused multiply-add.  Build with
