@@ -620,6 +620,26 @@ def test_more_than_2_31_voxels(pkg, oracle, synth, sem):
         assert touched > 10 ** 4
         with pytest.raises(Exception):
             vol.download_range(n - 10, 11)
+        # mesh readback past voxel 2^31 (64-bit coordinate decode, tile offsets and record indices): the
+        # 8-wide, 4-wide and scalar sweeps agree, every vertex lies on its grid edge inside the volume
+        counts = []
+        for variant in (0, 262144, 65536):
+            vol.set_variant(variant)
+            vol.upload()                                  # no arrays: invalidates the cached sweep
+            counts.append(vol.mesh_count())
+        vol.set_variant(0)
+        assert counts[0] == counts[1] == counts[2] and counts[0][0] > 10 ** 5 and counts[0][1] > 10 ** 5
+        mv, mf, mn, _ = vol.extract_mesh()
+        assert mf.min() >= 0 and mf.max() == len(mv) - 1
+        q = (mv.astype(np.float64) - np.asarray(origin, np.float32).astype(np.float64)) / float(np.float32(vs))
+        assert q.min() > -1e-3 and np.all(q.max(0) < np.array(dims) - 1 + 1e-3)
+        off_grid = np.abs(q - np.round(q)) > 2e-3         # exactly one coordinate of a vertex is fractional (or none)
+        assert off_grid.sum(1).max() <= 1
+        # the three vertices of a triangle sit on edges of ONE cell (a wrong 64-bit rank would point far away);
+        # the edge audit itself (every edge shared by two triangles) runs at sizes the host can sort, tests/test_mesh.py
+        tri = q[mf[:: max(1, len(mf) // 200000)]]
+        assert (tri.max(1) - tri.min(1)).max() <= 1 + 4e-3
+        assert np.all(np.floor(tri.min(1) + 2e-3) + 1 >= tri.max(1) - 2e-3)
 
 
 def test_handles_driven_from_different_host_threads(pkg, oracle, synth):
