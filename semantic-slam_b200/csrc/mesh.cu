@@ -44,7 +44,7 @@ struct MeshP {
   float o[3], vs;
   const float* t;
   const float* color;
-  // i / n_fast and row / n_mid as multiply-shift, exact for dividends below 2^31 (k_mc_mark4)
+  // i / n_fast and row / n_mid as multiply-shift, exact for dividends below 2^31 (k_mc_mark4 / 8)
   uint32_t magic_f, shift_f, magic_m, shift_m;
 };
 
@@ -136,15 +136,14 @@ k_mc_mark(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
 // The same pass for fast axes that are a multiple of 4 voxels: a thread owns 4 consecutive voxels
 // (four LDG.128 — its own run and the runs one step along mid, slow and mid+slow — instead of 32
 // scalar loads; the fifth value along the fast axis comes from the next lane by shuffle, lane 31
-// loads it) and stores its four case bytes as one word.  Everything after the 20 compares is
-// integer bit arithmetic on 5-bit row masks (the first form, with per-voxel booleans, ballots and
-// selects, was ALU-bound at 83 % pipe utilisation: profiles/r1_v9_mesh_mark4_v1.txt):
-//   edges   (m0 ^ m0>>1), (m0 ^ m_mid), (m0 ^ m_slow)            one nibble per axis per thread
-//   cases   4x4 bit transpose by multiplication: S(m) = (m * 0x00204081) & 0x01010101 puts bit j
-//           of m at bit 8j; the four rows land at their corner positions, the run shifted by one
-//           voxel supplies the other four corners
-//   record  a run leaves its three nibbles and its triangle count in one shared-memory word; after
-//           the block barrier 64 threads assemble the 64 groups' record words from eight runs each
+// loads it) and stores its four case bytes as one word.  Per row the four inside tests become one
+// word of 0x00/0xff bytes (sign_bytes2 below), and everything after that is bit arithmetic on whole
+// words (the first form, with per-voxel booleans, 24 ballots and selects, was ALU-bound at 83 % pipe
+// utilisation; every step is in profiles/r1_v9_mesh_kernels_ncu.jsonl):
+//   edges   S0 ^ H0 (H = the row shifted by one voxel), S0 ^ S_mid, S0 ^ S_slow, one bit per byte
+//   cases   the eight corner bits of four cells are eight (byte mask & constant) terms of one OR chain
+//   record  a run leaves its edge bits and its triangle count in one shared-memory word; after the
+//           block barrier every thread gathers one (group, axis) record word from eight runs
 //           (redux.sync under per-group masks compiles to a loop over the masks: measured slower)
 //           — records, offsets and the two emit kernels are the scalar pass's.
 // Coordinates come from a multiply-shift division (exact for indices below 2^31; host-made magic).
@@ -198,7 +197,7 @@ k_mc_mark4(MeshP p, uint4* __restrict__ recs, uint8_t* __restrict__ cases,
       m = (uint32_t)(row - (int64_t)s * p.n_mid);
     }
     // the run has a neighbour run along fast / mid / slow; a missing neighbour row aliases the run's
-    // own row, which makes its edge nibble (m0 ^ m_row) zero without a select
+    // own row, which makes its edge bits (S0 ^ S_row) zero without a select
     const bool hf4 = live && (int)f + 4 < p.n_fast, hm = live && (int)m + 1 < p.n_mid,
                hs = live && (int)s + 1 < n_slow;
     const float* q[4];
