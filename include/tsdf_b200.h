@@ -308,6 +308,16 @@ int tsdf_invert_matrix(const float m[16], float out[16]); /* src/tsdf.cu:276-403
  * cap = 0 to size).  TSDF_E_IO on open/parse failure, TSDF_E_CAPACITY if cap is too small.  */
 int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int* n_cams);
 
+/* Pose ingest for the stereo / lidar run: `CameraTrajectory.txt` (SaveTrajectoryKITTI,
+ * src/ORB_SLAM2/System.cc:455-508, written by examples/stereo_kitti.cpp:113) — one line per tracked
+ * frame, 12 values = the 3x4 row-major [Rwc | twc] relative to the first keyframe, i.e. already the
+ * camera-to-world pose Integrate takes.  Twc: cap*16 floats (fourth row 0 0 0 1 added) or NULL;
+ * *n_poses receives the line count (cap = 0 to size).  TSDF_E_IO / TSDF_E_CAPACITY as above.     */
+int tsdf_read_trajectory_kitti(const char* path, float* Twc, int cap, int* n_poses);
+/* `frame_id.txt` (SaveFrameId, src/ORB_SLAM2/System.cc:1104-1121, examples/stereo_kitti.cpp:117):
+ * the sequence frame number of every good keyframe, one per line, in bundle.txt's camera order. */
+int tsdf_read_frame_ids(const char* path, int64_t* ids, int cap, int* n_ids);
+
 /* Image-name ingest for the same replay: `associations.txt` of a saved run (written by
  * src/ORB_SLAM2/System.cc:981; one line per keyframe "<t_rgb> <rgb file> <t_depth> <depth file>",
  * parsed by LoadImageNames, examples/label_instance_rgbd.cpp:239-268, which pairs line i with

@@ -101,6 +101,8 @@ SIGNATURES = {
     "tsdf_multiply_matrix": (None, [_VP, _VP, _VP]),
     "tsdf_invert_matrix": (_I, [_VP, _VP]),
     "tsdf_read_bundle_poses": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
+    "tsdf_read_trajectory_kitti": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
+    "tsdf_read_frame_ids": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
     "tsdf_read_associations": (_I, [C.c_char_p, _VP, _VP, _VP, _VP, _I, _I, C.POINTER(_I)]),
     "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
     "tsdf_set_variant": (_I, [_VP, _I]),

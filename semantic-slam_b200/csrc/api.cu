@@ -963,6 +963,75 @@ extern "C" int tsdf_read_bundle_poses(const char* path, float* Twc, int cap, int
   return TSDF_OK;
 }
 
+// CameraTrajectory.txt of the stereo / lidar run (src/ORB_SLAM2/System.cc:455-508, written by
+// examples/stereo_kitti.cpp:113): one line per tracked frame, the 3x4 row-major [Rwc | twc] relative
+// to the first keyframe — already camera-to-world, what Integrate takes; the fourth row is added.
+extern "C" int tsdf_read_trajectory_kitti(const char* path, float* Twc, int cap, int* n_poses) {
+  REQUIRE(path && n_poses, "null argument");
+  FILE* f = fopen(path, "r");
+  if (!f) { tsdf_set_error("tsdf_read_trajectory_kitti: cannot open %s", path); return TSDF_E_IO; }
+  char line[2048];
+  int n = 0, rc = TSDF_OK;
+  while (fgets(line, sizeof line, f)) {
+    float v[12];
+    const int got = sscanf(line, "%f %f %f %f %f %f %f %f %f %f %f %f", &v[0], &v[1], &v[2], &v[3], &v[4], &v[5],
+                           &v[6], &v[7], &v[8], &v[9], &v[10], &v[11]);
+    if (got < 0) continue;  // empty line (sscanf: EOF before the first conversion)
+    if (got != 12) {
+      tsdf_set_error("tsdf_read_trajectory_kitti: line %d of %s has %d values, not 12", n + 1, path, got);
+      rc = TSDF_E_IO;
+      break;
+    }
+    if (Twc && n < cap) {
+      float* T = Twc + 16 * (size_t)n;
+      for (int k = 0; k < 12; ++k) T[k] = v[k];
+      T[12] = T[13] = T[14] = 0.0f;
+      T[15] = 1.0f;
+    }
+    ++n;
+  }
+  fclose(f);
+  if (rc) return rc;
+  *n_poses = n;
+  if (Twc && cap > 0 && cap < n) {
+    tsdf_set_error("tsdf_read_trajectory_kitti: capacity %d < %d poses", cap, n);
+    return TSDF_E_CAPACITY;
+  }
+  return TSDF_OK;
+}
+
+// frame_id.txt (src/ORB_SLAM2/System.cc:1104-1121, examples/stereo_kitti.cpp:117): the frame number
+// of every good keyframe, one per line, in the keyframe order of bundle.txt — which image of the
+// sequence belongs to camera i of the bundle.
+extern "C" int tsdf_read_frame_ids(const char* path, int64_t* ids, int cap, int* n_ids) {
+  REQUIRE(path && n_ids, "null argument");
+  FILE* f = fopen(path, "r");
+  if (!f) { tsdf_set_error("tsdf_read_frame_ids: cannot open %s", path); return TSDF_E_IO; }
+  char line[256];
+  int n = 0, rc = TSDF_OK;
+  while (fgets(line, sizeof line, f)) {
+    long long v = 0;
+    char extra = 0;
+    const int got = sscanf(line, "%lld %c", &v, &extra);
+    if (got < 0) continue;  // empty line
+    if (got != 1 || v < 0) {
+      tsdf_set_error("tsdf_read_frame_ids: bad line %d in %s", n + 1, path);
+      rc = TSDF_E_IO;
+      break;
+    }
+    if (ids && n < cap) ids[n] = (int64_t)v;
+    ++n;
+  }
+  fclose(f);
+  if (rc) return rc;
+  *n_ids = n;
+  if (ids && cap > 0 && cap < n) {
+    tsdf_set_error("tsdf_read_frame_ids: capacity %d < %d ids", cap, n);
+    return TSDF_E_CAPACITY;
+  }
+  return TSDF_OK;
+}
+
 extern "C" int tsdf_read_associations(const char* path, double* t_rgb, double* t_depth, char* rgb_names,
                                       char* depth_names, int name_stride, int cap, int* n_lines) {
   REQUIRE(path && n_lines, "null argument");

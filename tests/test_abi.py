@@ -161,3 +161,41 @@ def test_product_does_not_import_oracle():
                 txt = open(path, errors="replace").read()
                 assert not re.search(r"#include\s+[\"<][^\">]*oracle", txt), f"{f} includes oracle code"
                 assert "liboracle" not in txt and "libtsdf_ref" not in txt, f"{f} links oracle artefacts"
+
+
+def test_read_trajectory_kitti_and_frame_ids(pkg, synth, tmp_path):
+    """CameraTrajectory.txt as SaveTrajectoryKITTI writes it (src/ORB_SLAM2/System.cc:502-505: `fixed`,
+    setprecision(9), the 3x4 [Rwc | twc] row by row) and frame_id.txt (:1104-1121, one integer per line)."""
+    lib = pkg.load()
+    rng = np.random.default_rng(8)
+    poses = [synth.pose(synth.rot_xyz(*rng.uniform(-1, 1, 3)), rng.uniform(-50, 50, 3)).reshape(4, 4) for _ in range(7)]
+    path = tmp_path / "CameraTrajectory.txt"
+    with open(path, "w") as f:
+        for T in poses:
+            f.write(" ".join("%.9f" % float(v) for v in T[:3].reshape(-1)) + "\n")
+        f.write("\n")
+    n = C.c_int(0)
+    p = str(path).encode()
+    assert lib.tsdf_read_trajectory_kitti(p, None, 0, C.byref(n)) == 0 and n.value == 7
+    T = np.zeros((7, 16), np.float32)
+    assert lib.tsdf_read_trajectory_kitti(p, T.ctypes.data_as(C.c_void_p), 3, C.byref(n)) == pkg.capi.E_CAPACITY
+    assert lib.tsdf_read_trajectory_kitti(p, T.ctypes.data_as(C.c_void_p), 7, C.byref(n)) == 0 and n.value == 7
+    for got, want in zip(T.reshape(7, 4, 4), poses):
+        # "%.9f" of a float32 parses back to the same float32 for |x| < 2^6 or so; translations up to 50 m
+        # keep 9 decimals >> the 2^-18 spacing of float32 there
+        assert np.array_equal(got[:3], np.float32([[float("%.9f" % float(v)) for v in r] for r in want[:3]]))
+        assert list(got[3]) == [0, 0, 0, 1]
+    (tmp_path / "bad.txt").write_text("1 0 0 0 0 1 0 0 0 0 1\n")
+    assert lib.tsdf_read_trajectory_kitti(str(tmp_path / "bad.txt").encode(), None, 0, C.byref(n)) == pkg.capi.E_IO
+    assert "11 values" in lib.tsdf_last_error().decode()
+    assert lib.tsdf_read_trajectory_kitti(str(tmp_path / "missing.txt").encode(), None, 0, C.byref(n)) == pkg.capi.E_IO
+
+    ids = [0, 3, 17, 18, 4540]
+    (tmp_path / "frame_id.txt").write_text("".join("%d\n" % i for i in ids))
+    q = str(tmp_path / "frame_id.txt").encode()
+    assert lib.tsdf_read_frame_ids(q, None, 0, C.byref(n)) == 0 and n.value == 5
+    out = np.zeros(5, np.int64)
+    assert lib.tsdf_read_frame_ids(q, out.ctypes.data_as(C.c_void_p), 2, C.byref(n)) == pkg.capi.E_CAPACITY
+    assert lib.tsdf_read_frame_ids(q, out.ctypes.data_as(C.c_void_p), 5, C.byref(n)) == 0 and list(out) == ids
+    (tmp_path / "bad_ids.txt").write_text("12\nx\n")
+    assert lib.tsdf_read_frame_ids(str(tmp_path / "bad_ids.txt").encode(), None, 0, C.byref(n)) == pkg.capi.E_IO
