@@ -36,6 +36,8 @@ UNIT = "Gvox/s"
 DIM = int(os.environ.get("TSDF_BENCH_DIM", "1024"))
 VS = float(os.environ.get("TSDF_BENCH_VS", "0.002"))
 N_DISTINCT = 4
+SPHERE = os.environ.get("TSDF_BENCH_SPHERE", "1") != "0"
+WINDOWS = max(1, int(os.environ.get("TSDF_BENCH_WINDOWS", "5")))
 
 
 def peaks():
@@ -111,15 +113,24 @@ def visible_index(local_rank):
 # ----------------------------------------------------------------------------------------
 # CPU arms (test infrastructure: the one place bench.py may execute oracle/)
 # ----------------------------------------------------------------------------------------
-def cpu_sample(frames, origin, dims, vs, want_seconds=12.0):
-    """Times the reference's CPU arithmetic on a z-slab sample of the same workload, all host
-    cores.  Returns dict(ref=..., port=...) in Gvox/s plus the sample description."""
+def host_threads():
+    """Threads the CPU arms may use: the cores this process is allowed on (cgroup / affinity aware)."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def cpu_sample(frames, origin, dims, vs, want_seconds=10.0):
+    """Times the reference's CPU arithmetic on a bounded z-slab sample of the same workload, all
+    host threads (set explicitly: a launcher may export OMP_NUM_THREADS=1; the count REPORTED is
+    what the OpenMP runtime says it will use).  Returns dict(ref=..., port=...) in Gvox/s."""
     from oracle.oracle import Oracle, RefLift, ref_available, SEM_FUSIONPY
     synth = importlib.import_module("semantic-slam_b200.synth")
-    cores = os.cpu_count() or 1
     depth, rgb, T = frames[0]
     trunc = np.float32(vs) * np.float32(5)
     o = Oracle(omp=True)
+    out = {"cores": o.set_threads(host_threads())}
     packed = o.pack_color(rgb)
 
     def run_port(nz):
@@ -129,52 +140,58 @@ def cpu_sample(frames, origin, dims, vs, want_seconds=12.0):
         o.integrate(p, T.reshape(16), depth, packed, 1.0, t, w, c)
         return dims[0] * dims[1] * nz / (time.perf_counter() - t0) / 1e9
 
-    def run_ref(nz):
-        r = RefLift(omp=True)
-        n = dims[0] * dims[1] * nz
-        t, w = np.ones(n, np.float32), np.zeros(n, np.float32)
-        t0 = time.perf_counter()
-        r.integrate(synth.TUM3_K, T.reshape(16), depth, (dims[0], dims[1], nz), origin, vs, trunc, t, w)
-        return n / (time.perf_counter() - t0) / 1e9
-
-    out = {"cores": cores}
     probe = max(4, min(dims[2], 8))
     rate = run_port(probe)
     nz = int(min(dims[2], max(probe, want_seconds * rate * 1e9 / (dims[0] * dims[1]))))
     out["port"] = run_port(nz)
-    out["port_sample"] = f"1 frame into a {dims[0]}x{dims[1]}x{nz} z-slab of the {dims[0]}x{dims[1]}x{dims[2]} grid (colour, obs_weight)"
+    out["port_sample"] = (f"1 frame into a {dims[0]}x{dims[1]}x{nz} z-slab of the {dims[0]}x{dims[1]}x{dims[2]} grid, "
+                          f"oracle/tsdf_oracle.c (OpenMP), depth+weight+colour, obs_weight (24 B/voxel, like the B200 arm)")
     if ref_available("omp"):
+        r = RefLift(omp=True)
+        out["ref_cores"] = r.set_threads(host_threads())
+
+        def run_ref(nz):
+            n = dims[0] * dims[1] * nz
+            t, w = np.ones(n, np.float32), np.zeros(n, np.float32)
+            t0 = time.perf_counter()
+            r.integrate(synth.TUM3_K, T.reshape(16), depth, (dims[0], dims[1], nz), origin, vs, trunc, t, w)
+            return n / (time.perf_counter() - t0) / 1e9
         rate = run_ref(probe)
         nz2 = int(min(dims[2], max(probe, want_seconds * rate * 1e9 / (dims[0] * dims[1]))))
         out["ref"] = run_ref(nz2)
-        out["ref_sample"] = f"1 frame into a {dims[0]}x{dims[1]}x{nz2} z-slab (reference's own GpuIntegrate lines as CPU C++, depth+weight only)"
+        out["ref_sample"] = (f"1 frame into a {dims[0]}x{dims[1]}x{nz2} z-slab (the reference's own GpuIntegrate lines "
+                             f"src/tsdf.cu:15-60 as CPU C++, OpenMP over z; depth+weight only, 16 B/voxel)")
     return out
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's own CPU implementation of the path, all host threads,
-    on this arm's config/metric/unit; each step is a bounded z-slab sample of the workload."""
+    """--impl reference: the reference's own CPU implementation of the path (oracle/_ref =
+    src/tsdf.cu:15-60 compiled as CPU C++) on the box's host threads.  Each step integrates one
+    frame into the WHOLE 1024^3 grid (8.6 GB of host arrays), so ms_per_step is measured, not
+    extrapolated; only when a probe says the run could not end within a few minutes (a box with a
+    handful of threads) is a step a z-slab sample, and then ms_per_step is the sample's own time."""
     if rank != 0:
         return
     from oracle.oracle import Oracle, RefLift, ref_available, SEM_FUSIONPY
     synth = importlib.import_module("semantic-slam_b200.synth")
     dims = (DIM, DIM, DIM)
-    origin, frames = synth.s_full(dims, VS, n_frames=N_DISTINCT)
-    cores = os.cpu_count() or 1
+    origin, frames = bench_frames(synth, dims)
     trunc = np.float32(VS) * np.float32(5)
     use_ref = ref_available("omp")
-    # size one step to ~1.5 s of CPU work
-    probe = 4
+    probe = 8
     if use_ref:
         r = RefLift(omp=True)
+        threads = r.set_threads(host_threads())
 
         def step(nz, f, state):
             d, _, T = frames[f % N_DISTINCT]
             r.integrate(synth.TUM3_K, T.reshape(16), d, (dims[0], dims[1], nz), origin, VS, trunc, state[0], state[1])
         kind = "reference"
-        what = "reference's own src/tsdf.cu:15-60 lines compiled as CPU C++ (OpenMP over z; depth+weight only: the colour path is third-party and un-vendored)"
+        what = ("the reference's own src/tsdf.cu:15-60 lines compiled as CPU C++ (oracle/_ref, OpenMP over z); "
+                "depth+weight only, 16 B/voxel: the colour path is third-party and un-vendored")
     else:
         o = Oracle(omp=True)
+        threads = o.set_threads(host_threads())
         packed = [o.pack_color(f[1]) for f in frames]
 
         def step(nz, f, state):
@@ -182,17 +199,23 @@ def run_reference(args, rank, world):
             p = o.params(dims, VS, trunc, origin, d.shape, synth.TUM3_K, np.inf, SEM_FUSIONPY, (0, nz))
             o.integrate(p, T.reshape(16), d, packed[f % N_DISTINCT], 1.0, state[0], state[1], state[2])
         kind = "port"
-        what = "oracle/tsdf_oracle.c restatement (OpenMP, colour)"
+        what = "oracle/tsdf_oracle.c restatement (OpenMP, depth+weight+colour)"
 
     def new_state(nz):
         n = dims[0] * dims[1] * nz
-        return [np.ones(n, np.float32), np.zeros(n, np.float32), np.zeros(n, np.float32)]
+        st = [np.ones(n, np.float32), np.zeros(n, np.float32)]
+        if not use_ref:
+            st.append(np.zeros(n, np.float32))
+        return st
     st = new_state(probe)
-    t0 = time.perf_counter()
     step(probe, 0, st)
+    t0 = time.perf_counter()
+    step(probe, 1, st)
     rate = dims[0] * dims[1] * probe / (time.perf_counter() - t0)
-    budget = 120.0 / max(1, args.steps + args.warmup)
-    nz = int(min(dims[2], max(probe, min(1.5, budget) * rate / (dims[0] * dims[1]))))
+    n_steps = max(1, args.steps + args.warmup)
+    nz = dims[2]
+    if n_steps * dims[0] * dims[1] * dims[2] / rate > 240.0:     # would not end within a few minutes
+        nz = int(min(dims[2], max(probe, 240.0 / n_steps * rate / (dims[0] * dims[1]))))
     st = new_state(nz)
     for i in range(args.warmup):
         step(nz, i, st)
@@ -201,24 +224,61 @@ def run_reference(args, rank, world):
         step(nz, i, st)
     dt = time.perf_counter() - t0
     gvox = args.steps * dims[0] * dims[1] * nz / dt / 1e9
-    sample = f"each step = 1 frame into a {dims[0]}x{dims[1]}x{nz} z-slab of the {DIM}^3 grid; {what}"
+    whole = nz == dims[2]
+    sample = (f"each step = 1 frame into {'the WHOLE' if whole else 'a'} {dims[0]}x{dims[1]}x{nz} "
+              f"{'grid' if whole else f'z-slab sample of the {DIM}^3 grid (ms_per_step is the sample, not extrapolated)'}; {what}")
     line = {"impl": "reference", "metric": METRIC, "value": gvox, "unit": UNIT, "n_gpus": args.gpus,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3 * (dims[2] / nz),
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "config": workload_config(args.gpus),
-            "cpu_baseline": {"value": gvox, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "cpu_baseline": {"value": gvox, "unit": UNIT, "cores": threads, "kind": kind, "sample": sample,
+                             "omp_num_threads_env": os.environ.get("OMP_NUM_THREADS"),
+                             "cpu_count": os.cpu_count()},
             "e2e": {"value": gvox, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
+    # like-for-like beside it: the colour-capable port (24 B/voxel, what the B200 arm computes) on a
+    # bounded z-slab sample
+    try:
+        o2 = Oracle(omp=True)
+        o2.set_threads(host_threads())
+        d, rgb, T = frames[0]
+        nzp = 32
+        p = o2.params(dims, VS, trunc, origin, d.shape, synth.TUM3_K, np.inf, SEM_FUSIONPY, (0, nzp))
+        t, w, c = o2.new_volume(p, True)
+        pc = o2.pack_color(rgb)
+        o2.integrate(p, T.reshape(16), d, pc, 1.0, t, w, c)
+        t0 = time.perf_counter()
+        o2.integrate(p, T.reshape(16), d, pc, 1.0, t, w, c)
+        line["cpu_baseline"]["port_with_colour"] = {
+            "value": dims[0] * dims[1] * nzp / (time.perf_counter() - t0) / 1e9, "unit": UNIT,
+            "sample": f"1 frame into a {dims[0]}x{dims[1]}x{nzp} z-slab, oracle/tsdf_oracle.c OpenMP, depth+weight+colour (24 B/voxel)"}
+    except Exception as e:
+        line["cpu_baseline"]["port_with_colour"] = {"error": str(e)}
     print(json.dumps(line))
 
 
+def bench_frames(synth, dims):
+    """The bench workload's frames (both arms): S-full with a sphere inside the volume, so that the
+    readback leg has a surface to extract (BASELINE config 4: "... with point-cloud extraction
+    readback"); seeded, identical on every rank."""
+    return synth.s_full(dims, VS, n_frames=N_DISTINCT, sphere=SPHERE)
+
+
 def workload_config(n_gpus):
+    """Identical in both arms (the driver compares them)."""
+    scene = ("S-full + a 0.31 m sphere inside the volume (every voxel in view and in front of the wall; all "
+             "but the sphere's interior/shadow, ~5 %, written every frame)") if SPHERE else \
+        "S-full (every voxel written every frame)"
     return {"workload": f"C4: {DIM}^3 fp32 tsdf+weight+packed-RGB volume, {VS*1000:g} mm voxels, 640x480 RGB-D "
-                        f"frames (TUM3 intrinsics), scene S-full (every voxel written every frame), "
-                        f"FUSIONPY semantics (colour + obs_weight)",
+                        f"frames (TUM3 intrinsics), scene {scene}, FUSIONPY semantics (colour + obs_weight)",
             "grid": [DIM, DIM, DIM], "frame": [480, 640], "sharding": f"{n_gpus} z-slab(s), one process per GPU",
             "l2": "inputs larger than L2 (volume slab >= 1.6 GB per GPU vs 126 MB L2)",
-            "distinct_frames": N_DISTINCT}
+            "distinct_frames": N_DISTINCT,
+            "arms": "b200 arm: depth+weight+colour, 24 B per written voxel; --impl reference arm: the reference's "
+                    "first-party CPU lines (src/tsdf.cu:15-60) integrate depth+weight only, 16 B per written voxel "
+                    "(its colour path is third-party, un-vendored) - it does LESS work per voxel; the "
+                    "colour-capable CPU port is reported beside it (cpu_baseline.port_with_colour)",
+            "timing": f"median of {WINDOWS} timed windows of --steps steps each (min/max reported)"}
 
 
 # ----------------------------------------------------------------------------------------
@@ -268,7 +328,7 @@ def run_b200(args, rank, world, local_rank):
         tdev = torch.device("cuda", local_rank)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=tdev)
     dims = (DIM, DIM, DIM)
-    origin, frames = synth.s_full(dims, VS, n_frames=N_DISTINCT)  # seeded: identical on every rank
+    origin, frames = bench_frames(synth, dims)  # seeded: identical on every rank
     H, W = frames[0][0].shape
     cfg = pkg.make_config(dims, VS, origin, semantics=pkg.SEM_FUSIONPY, with_color=True, device=local_rank)
     if world > 1:
@@ -279,6 +339,13 @@ def run_b200(args, rank, world, local_rank):
         sv, vol = None, pkg.Volume(cfg)
     df = DeviceFrames(pkg, local_rank, frames) if rank == 0 else None
     n_total = DIM ** 3
+    lib = pkg.load()
+
+    def launches():
+        import ctypes as C
+        n = C.c_int64(0)
+        pkg.capi.check(lib.tsdf_launch_count(C.byref(n)))
+        return n.value
 
     def barrier():
         vol.sync()
@@ -300,53 +367,57 @@ def run_b200(args, rank, world, local_rank):
         else:
             vol.integrate(d, c, T, sync=False)
 
-    def max_over_ranks(x):
+    def reduce_ranks(x, op):
         if world == 1:
             return x
         import torch
         t = torch.tensor([x], dtype=torch.float64, device=tdev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t, op=getattr(dist.ReduceOp, op))
         return float(t.item())
 
-    def sum_over_ranks(x):
-        if world == 1:
-            return x
-        import torch
-        t = torch.tensor([x], dtype=torch.float64, device=tdev)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
-
-    def timed(host, steps, extract_at_end=False):
+    def readback():
+        """The job's point-cloud readback (BASELINE config 4): extraction on every rank, records
+        gathered to rank 0 and merged to reference order, into caller (host) arrays.  Host clock
+        around the blocking call, barrier on both sides, max over ranks."""
         barrier()
-        vol.kernel_timing(True)
+        t0 = time.perf_counter()
+        if sv is not None:
+            _, _, _, n_pts = sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5)
+        else:
+            n_pts = len(vol.extract_points(pkg.PRED_ABS_LT, 0.999, 0.5)[2])
+        ms = (time.perf_counter() - t0) * 1e3
+        return reduce_ranks(ms, "MAX"), n_pts
+
+    def timed(host, steps):
+        """WINDOWS timed windows of `steps` steps each; every window is bracketed by a barrier + sync
+        on both sides and timed with CUDA events on the compute stream, max over ranks."""
+        wins, ksum_all, kn_all, launched = [], 0.0, 0, 0
         sampler = ClockSampler(visible_index(local_rank))
         sampler.start()
-        vol.timer_start()
-        for i in range(steps):
-            step(i, host)
-        n_pts = None
-        ext_ms = None
-        ms = vol.timer_stop()
-        if extract_at_end:
-            # one surface-extraction pass (count + records to the host) after the timed region:
-            # a blocking readback call, timed by the host clock and reported beside the e2e value
-            t_host0 = time.perf_counter()
-            if sv is not None:
-                _, _, _, n_pts = sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5)
-            else:
-                n_pts = len(vol.extract_points(pkg.PRED_ABS_LT, 0.999, 0.5)[2])
-            ext_ms = (time.perf_counter() - t_host0) * 1e3
+        for _ in range(WINDOWS):
+            barrier()
+            vol.kernel_timing(True)
+            l0 = launches()
+            vol.timer_start()
+            for i in range(steps):
+                step(i, host)
+            ms = vol.timer_stop()
+            launched = launches() - l0
+            ksum, kn = vol.kernel_timing_read(reset=True)
+            vol.kernel_timing(False)
+            ksum_all += ksum
+            kn_all += kn
+            wins.append(reduce_ranks(ms, "MAX"))
         clocks = sampler.result()
-        ksum, kn = vol.kernel_timing_read(reset=True)
-        vol.kernel_timing(False)
         written = vol.stats().voxels_written  # last launch, this rank
         if world > 1:
             dist.barrier()
-        return max_over_ranks(ms), ksum, kn, written, clocks, n_pts, ext_ms
+        return wins, ksum_all, kn_all, written, clocks, launched
 
     for i in range(args.warmup):
         step(i, False)
-    ms, ksum, kn, written, clocks, _, _ = timed(False, args.steps)
+    wins, ksum, kn, written, clocks, launched = timed(False, args.steps)
+    ms = float(np.median(wins))
     value = args.steps * n_total / (ms * 1e-3) / 1e9
     # roofline of the integrate kernel on this rank's slab (rank 0 reports)
     k_ms = ksum / max(kn, 1)
@@ -355,40 +426,52 @@ def run_b200(args, rank, world, local_rank):
     achieved = alg_bytes / (k_ms * 1e-3) / 1e9
     for i in range(min(args.warmup, 3)):
         step(i, True)
-    # warm the extraction path too (first call allocates its scratch and loads its kernels)
-    if sv is not None:
-        sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5)
-    else:
-        vol.extract_count(pkg.PRED_ABS_LT, 0.999, 0.5)
-    ms_e, ksum_e, kn_e, _, clocks_e, n_pts, ext_ms = timed(True, args.steps, extract_at_end=True)
+    wins_e, ksum_e, kn_e, _, clocks_e, launched_e = timed(True, args.steps)
+    ms_e = float(np.median(wins_e))
     e2e = args.steps * n_total / (ms_e * 1e-3) / 1e9
-    written_total = sum_over_ranks(float(written))
+    written_total = reduce_ranks(float(written), "SUM")
+    readback()                                    # warm: first call allocates scratch / staging
+    vol.upload()                                  # no arrays: only invalidates the cached mark pass
+    rb_ms, n_pts = readback()
+    rb_bytes = (n_pts or 0) * (12 + 3 + 8)
 
     line = None
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
                 "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": dict(workload_config(world), frame_distribution=(
-                    "none (1 GPU)" if sv is None else "peer-pull fused into the prep kernel (NVLink, cudaIpc)"
-                    if sv.peer_pull() else "ncclBroadcast")),
+                "config": workload_config(world),
+                "frame_distribution": ("none (1 GPU)" if sv is None else sv.distribution()),
+                "windows": {"n": WINDOWS, "ms_per_step": [w / args.steps for w in wins],
+                            "min": min(wins) / args.steps, "max": max(wins) / args.steps},
                 "frames_per_sec": args.steps / (ms * 1e-3),
                 "coverage": written_total / n_total,
                 "clocks": clocks,
                 "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": H * W * 7, "d2h_bytes_per_step": 8,
                         "ms_per_step": ms_e / args.steps, "kernel_ms": ksum_e / max(kn_e, 1),
+                        "windows_ms_per_step": [w / args.steps for w in wins_e],
                         "sm_mhz": clocks_e.get("sm_mhz") if isinstance(clocks_e, dict) else None,
                         "includes": "per step: pinned-host frame H2D (+ distribution to the other ranks) + prep + "
                                     "integrate + the step's 8 B N_written written to host memory",
-                        "extraction_pass_after_ms": ext_ms, "extracted_points": n_pts},
-                "gpu_launches": int(args.steps * 3),  # k_frame_prep + k_integrate + k_publish per step
+                        "readback": {"what": "after the timed steps: surface extraction on every rank (|tsdf| < 0.999, "
+                                             "weight > 0.5), records gathered to rank 0 and merged to reference order, "
+                                             "xyz f32x3 + rgb u8x3 + idx i64 into host arrays; host clock, max over ranks",
+                                     "ms": rb_ms, "points": n_pts, "bytes_to_host": rb_bytes,
+                                     "GBps_to_host": rb_bytes / (rb_ms * 1e-3) / 1e9 if rb_ms else None},
+                        "value_with_readback": args.steps * n_total / ((ms_e + rb_ms) * 1e-3) / 1e9,
+                        "gpu_launches": int(launched_e)},
+                "gpu_launches": int(launched),
+                "gpu_launches_note": "counted by the library (every <<<>>> of libtsdf_b200.so on this rank) inside one "
+                                     "timed window of --steps steps",
                 "roofline": {"bound": "hbm", "kernel": "k_integrate<ZFAST,COLOR,NF=1,VEC=4>", "achieved": achieved,
                              "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(world),
+                             "traffic_source": "committed ncu capture (profiles/traffic.json, S-full without the sphere), "
+                                               "NOT measured in this run",
                              "peak_source": peak_src, "kernel_ms": k_ms, "launches_timed": kn,
                              "algorithmic_bytes_per_launch": alg_bytes,
-                             "note": "24 B x N_written + 8 B x H*W per launch on rank 0's slab; peak is the driver-measured "
-                                     "torch copy_ bandwidth, which this kernel's read/write stream can slightly exceed "
-                                     "(nominal HBM3e 8 TB/s: frac_nominal below)",
+                             "note": "24 B x N_written (exact, counted by the kernel) + 8 B x H*W per launch on rank 0's slab; "
+                                     "peak is the driver-measured torch copy_ bandwidth, which this kernel's read/write "
+                                     "stream can slightly exceed (nominal HBM3e 8 TB/s: frac_nominal below)",
                              "frac_nominal_8TBps": achieved / 8000.0}}
     return pkg, vol, sv, df, frames, origin, line
 

@@ -346,6 +346,10 @@ int tsdf_timer_stop(tsdf_vol* v, float* ms);
 /* Per-launch timing of the integrate kernel: when enabled every launch is
  * bracketed by its own CUDA event pair on the launching stream; read returns
  * the summed kernel ms and the number of launches since the last reset.     */
+/* Number of kernels this library has launched in this process so far (every <<<>>> of
+ * libtsdf_b200.so, all handles, all devices): the bench's `gpu_launches` is a difference of two
+ * reads around its timed window.                                              */
+int tsdf_launch_count(int64_t* n);
 int tsdf_kernel_timing(tsdf_vol* v, int enable);
 int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset);
 

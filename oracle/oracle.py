@@ -64,6 +64,8 @@ class Oracle:
         L.oracle_integrate_range.restype = C.c_int64
         L.oracle_integrate_range.argtypes = [C.POINTER(OracleParams), _f32p, _f32p, C.c_void_p, C.c_float,
                                              C.c_int64, C.c_int64, _f32p, _f32p, C.c_void_p]
+        L.oracle_count_trunc_ties.restype = C.c_int64
+        L.oracle_count_trunc_ties.argtypes = [C.POINTER(OracleParams), _f32p, _f32p]
         L.oracle_extract.restype = C.c_int64
         L.oracle_extract.argtypes = [C.POINTER(OracleParams), _f32p, _f32p, C.c_void_p, C.c_int,
                                      C.c_float, C.c_float, C.c_void_p, C.c_void_p, C.c_void_p,
@@ -87,6 +89,11 @@ class Oracle:
         L.oracle_save_ply.restype = C.c_int
         L.oracle_save_ply.argtypes = [C.c_char_p, C.POINTER(OracleParams), _f32p, _f32p, C.c_int,
                                       C.c_float, C.c_float]
+
+    def set_threads(self, n):
+        """OpenMP threads of the omp build, set explicitly; returns what the runtime will use."""
+        self.lib.oracle_set_threads(int(n))
+        return int(self.lib.oracle_max_threads())
 
     @staticmethod
     def params(dims, voxel_size, trunc, origin, im_hw, K, max_depth, semantics, z_range=None):
@@ -146,6 +153,11 @@ class Oracle:
         return int(self.lib.oracle_integrate(C.byref(p), np.ascontiguousarray(cam2base, np.float32).reshape(16),
                                              np.ascontiguousarray(depth, np.float32).reshape(-1), cp,
                                              np.float32(obs_weight), tsdf, weight, cv))
+
+    def count_trunc_ties(self, p, cam2base, depth):
+        """Voxels that reach src/tsdf.cu:49 with diff == -trunc exactly (where `<` and `<=` differ)."""
+        return int(self.lib.oracle_count_trunc_ties(C.byref(p), np.ascontiguousarray(cam2base, np.float32).reshape(16),
+                                                    np.ascontiguousarray(depth, np.float32).reshape(-1)))
 
     def integrate_range(self, p, cam2base, depth, color_packed, obs_weight, first, n, tsdf, weight, color):
         """As integrate, but only the voxels [first, first + n) of the slab's storage order
@@ -232,6 +244,10 @@ class RefLift:
         L.ref_invert_matrix.argtypes = [_f32p, _f32p]
         L.ref_save_ply.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float,
                                    C.c_float, C.c_float, _f32p, _f32p, C.c_float, C.c_float]
+
+    def set_threads(self, n):
+        self.lib.ref_set_threads(int(n))
+        return int(self.lib.ref_max_threads())
 
     def integrate(self, K, cam2base, depth, dims, origin, vs, trunc, tsdf, weight):
         H, W = depth.shape

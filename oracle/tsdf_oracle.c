@@ -201,6 +201,18 @@ int64_t oracle_integrate(const oracle_params* p, const float* cam2base, const fl
   const int z0 = p->z_begin, z1 = p->z_end, dzl = z1 - z0;
   const int sem = p->semantics;
   int64_t written = 0;
+  if (sem == SEM_FUSIONPY) {
+    /* voxels are independent, so the visiting order is free: walk the plugin's [x][y][z] storage
+     * order (z innermost) instead of the first-party nest, whose inner x loop would stride by
+     * Dy*Dz floats here — same results, but the timed CPU port is not a cache-miss benchmark */
+#pragma omp parallel for collapse(2) schedule(static) reduction(+ : written)
+    for (int x = 0; x < dx; ++x)
+      for (int y = 0; y < dy; ++y)
+        for (int z = z0; z < z1; ++z)
+          written += update_voxel(p, cam2base, depth, color_packed, obs_weight, x, y, z,
+                                  lin_index(sem, x, y, z - z0, dx, dy, dzl), tsdf, weight, color);
+    return written;
+  }
 #pragma omp parallel for collapse(2) schedule(static) reduction(+ : written)
   for (int z = z0; z < z1; ++z)
     for (int y = 0; y < dy; ++y)
@@ -208,6 +220,53 @@ int64_t oracle_integrate(const oracle_params* p, const float* cam2base, const fl
         written += update_voxel(p, cam2base, depth, color_packed, obs_weight, x, y, z,
                                 lin_index(sem, x, y, z - z0, dx, dy, dzl), tsdf, weight, color);
   return written;
+}
+
+/* OpenMP control for the timed CPU arms (bench.py): torch.distributed.run exports
+ * OMP_NUM_THREADS=1 to its workers, so the thread count is set explicitly and REPORTED from the
+ * runtime, never assumed from the core count.  No-ops (1 thread) in the strict build. */
+#ifdef _OPENMP
+#include <omp.h>
+void oracle_set_threads(int n) { if (n > 0) omp_set_num_threads(n); }
+int oracle_max_threads(void) { return omp_get_max_threads(); }
+#else
+void oracle_set_threads(int n) { (void)n; }
+int oracle_max_threads(void) { return 1; }
+#endif
+
+/* Number of voxels of the slab that reach the truncation compare of src/tsdf.cu:49 with
+ * diff == -trunc EXACTLY.  The first-party kernel skips them (`<=`), the plugin semantics keeps
+ * them (`<`): on an input where this count is 0 the two compares cannot differ, so SEM_FUSIONPY
+ * with colour off, obs_weight = 1 and max_depth = 6 must equal the reference's own lines
+ * (oracle/_ref) after the [x][y][z] -> [z][y][x] transpose.  Same operation sequence as
+ * update_voxel up to :48; touches no volume array. */
+int64_t oracle_count_trunc_ties(const oracle_params* p, const float* c, const float* depth) {
+  const int W = p->im_w, H = p->im_h;
+  const float vs = p->voxel_size, trunc = p->trunc_margin;
+  const float* K = p->K;
+  int64_t ties = 0;
+#pragma omp parallel for collapse(2) schedule(static) reduction(+ : ties)
+  for (int z = p->z_begin; z < p->z_end; ++z)
+    for (int y = 0; y < p->dim_y; ++y)
+      for (int x = 0; x < p->dim_x; ++x) {
+        float bx = p->origin[0] + (float)x * vs;
+        float by = p->origin[1] + (float)y * vs;
+        float bz = p->origin[2] + (float)z * vs;
+        float t0 = bx - c[3], t1 = by - c[7], t2 = bz - c[11];
+        float cx_ = c[0] * t0 + c[4] * t1; cx_ = cx_ + c[8] * t2;
+        float cy_ = c[1] * t0 + c[5] * t1; cy_ = cy_ + c[9] * t2;
+        float cz_ = c[2] * t0 + c[6] * t1; cz_ = cz_ + c[10] * t2;
+        if (cz_ <= 0) continue;
+        int okx, oky;
+        int px = round_pix(K[0] * (cx_ / cz_) + K[2], W, &okx);
+        int py = round_pix(K[4] * (cy_ / cz_) + K[5], H, &oky);
+        if (!okx || !oky) continue;
+        float d = depth[(int64_t)py * W + px];
+        if (d <= 0 || d > p->max_depth) continue;
+        float diff = d - cz_;
+        if (diff == -trunc) ++ties;
+      }
+  return ties;
 }
 
 /* The same frame into the voxels [first, first + n) of the slab's linear storage order only

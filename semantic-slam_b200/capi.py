@@ -108,6 +108,7 @@ SIGNATURES = {
     "tsdf_set_variant": (_I, [_VP, _I]),
     "tsdf_timer_start": (_I, [_VP]),
     "tsdf_timer_stop": (_I, [_VP, C.POINTER(_F)]),
+    "tsdf_launch_count": (_I, [C.POINTER(_I64)]),
     "tsdf_kernel_timing": (_I, [_VP, _I]),
     "tsdf_kernel_timing_read": (_I, [_VP, C.POINTER(C.c_double), C.POINTER(_I64), _I]),
     "tsdf_selftest_exactmath": (_I, [_I, _I64, C.c_uint64, C.POINTER(_I64)]),

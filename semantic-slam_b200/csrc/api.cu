@@ -20,6 +20,12 @@ void tsdf_set_error(const char* fmt, ...) {
   va_end(ap);
 }
 extern "C" const char* tsdf_last_error(void) { return g_err; }
+std::atomic<long long> g_tsdf_launches{0};
+extern "C" int tsdf_launch_count(int64_t* n) {
+  REQUIRE(n, "null argument");
+  *n = (int64_t)g_tsdf_launches.load(std::memory_order_relaxed);
+  return TSDF_OK;
+}
 extern "C" int tsdf_version(void) { return TSDF_B200_VERSION; }
 
 extern "C" int tsdf_device_count(int* n) {
@@ -372,6 +378,16 @@ bool account_weights(tsdf_vol* v, const FrameP* fp, int nf) {
   return v->intw && v->w_bound <= 4094;
 }
 
+// rcp_rn / div_rn of the hot loop are exact for operands in [2^-60, 2^60]; the weights this bound
+// admits stay far inside it.  Shared by every integrate entry point (single, multi, bcast, batch).
+int check_obs_weight(float obs_weight) {
+  if (!(obs_weight >= 1e-6f && obs_weight <= 1e6f)) {   // also rejects NaN
+    tsdf_set_error("obs_weight must be in [1e-6, 1e6] (got %g)", (double)obs_weight);
+    return TSDF_E_INVALID;
+  }
+  return TSDF_OK;
+}
+
 // Launches the integrate kernel for nf prepared frames and records stats/events.
 static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
   if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
@@ -417,7 +433,8 @@ extern "C" int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int dept
     const float* k = K ? K : v->cfg.K;
     REQUIRE(k[0] != 0.0f && k[4] != 0.0f, "range formats need non-zero fx, fy");
   }
-  REQUIRE(obs_weight >= 1e-6f && obs_weight <= 1e6f, "obs_weight must be in [1e-6, 1e6]");
+  int rcw = check_obs_weight(obs_weight);
+  if (rcw) return rcw;
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   FrameSlot* s = nullptr;
@@ -446,6 +463,8 @@ extern "C" int tsdf_integrate(tsdf_vol* v, const float* depth, const uint8_t* rg
 extern "C" int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth, const uint8_t* rgb,
                                           const float* K, const float* T_wc, float obs_weight) {
   REQUIRE(v && depth && T_wc && k >= 1, "null argument or k < 1");
+  int rcw = check_obs_weight(obs_weight);
+  if (rcw) return rcw;
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   const size_t px = frame_pixels(v->cfg);

@@ -31,6 +31,7 @@ __global__ void k_expand_masks(const uint8_t* __restrict__ crops, const MaskBox*
 
 struct tsdf_batch {
   int n = 0;
+  std::vector<char> seen;        // scratch of the duplicate-id check
   std::vector<tsdf_vol*> vols;   // per-instance state (arrays, config, base pose); own streams unused
   tsdf_vol* frame_owner = nullptr;  // vols[0]: its slots/streams carry the shared frame
   BatchDesc* d_descs = nullptr;
@@ -83,8 +84,12 @@ extern "C" int tsdf_batch_create(const tsdf_config* cfgs, int n, tsdf_batch** ou
     tsdf_vol* v = nullptr;
     int rc = tsdf_create(&cfgs[i], &v);
     if (rc) { tsdf_batch_destroy(b); return rc; }
-    REQUIRE(v->dzl == v->cfg.dim_z, "batched instances must be whole grids");
-    b->vols.push_back(v);
+    b->vols.push_back(v);   // owned by the batch from here on: tsdf_batch_destroy frees it
+    if (v->dzl != v->cfg.dim_z) {
+      tsdf_batch_destroy(b);
+      tsdf_set_error("tsdf_batch_create: batched instances must be whole grids");
+      return TSDF_E_INVALID;
+    }
   }
   b->frame_owner = b->vols[0];
   DeviceGuard g(cfgs[0].device);
@@ -115,6 +120,16 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
                            int n_active, const uint8_t* masks, const int32_t* boxes, const uint8_t* crops,
                            const float* K, const float* T_wc, float obs_weight) {
   REQUIRE(b && depth && T_wc && active && n_active >= 1 && n_active <= b->n, "bad argument");
+  int rcw = check_obs_weight(obs_weight);
+  if (rcw) return rcw;
+  // every id in range and at most once: two blockIdx.z slices on one instance would race on its
+  // voxels (and count its weights twice)
+  b->seen.assign((size_t)b->n, 0);
+  for (int i = 0; i < n_active; ++i) {
+    REQUIRE(active[i] >= 0 && active[i] < b->n, "instance id out of range");
+    REQUIRE(!b->seen[(size_t)active[i]], "duplicate instance id in the active list");
+    b->seen[(size_t)active[i]] = 1;
+  }
   tsdf_vol* fo = b->frame_owner;
   DeviceGuard g(fo->cfg.device);
   const size_t px = frame_pixels(fo->cfg);
@@ -153,7 +168,7 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
     }
     CU_CHECK(cudaMemcpyAsync(b->d_boxes, b->h_boxes, sizeof(MaskBox) * (size_t)n_active, cudaMemcpyHostToDevice, fo->s_copy));
     k_expand_masks<<<dim3(32, n_active), 256, 0, fo->s_copy>>>(b->d_crops, b->d_boxes, H, W, b->d_masks);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
     d_masks = b->d_masks;
   } else if (masks) {
     cudaPointerAttributes a;
@@ -175,7 +190,6 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
   bool vec4 = true;
   bool wmode = true;
   for (int i = 0; i < n_active; ++i) {
-    REQUIRE(active[i] >= 0 && active[i] < b->n, "instance id out of range");
     tsdf_vol* v = b->vols[active[i]];
     ++v->epoch;
     const tsdf_config& c = v->cfg;

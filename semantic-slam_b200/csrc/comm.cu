@@ -299,7 +299,7 @@ static int p2p_setup(tsdf_vol* v, tsdf_comm* c, int root) {
 static int set_done_flag(void* arg, cudaStream_t st) {   // after_prep hook of a non-root rank
   tsdf_comm* c = static_cast<tsdf_comm*>(arg);
   k_set_flag<<<1, 1, 0, st>>>(c->peer_flags + 8 + c->rank, (unsigned)c->bseq);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
@@ -330,17 +330,17 @@ extern "C" int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, c
     if (is_root) {
       // slot k last held frame seq-3: wait until every peer has consumed it, then overwrite
       k_wait_all<<<1, 32, 0, v->s_copy>>>(c->d_flags + 8, c->nranks, root, seq - 3, c->hd_err, g_wait_timeout_ns);
-      CU_CHECK(cudaGetLastError());
+      CU_LAUNCHED();
       rc = bcast_stage(v, true, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, true);
       if (rc) return rc;
       k_set_flag<<<1, 1, 0, v->s_copy>>>(c->d_flags, (unsigned)seq);   // ready: frame seq is in slot k
-      CU_CHECK(cudaGetLastError());
+      CU_LAUNCHED();
       return bcast_finish(v, slot, color, K, T_wc, obs_weight, nullptr, nullptr, nullptr);
     }
     rc = bcast_stage(v, false, nullptr, nullptr, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, false);
     if (rc) return rc;
     k_wait_flag<<<1, 1, 0, v->s_copy>>>(c->peer_flags, seq, c->hd_err, g_wait_timeout_ns);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
     return bcast_finish(v, slot, color, K, T_wc, obs_weight, c->peer_raw[k], set_done_flag, c);
   }
   rc = bcast_stage(v, is_root, depth, rgb, color, &slot, &d_depth, &d_rgb, &s_depth, &s_rgb, false);

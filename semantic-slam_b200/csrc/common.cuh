@@ -6,6 +6,7 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
 #include <string>
 #include <vector>
 
@@ -20,6 +21,14 @@ void tsdf_set_error(const char* fmt, ...);  // thread-local, printf style
       tsdf_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
       return e__ == cudaErrorMemoryAllocation ? TSDF_E_NOMEM : TSDF_E_CUDA;               \
     }                                                                                     \
+  } while (0)
+// every kernel launch site ends with this: counts the launch (tsdf_launch_count, the bench's
+// `gpu_launches`) and picks up a launch-configuration error
+extern std::atomic<long long> g_tsdf_launches;
+#define CU_LAUNCHED()                                           \
+  do {                                                          \
+    g_tsdf_launches.fetch_add(1, std::memory_order_relaxed);    \
+    CU_CHECK(cudaGetLastError());                               \
   } while (0)
 #define REQUIRE(cond, msg)                                  \
   do {                                                      \
@@ -200,6 +209,7 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
                 int32_t* d_faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
 
 // api.cpp helpers used elsewhere
+int check_obs_weight(float obs_weight);  // one validation for every integrate entry point
 int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);
 int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
                       const void* d_frame, FrameP* out);

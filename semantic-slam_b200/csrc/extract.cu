@@ -267,9 +267,9 @@ int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, int64_t* d_tot
   p.m = m;
   const dim3 grid((unsigned)((m + kScanTile - 1) / kScanTile), d_cnt_b ? 2 : 1);
   k_scan_local<<<grid, kScanBlock, 0, st>>>(p);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   k_scan_carry<<<grid, kScanBlock, 0, st>>>(p);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
@@ -310,7 +310,7 @@ int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_t
     v->mark_valid = false;
     k_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(v->d_tsdf, v->d_weight, n, predicate, tsdf_thresh,
                                                    weight_thresh, d_bal, d_cnt);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
     if ((rc = launch_scan(d_cnt, n_tiles, d_off, d_tot, st))) return rc;
     CU_CHECK(cudaMemcpyAsync(&total, d_off + n_tiles, 8, cudaMemcpyDeviceToHost, st));
     CU_CHECK(cudaStreamSynchronize(st));
@@ -331,7 +331,7 @@ int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_t
   p.ox = v->cfg.origin[0]; p.oy = v->cfg.origin[1]; p.oz = v->cfg.origin[2]; p.vs = v->cfg.voxel_size;
   p.color = v->d_color;
   k_emit<<<(unsigned)n_tiles, kThreads, 0, st>>>(d_bal, d_off, p, d_xyz, d_rgb, d_idx);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   CU_CHECK(cudaStreamSynchronize(st));
   return TSDF_OK;
 }

@@ -135,14 +135,14 @@ int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int
   CU_CHECK(cudaMemsetAsync(d_dmax, 0, frame_tail_bytes(H, W), st));
   k_frame_prep<<<(n + 255) / 256, 256, 0, st>>>(d_depth, depth_fmt, depth_scale, sub_c, sub_r, d_rgb,
                                                 d_mask, H, W, max_depth, with_color, k4, d_frame, d_dmax);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
 int launch_fill(float* p, float val, int64_t n, cudaStream_t st) {
   if (n <= 0) return TSDF_OK;
   k_fill<<<148 * 8, 256, 0, st>>>(p, val, n);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
@@ -151,6 +151,6 @@ int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, i
   const float init[3] = {1000.0f, 1000.0f, 1000.0f};
   CU_CHECK(cudaMemcpyAsync(d_out3, init, sizeof(init), cudaMemcpyHostToDevice, st));
   k_instance_origin<<<148, 256, 0, st>>>(d_depth, d_mask, H, W, cx, cy, 1.0f / fx, 1.0f / fy, d_out3);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }

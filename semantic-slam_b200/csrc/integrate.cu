@@ -514,7 +514,9 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       }
     }
   }
-  if (f0 >= g.n_fast) return;  // (after the ballots: they need the whole warp)
+  // A thread whose run lies beyond the row (ragged fast axis) does no row work but stays: the
+  // closing warp reduction of n_written names every lane in its mask.
+  const bool live = f0 < g.n_fast;
 
   // per-run terms: the products of the fast-axis coordinate (registers, frame 0 only when
   // several frames are fused: the others are recomputed per row to bound register use)
@@ -533,7 +535,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   // weight).  A row is prefetched when the row before it was updated (coherent frames), and
   // the first row of a block unless it is culled.
   bool any_prev = true;
-  for (int lr = tr; lr < rows_per_block; lr += rp, rowmask >>= 1) {
+  for (int lr = tr; live && lr < rows_per_block; lr += rp, rowmask >>= 1) {
     const int r = row0 + lr;
     if (r >= n_rows) break;
     if constexpr (CULL != 0) {
@@ -779,7 +781,7 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
   else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
@@ -846,7 +848,7 @@ static bool slab_inside_every_frustum(const GridP& g, const FrameP* fr, int nf) 
 
 int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st) {
   k_publish<<<1, 1, 0, st>>>(v->d_written, v->hd_written, accumulate ? 1 : 0);
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }
 
@@ -908,6 +910,6 @@ int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast,
     else       { if (vec4) LB(false, false, true, 4, 0); else LB(false, false, true, 1, 0); }
   }
 #undef LB
-  CU_CHECK(cudaGetLastError());
+  CU_LAUNCHED();
   return TSDF_OK;
 }

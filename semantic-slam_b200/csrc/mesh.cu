@@ -671,7 +671,7 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
       k_mc_mark4<false><<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
     else
       k_mc_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_vcnt, d_tcnt);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
     CU_CHECK(cudaMemsetAsync(d_nlist, 0, 8, st));
     int rc = launch_scan(d_vcnt, n_tiles, d_voff, d_vtot, st, d_tcnt, d_toff, d_ttot,  // both arrays per launch
                          d_vlist, d_flist, d_nlist);
@@ -704,11 +704,11 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
   }
   if (nv && (d_verts || d_norms || d_cols)) {
     k_mc_verts<<<v->mesh_vtiles, kThreads, 0, st>>>(p, d_recs, d_voff, d_vlist, d_verts, d_norms, d_cols);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
   }
   if (nf && d_faces) {
     k_mc_faces<<<v->mesh_ftiles, kThreads, 0, st>>>(p, d_recs, d_cases, d_voff, d_toff, d_flist, d_faces);
-    CU_CHECK(cudaGetLastError());
+    CU_LAUNCHED();
   }
   CU_CHECK(cudaStreamSynchronize(st));
   return TSDF_OK;

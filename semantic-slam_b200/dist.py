@@ -87,6 +87,9 @@ class ShardedVolume:
         check(self.lib.tsdf_comm_peer_pull(self.comm, C.byref(a)))
         return bool(a.value)
 
+    def distribution(self):
+        return ("peer-pull fused into the prep kernel (NVLink, cudaIpc)" if self.peer_pull() else "ncclBroadcast")
+
     def sync(self):
         self.vol.sync()
         self._keep.clear()

@@ -131,9 +131,11 @@ def render(scene, K, hw, T_wc, rng, noise_sigma=0.0, hole_frac=0.0, max_range=np
 # S-full: every voxel of the grid is inside the frustum and in front of the wall, so
 # N_written == N_vox each frame (the roofline case).
 # --------------------------------------------------------------------------------------
-def s_full(dims, voxel_size, n_frames=4, seed=SEED_BASE, K=TUM3_K, hw=TUM3_HW, jitter=True):
+def s_full(dims, voxel_size, n_frames=4, seed=SEED_BASE, K=TUM3_K, hw=TUM3_HW, jitter=True, sphere=False):
     """Returns (origin[3], frames) with frames = list of (depth, rgb, T_wc).
-    The volume is an axis-aligned box in the world frame, camera looks along +z."""
+    The volume is an axis-aligned box in the world frame, camera looks along +z.
+    sphere=True puts a sphere of radius 0.15 * min(L) (0.31 m at the 2.048 m bench volume) at the
+    volume centre: a surface for the readback leg; its interior and shadow are not written."""
     rng = np.random.default_rng(seed)
     Kf = np.asarray(K, float)
     H, W = hw
@@ -145,6 +147,8 @@ def s_full(dims, voxel_size, n_frames=4, seed=SEED_BASE, K=TUM3_K, hw=TUM3_HW, j
     origin = np.array([-L[0] / 2, -L[1] / 2, z_near], np.float32)
     wall_z = z_near + L[2] + 0.25
     scene = Scene().plane((0, 0, 1), wall_z)
+    if sphere:
+        scene.sphere((0.0, 0.0, z_near + L[2] / 2), 0.15 * L.min())
     frames = []
     for i in range(n_frames):
         if jitter and i > 0:
@@ -229,6 +233,31 @@ def s_kitti(n_frames=4, seed=SEED_BASE + 2, voxel_size=0.1, dims=(1024, 256, 102
             disp = np.round(KITTI_BF / depth * 16.0) / 16.0
             dq = np.where((depth > 0) & (disp > 0), KITTI_BF / disp, 0.0)
         frames.append((np.ascontiguousarray(dq, np.float32), rgb, T))
+    return origin, frames
+
+
+# --------------------------------------------------------------------------------------
+# S-corridor: a long volume seen end-on (floor, side walls, an end wall and boxes all the way
+# along z), so that EVERY z-slab of a sharded grid holds written voxels — the multi-GPU parity
+# worker's scene (a room in the middle of a long grid leaves the outer slabs empty).
+# --------------------------------------------------------------------------------------
+def s_corridor(dims, voxel_size, n_frames=4, seed=SEED_BASE + 3, K=TUM3_K, hw=TUM3_HW):
+    rng = np.random.default_rng(seed)
+    L = np.array(dims, float) * voxel_size
+    origin = np.array([-L[0] / 2, -L[1] / 2, 0.5], np.float32)
+    scene = Scene().plane((0, 1, 0), 0.35 * L[1]).plane((1, 0, 0), 0.47 * L[0]).plane((1, 0, 0), -0.47 * L[0])
+    scene.plane((0, 0, 1), 0.5 + 0.985 * L[2])
+    n_box = max(6, int(L[2] / 1.2))
+    for k in range(n_box):
+        z = 0.5 + (k + rng.uniform(0.1, 0.6)) * L[2] / n_box
+        x = rng.uniform(-0.4, 0.2) * L[0]
+        w, h, d = rng.uniform(0.1, 0.3) * L[0], rng.uniform(0.15, 0.5) * L[1], rng.uniform(0.2, 0.6)
+        scene.box((x, 0.35 * L[1] - h, z), (x + w, 0.35 * L[1], z + d))
+    frames = []
+    for i in range(n_frames):
+        T = pose(rot_xyz(0.01 * i, 0.015 * (i - 1), 0.005 * i), (0.03 * i, -0.02 * i, -1.0 + 0.35 * i))
+        depth, rgb = render(scene, K, hw, T, rng, noise_sigma=0.004, hole_frac=0.03)
+        frames.append((depth, rgb, T))
     return origin, frames
 
 

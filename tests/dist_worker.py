@@ -23,10 +23,12 @@ def main():
     dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
     o = Oracle()
     synth = pkg.synth
-    dims, vs = (48, 40, 72), 0.04
-    origin, frames = synth.s_real(dims, vs, n_frames=4, seed=77)   # same seed => same data on all ranks
+    # >= 64 slices per rank (a C3 slab is 128): the slab kernel runs whole blocks, not an 8-slice sliver
+    dims, vs = (56, 40, max(72, 64 * world)), 0.04
+    origin, frames = synth.s_corridor(dims, vs, n_frames=4, seed=77)   # same seed => same data on all ranks
+    MD = 40.0   # the corridor is up to 20 m long: class-TSDF's default max_depth of 6 m would cut it
     for sem, color in ((SEM_FUSIONPY, True), (SEM_TSDFCU, False)):
-        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color)
+        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=MD)
         uid = pkg.dist.exchange_uid(pkg.dist.make_nccl_uid, rank, dist, dev)
         sv = pkg.dist.ShardedVolume(cfg, rank, world, local, uid)
         zr = (sv.vol.cfg.z_begin, sv.vol.cfg.z_end)
@@ -45,6 +47,7 @@ def main():
         t, w, c = o.new_volume(p, color)
         for d, rgb, T in frames:
             o.integrate(p, T.reshape(16), d, o.pack_color(rgb) if color else None, 1.0, t, w, c)
+        assert w.max() >= 2, f"rank {rank}: slab {zr} saw nothing (scene does not reach it)"
         assert np.array_equal(gw, w), f"rank {rank}: weights differ"
         assert np.array_equal(gt.view(np.uint32), t.view(np.uint32)), f"rank {rank}: tsdf differs"
         if color:

@@ -187,3 +187,79 @@ def test_oracle_range_equals_whole(oracle, synth):
             s = slice(first, first + cnt)
             assert 0 < part < total and part == int(w[s].sum())
             assert np.array_equal(bits(t[s]), bits(t2)) and np.array_equal(w[s], w2) and np.array_equal(c[s], c2)
+
+
+# ---- SEM_FUSIONPY geometry / weight / tsdf half pinned against the reference's own lines ---------
+# With colour off, obs_weight = 1 and max_depth = 6 the plugin semantics differs from
+# src/tsdf.cu:15-60 only in the storage order ([x][y][z] vs [z][y][x]) and in the truncation
+# compare (`<` vs `<=`, src/tsdf.cu:49), and the compare matters only for a voxel whose
+# diff == -trunc exactly.  On inputs with zero such ties (asserted) the two must agree bit for bit
+# after a transpose.  Only the colour blend and the mesh stay unpinned (third-party, un-vendored).
+def fusionpy_geometry(oracle, dims, vs, origin, hw, K, frames_c2b, trunc=None):
+    trunc = np.float32(vs) * np.float32(5) if trunc is None else trunc
+    p = oracle.params(dims, vs, trunc, origin, hw, K, 6.0, SEM_FUSIONPY)
+    t, w, _ = oracle.new_volume(p)
+    ties = 0
+    for d, c2b in frames_c2b:
+        ties += oracle.count_trunc_ties(p, c2b, d)
+        oracle.integrate(p, c2b, d, None, 1.0, t, w, None)
+    to_zyx = lambda a: np.ascontiguousarray(a.reshape(dims).transpose(2, 1, 0)).reshape(-1)  # noqa: E731
+    return to_zyx(t), to_zyx(w), ties
+
+
+def test_fusionpy_geometry_matches_reference_golden(oracle, golden_cu):
+    g = golden_cu
+    dims, vs, hw = tuple(int(x) for x in g["dims"]), float(g["vs"]), tuple(int(x) for x in g["hw"])
+    t, w, ties = fusionpy_geometry(oracle, dims, vs, g["origin"], hw, g["K"], list(zip(g["depth"], g["cam2base"])))
+    assert ties == 0, "golden input has diff == -trunc ties: `<` vs `<=` would matter"
+    assert w.max() >= 2 and np.array_equal(w, g["weight"]) and np.array_equal(bits(t), bits(g["tsdf"]))
+
+
+@pytest.mark.skipif(not ref_available(), reason="oracle/_ref not built (needs /root/reference at build time)")
+def test_fusionpy_geometry_vs_reference_lift_random(oracle, synth):
+    r = RefLift()
+    rng = np.random.default_rng(23)
+    for k, (dims, vs) in enumerate([((50, 44, 38), 0.03), ((36, 52, 64), 0.025), ((64, 64, 64), 0.02)]):
+        origin, frames = synth.s_real(dims, vs, n_frames=4, seed=40 + k)
+        base = synth.pose(synth.rot_xyz(*rng.uniform(-0.05, 0.05, 3)), rng.uniform(-0.1, 0.1, 3))
+        fc = [(d, oracle.compose(base, T)) for d, _, T in frames]
+        t, w, ties = fusionpy_geometry(oracle, dims, vs, origin, synth.TUM3_HW, synth.TUM3_K, fc)
+        t2 = np.ones(int(np.prod(dims)), np.float32)
+        w2 = np.zeros_like(t2)
+        for d, c2b in fc:
+            r.integrate(synth.TUM3_K, c2b, d, dims, origin, vs, np.float32(vs) * np.float32(5), t2, w2)
+        assert ties == 0
+        assert w2.max() >= 2 and np.array_equal(w, w2) and np.array_equal(bits(t), bits(t2))
+
+
+def test_trunc_tie_counter_sees_a_planted_tie(oracle, synth):
+    """The tie counter itself: a depth image made so that one voxel's diff is exactly -trunc."""
+    dims, vs = (8, 8, 8), np.float32(0.125)
+    trunc = np.float32(0.5)
+    K = np.array([100, 0, 32, 0, 100, 32, 0, 0, 1], np.float32)
+    T = np.eye(4, dtype=np.float32)
+    origin = np.array([-0.5, -0.5, 1.0], np.float32)   # voxel (4,4,k) sits on the optical axis at z = 1 + k/8
+    depth = np.full((64, 64), 1.0, np.float32)          # diff = 1 - (1 + k/8) == -0.5 exactly at k = 4
+    for sem in (SEM_TSDFCU, SEM_FUSIONPY):
+        p = oracle.params(dims, vs, trunc, origin, (64, 64), K, 6.0, sem)
+        assert oracle.count_trunc_ties(p, T.reshape(16), depth) > 0
+        t, w, _ = oracle.new_volume(p)
+        oracle.integrate(p, T.reshape(16), depth, None, 1.0, t, w, None)
+        idx = 4 * 64 + 4 * 8 + 4   # (4,4,4) in either order
+        assert w[idx] == (0.0 if sem == SEM_TSDFCU else 1.0)   # `<=` skips the tie, `<` keeps it
+
+
+def test_openmp_build_equals_strict_build(oracle, synth):
+    """liboracle_omp.so (-O3 -march=x86-64-v3 -fopenmp, still -ffp-contract=off: the checker of the
+    full-size GPU tests and the cpu_baseline port) computes the same bits as the strict build."""
+    omp = Oracle(omp=True)
+    dims, vs = (72, 56, 64), 0.03
+    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=17)
+    for sem, color in ((SEM_TSDFCU, False), (SEM_FUSIONPY, True)):
+        p = oracle.params(dims, vs, 5 * vs, origin, synth.TUM3_HW, synth.TUM3_K, 6.0, sem)
+        a, b = oracle.new_volume(p, color), omp.new_volume(p, color)
+        for d, rgb, T in frames:
+            pc = oracle.pack_color(rgb) if color else None
+            assert oracle.integrate(p, T.reshape(16), d, pc, 0.5, *a) == omp.integrate(p, T.reshape(16), d, pc, 0.5, *b)
+        assert np.array_equal(bits(a[0]), bits(b[0])) and np.array_equal(a[1], b[1])
+        assert not color or np.array_equal(a[2], b[2])
