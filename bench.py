@@ -35,6 +35,10 @@ METRIC = "tsdf_voxel_updates_per_sec"
 UNIT = "Gvox/s"
 DIM = int(os.environ.get("TSDF_BENCH_DIM", "1024"))
 VS = float(os.environ.get("TSDF_BENCH_VS", "0.002"))
+# development knobs (never set by the driver): a non-cubic grid DIM x DIM x DZ gives N ranks the slab
+# an 8-rank run of the headline grid has (e.g. DZ=256 on 2 GPUs); TRACE dumps per-frame timelines
+DZ = int(os.environ.get("TSDF_BENCH_DZ", str(DIM)))
+TRACE = os.environ.get("TSDF_BENCH_TRACE")
 N_DISTINCT = 4
 SPHERE = os.environ.get("TSDF_BENCH_SPHERE", "1") != "0"
 WINDOWS = max(1, int(os.environ.get("TSDF_BENCH_WINDOWS", "5")))
@@ -266,12 +270,12 @@ def bench_frames(synth, dims):
 
 def workload_config(n_gpus):
     """Identical in both arms (the driver compares them)."""
-    scene = ("S-full + a 0.31 m sphere inside the volume (every voxel in view and in front of the wall; all "
-             "but the sphere's interior/shadow, ~5 %, written every frame)") if SPHERE else \
+    scene = ("S-full + a 0.31 m sphere against the volume's far face (every voxel in view and in front of the wall; all "
+             "but the sphere's interior/shadow, ~1.5 %, written every frame)") if SPHERE else \
         "S-full (every voxel written every frame)"
     return {"workload": f"C4: {DIM}^3 fp32 tsdf+weight+packed-RGB volume, {VS*1000:g} mm voxels, 640x480 RGB-D "
                         f"frames (TUM3 intrinsics), scene {scene}, FUSIONPY semantics (colour + obs_weight)",
-            "grid": [DIM, DIM, DIM], "frame": [480, 640], "sharding": f"{n_gpus} z-slab(s), one process per GPU",
+            "grid": [DIM, DIM, DZ], "frame": [480, 640], "sharding": f"{n_gpus} z-slab(s), one process per GPU",
             "l2": "inputs larger than L2 (volume slab >= 1.6 GB per GPU vs 126 MB L2)",
             "distinct_frames": N_DISTINCT,
             "arms": "b200 arm: depth+weight+colour, 24 B per written voxel; --impl reference arm: the reference's "
@@ -327,7 +331,7 @@ def run_b200(args, rank, world, local_rank):
         torch.cuda.set_device(local_rank)
         tdev = torch.device("cuda", local_rank)
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=tdev)
-    dims = (DIM, DIM, DIM)
+    dims = (DIM, DIM, DZ)
     origin, frames = bench_frames(synth, dims)  # seeded: identical on every rank
     H, W = frames[0][0].shape
     cfg = pkg.make_config(dims, VS, origin, semantics=pkg.SEM_FUSIONPY, with_color=True, device=local_rank)
@@ -338,8 +342,9 @@ def run_b200(args, rank, world, local_rank):
     else:
         sv, vol = None, pkg.Volume(cfg)
     df = DeviceFrames(pkg, local_rank, frames) if rank == 0 else None
-    n_total = DIM ** 3
+    n_total = DIM * DIM * DZ
     lib = pkg.load()
+    pool = pkg.PinnedPool()   # page-locked output arrays of the readback leg (tsdf_host_alloc)
 
     def launches():
         import ctypes as C
@@ -382,9 +387,9 @@ def run_b200(args, rank, world, local_rank):
         barrier()
         t0 = time.perf_counter()
         if sv is not None:
-            _, _, _, n_pts = sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5)
+            _, _, _, n_pts = sv.gather_points(pkg.PRED_ABS_LT, 0.999, 0.5, pool=pool)
         else:
-            n_pts = len(vol.extract_points(pkg.PRED_ABS_LT, 0.999, 0.5)[2])
+            n_pts = len(vol.extract_points(pkg.PRED_ABS_LT, 0.999, 0.5, pool=pool)[2])
         ms = (time.perf_counter() - t0) * 1e3
         return reduce_ranks(ms, "MAX"), n_pts
 
@@ -427,6 +432,20 @@ def run_b200(args, rank, world, local_rank):
     for i in range(min(args.warmup, 3)):
         step(i, True)
     wins_e, ksum_e, kn_e, _, clocks_e, launched_e = timed(True, args.steps)
+    if TRACE:   # one more e2e window with the per-frame timeline on, dumped per rank
+        barrier()
+        vol.trace_enable(True)
+        vol.timer_start()
+        for i in range(args.steps):
+            step(i, True)
+        tr_ms = vol.timer_stop()
+        tr = vol.trace_read()
+        vol.trace_enable(False)
+        os.makedirs(os.path.join(ROOT, "gpurun_out", TRACE), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", TRACE, f"trace_n{world}_rank{rank}.json"), "w") as f:
+            json.dump({"n_gpus": world, "rank": rank, "steps": args.steps, "window_ms": tr_ms,
+                       "columns": ["copy_begin", "frame_ready", "kernel_begin", "kernel_end"],
+                       "ms": tr.tolist()}, f)
     ms_e = float(np.median(wins_e))
     e2e = args.steps * n_total / (ms_e * 1e-3) / 1e9
     written_total = reduce_ranks(float(written), "SUM")
@@ -455,7 +474,8 @@ def run_b200(args, rank, world, local_rank):
                                     "integrate + the step's 8 B N_written written to host memory",
                         "readback": {"what": "after the timed steps: surface extraction on every rank (|tsdf| < 0.999, "
                                              "weight > 0.5), records gathered to rank 0 and merged to reference order, "
-                                             "xyz f32x3 + rgb u8x3 + idx i64 into host arrays; host clock, max over ranks",
+                                             "xyz f32x3 + rgb u8x3 + idx i64 into page-locked host arrays (tsdf_host_alloc); host clock around the "
+                                             "blocking call (mark sweep + scan + emit + gather + merge + D2H), max over ranks",
                                      "ms": rb_ms, "points": n_pts, "bytes_to_host": rb_bytes,
                                      "GBps_to_host": rb_bytes / (rb_ms * 1e-3) / 1e9 if rb_ms else None},
                         "value_with_readback": args.steps * n_total / ((ms_e + rb_ms) * 1e-3) / 1e9,
@@ -549,7 +569,12 @@ def extras(pkg, line, frames, origin, vol=None):
             ext_ms = (time.perf_counter() - t0) * 1e3
             t0 = time.perf_counter()
             pts = v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5)   # reuses the mark pass above: emit + D2H only
-            ext_full_ms = (time.perf_counter() - t0) * 1e3
+            ext_full_ms = (time.perf_counter() - t0) * 1e3            # into fresh pageable numpy arrays
+            pool2 = pkg.PinnedPool()
+            v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5, pool=pool2)  # warm: allocates the page-locked outputs
+            t0 = time.perf_counter()
+            v2.extract_points(pkg.PRED_ABS_LT, 0.5, 1.5, pool=pool2)  # emit + D2H straight into pinned outputs
+            ext_pinned_ms = (time.perf_counter() - t0) * 1e3
             # mesh readback (plugin SaveMesh): the first count call also allocates the scratch, so the
             # sweep is timed on a second one after an epoch bump (re-upload of nothing = reset of the cache)
             mesh = {}
@@ -562,7 +587,12 @@ def extras(pkg, line, frames, origin, vol=None):
                 t0 = time.perf_counter()
                 v2.extract_mesh()                 # reuses the sweep: vertex + face kernels + D2H
                 mesh_emit_ms = (time.perf_counter() - t0) * 1e3
+                v2.extract_mesh(pool=pool2)
+                t0 = time.perf_counter()
+                v2.extract_mesh(pool=pool2)       # the same into page-locked outputs
+                mesh_emit_pinned_ms = (time.perf_counter() - t0) * 1e3
                 mesh = {"mesh_sweep_ms": mesh_sweep_ms, "mesh_emit_to_host_ms": mesh_emit_ms,
+                        "mesh_emit_to_pinned_host_ms": mesh_emit_pinned_ms,
                         "mesh_sweep_GBps": 5.5 * 512 ** 3 / (mesh_sweep_ms * 1e-3) / 1e9,
                         "mesh_vertices": mnv, "mesh_faces": mnf}
                 # reported CPU baseline of the same readback: the oracle's marching cubes (one host
@@ -589,6 +619,7 @@ def extras(pkg, line, frames, origin, vol=None):
                             "value": nfr * 512 ** 3 / (ms * 1e-3) / 1e9, "unit": UNIT, "frames_per_sec": nfr / (ms * 1e-3),
                             "kernel_ms": ksum / max(kn, 1), "coverage_last_frame": wr / 512 ** 3,
                             "extract_count_ms": ext_ms, "extract_emit_to_host_ms": ext_full_ms,
+                            "extract_emit_to_pinned_host_ms": ext_pinned_ms,
                             "extract_sweep_GBps": 8 * 512 ** 3 / (ext_ms * 1e-3) / 1e9, "surface_points": npts, **mesh}
     except Exception as e:
         line["extra_c2"] = {"error": str(e)}
@@ -609,6 +640,7 @@ def extras(pkg, line, frames, origin, vol=None):
                 ref.close()
                 cfg = pkg.make_config((dim,) * 3, vs_r, o_r, semantics=pkg.SEM_TSDFCU, with_color=False, max_depth=1e9)
                 with pkg.Volume(cfg) as vr:
+                    vr.set_variant(0)   # A/B tooling handle: bench_kernel re-launches on the prepared frame
                     vr.integrate(fr_r[0][0], None, fr_r[0][2])
                     vr.bench_kernel(3)
                     ms_own = min(vr.bench_kernel(5) for _ in range(3))

@@ -79,6 +79,7 @@ enum { TSDF_DEPTH_F32 = 0, TSDF_DEPTH_U16 = 1, TSDF_DEPTH_RANGE_F32 = 2, TSDF_DE
 typedef struct tsdf_vol tsdf_vol;     /* one volume (or one z-slab of it) on one GPU */
 typedef struct tsdf_comm tsdf_comm;   /* one NCCL rank                              */
 typedef struct tsdf_batch tsdf_batch; /* N per-instance volumes, one launch          */
+typedef struct tsdf_group tsdf_group; /* one volume as z-slabs over several GPUs, ONE process */
 
 typedef struct tsdf_config {
   int32_t dim_x, dim_y, dim_z; /* GLOBAL grid dims (include/tsdf.hpp:65-67: 200^3)   */
@@ -124,7 +125,11 @@ int tsdf_config_from_bounds(const double vol_bnds[6], double voxel_size, tsdf_co
 
 /* ---- lifecycle (K3, K4) -------------------------------------------------- */
 int tsdf_create(const tsdf_config* cfg, tsdf_vol** out);
-int tsdf_destroy(tsdf_vol* v);           /* frees everything the handle owns */
+/* Frees everything the handle owns.  A volume whose frame slots a tsdf_comm has exported to /
+ * mapped from the other ranks (after the first tsdf_integrate_bcast_async) must outlive that
+ * communicator: tsdf_destroy returns TSDF_E_INVALID and frees nothing until tsdf_comm_destroy
+ * has been called.                                                              */
+int tsdf_destroy(tsdf_vol* v);
 int tsdf_reset(tsdf_vol* v);             /* tsdf=1, weight=0, colour=0 (src/tsdf.cu:79-81) */
 int tsdf_get_config(const tsdf_vol* v, tsdf_config* cfg);
 
@@ -154,6 +159,11 @@ int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int depth_fmt, floa
  * own launch.  depth: k*H*W, rgb: k*H*W*3 or NULL, K: 9 or NULL, T_wc: k*16.   */
 int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth, const uint8_t* rgb,
                                const float* K, const float* T_wc, float obs_weight);
+/* Waits for everything enqueued on the handle.  On a volume attached to a tsdf_comm it also
+ * surfaces a failed frame distribution (a peer-pull wait that timed out because a rank is gone):
+ * TSDF_E_NCCL, and the frames behind the failure were NOT integrated on this rank (the kernel
+ * skips them; the volume holds exactly the frames before it).  tsdf_get_stats, tsdf_download*,
+ * tsdf_extract_* and tsdf_gather_* sync first and report the same way.            */
 int tsdf_sync(tsdf_vol* v);
 int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s); /* syncs the handle's stream */
 
@@ -277,7 +287,10 @@ int tsdf_integrate_bcast_async(tsdf_vol* v, tsdf_comm* c, int root, const float*
 /* *active = 1 when frames are distributed by peer-pull (every non-root rank's prep kernel reads
  * the root's raw frame slot through NVLink, cudaIpc-mapped; set up by the first
  * tsdf_integrate_bcast_async call), 0 when ncclBroadcast is used (fallback, or
- * TSDF_B200_BCAST=nccl in the environment).  Results are identical either way.           */
+ * TSDF_B200_BCAST=nccl in the environment).  Results are identical either way.  Once peer-pull is
+ * active the volume is ATTACHED to the communicator: destroy the communicator first (tsdf_destroy
+ * refuses until then).  Calls of this function and plain tsdf_integrate* calls may be interleaved
+ * on the handle (the distribution has its own frame ring, indexed by its own sequence number).  */
 int tsdf_comm_peer_pull(const tsdf_comm* c, int* active);
 /* Collective: every rank extracts its slab; the root receives all points,
  * merged to ascending GLOBAL reference index.  Non-root ranks pass NULL/0
@@ -287,8 +300,58 @@ int tsdf_gather_points(tsdf_vol* v, tsdf_comm* c, int root, int predicate, float
                        float weight_thresh, float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap,
                        int64_t* count);
 
-/* ---- pinned host memory helpers (frame upload path) ----------------------- */
-int tsdf_host_alloc(void** p, size_t bytes); /* cudaHostAlloc: uploads skip the staging copy */
+/* Collective mesh readback of a sharded volume (plugin SaveMesh on the multi-GPU configuration,
+ * src/TSDFfusion.py.in:48-53): cells across a slab face need both sides, so every rank sends its
+ * tsdf (and colour) slab to the root over NVLink, the root assembles a temporary WHOLE-grid volume
+ * on its device (12 B per voxel of the whole grid) and meshes it there — vertices, faces and
+ * their order are exactly those of tsdf_extract_mesh on a single-GPU volume.  The assembly is
+ * reused while no rank's slab changes (sizing call + real call move the volume once) and freed by
+ * tsdf_comm_destroy.  Arguments as tsdf_extract_mesh; non-root ranks pass NULL/0 and get 0 counts. */
+int tsdf_gather_mesh(tsdf_vol* v, tsdf_comm* c, int root, float* verts, float* norms, uint8_t* colors,
+                     int64_t vcap, int32_t* faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
+
+/* ---- multi-GPU in ONE process: a device list behind one handle --------------- */
+/* The reference is a single process (Engine::Run, src/Engine.cpp:105).  tsdf_group cuts the grid of
+ * `cfg` (whole-grid config; cfg->device is ignored) into n_devices z-slabs, slab i on devices[i]
+ * (tsdf_slab_range), and drives them from the calling thread: the frame is staged once on
+ * devices[0]; every other slab's prep kernel reads it in place over NVLink
+ * (cudaDeviceEnablePeerAccess; cudaMemcpyPeerAsync where two devices have no peer access), ordered by
+ * CUDA events — no NCCL, no second process.  Results are bit-identical to one whole-grid volume.
+ * A device may be listed more than once (several slabs on one GPU).               */
+int tsdf_group_create(const tsdf_config* cfg, const int32_t* devices, int n_devices, tsdf_group** out);
+int tsdf_group_destroy(tsdf_group* g);
+int tsdf_group_size(const tsdf_group* g, int* n_slabs);
+int tsdf_group_slab(tsdf_group* g, int i, tsdf_vol** slab);        /* borrowed: do not destroy */
+int tsdf_group_peer_access(const tsdf_group* g, int* n_direct);    /* slabs 1.. that read devices[0] in place */
+/* Arguments as tsdf_integrate / tsdf_integrate_async (host pointers pageable or pinned; device
+ * pointers must be accessible from devices[0]).                                  */
+int tsdf_group_integrate(tsdf_group* g, const float* depth, const uint8_t* rgb, const float* K,
+                         const float* T_wc, float obs_weight);
+int tsdf_group_integrate_async(tsdf_group* g, const float* depth, const uint8_t* rgb, const float* K,
+                               const float* T_wc, float obs_weight);
+int tsdf_group_sync(tsdf_group* g);
+int tsdf_group_reset(tsdf_group* g);
+int tsdf_group_get_stats(tsdf_group* g, tsdf_stats* s);            /* sums over the slabs (ms: max) */
+/* GLOBAL Dx*Dy*Dz host arrays in the semantics' reference order; any pointer may be NULL. */
+int tsdf_group_download(tsdf_group* g, float* tsdf, float* weight, float* color);
+/* As tsdf_extract_points on one whole-grid volume: ascending GLOBAL reference index (the slabs'
+ * runs are merged on devices[0]).                                                 */
+int tsdf_group_extract_points(tsdf_group* g, int predicate, float tsdf_thresh, float weight_thresh,
+                              float* xyz, uint8_t* rgb, int64_t* idx, int64_t cap, int64_t* count);
+/* As tsdf_extract_mesh on one whole-grid volume (assembled on devices[0], see tsdf_gather_mesh;
+ * kept until a slab changes or tsdf_group_release_scratch).                       */
+int tsdf_group_extract_mesh(tsdf_group* g, float* verts, float* norms, uint8_t* colors, int64_t vcap,
+                            int32_t* faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
+int tsdf_group_release_scratch(tsdf_group* g);
+int tsdf_group_save_ply(tsdf_group* g, const char* path, int predicate, float tsdf_thresh, float weight_thresh);
+int tsdf_group_save_bin(tsdf_group* g, const char* path);
+int tsdf_group_save_mesh_ply(tsdf_group* g, const char* path);
+
+/* ---- pinned host memory helpers (frame upload path, readback) -------------- */
+/* cudaHostAlloc: uploads from such memory skip the staging copy, and the readback calls
+ * (tsdf_extract_points / _mesh, tsdf_gather_*, tsdf_group_extract_*) copy straight into output
+ * arrays allocated with it (pageable outputs go through a pinned staging ring).   */
+int tsdf_host_alloc(void** p, size_t bytes);
 int tsdf_host_free(void* p);
 int tsdf_device_alloc(int device, void** p, size_t bytes);
 int tsdf_device_free(int device, void* p);
@@ -350,6 +413,13 @@ int tsdf_timer_stop(tsdf_vol* v, float* ms);
  * libtsdf_b200.so, all handles, all devices): the bench's `gpu_launches` is a difference of two
  * reads around its timed window.                                              */
 int tsdf_launch_count(int64_t* n);
+/* Per-frame timeline of a handle: when enabled every integrate call (single, distributed, group)
+ * records four CUDA events {copy stream: first operation of the frame enqueued, prepared frame
+ * ready; compute stream: integrate kernel begins, ends}.  tsdf_trace_read returns them as ms
+ * relative to the first event since enable (ms4: 4 floats per frame), the evidence behind the
+ * multi-GPU step analysis in DESIGN.md §5.                                        */
+int tsdf_trace_enable(tsdf_vol* v, int enable);
+int tsdf_trace_read(tsdf_vol* v, float* ms4, int cap_frames, int* n_frames);
 int tsdf_kernel_timing(tsdf_vol* v, int enable);
 int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset);
 

@@ -6,5 +6,5 @@ TSDF / TSDFfusion surface over that ABI.  Import with
 """
 from . import capi, synth, volume, dist  # noqa: F401
 from .capi import (SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO, PRED_ABS_LT, TsdfError, load)  # noqa: F401
-from .volume import (Volume, Batch, TSDF, TSDFVolume, make_config, config_from_bounds, default_config,
+from .volume import (Volume, Group, PinnedPool, Batch, TSDF, TSDFVolume, make_config, config_from_bounds, default_config,
                      slab_range, device_count, meshwrite)  # noqa: F401

@@ -92,6 +92,24 @@ SIGNATURES = {
     "tsdf_slab_range": (None, [_I, _I, _I, C.POINTER(_I), C.POINTER(_I)]),
     "tsdf_integrate_bcast_async": (_I, [_VP, _VP, _I, _VP, _VP, _VP, _VP, _F]),
     "tsdf_gather_points": (_I, [_VP, _VP, _I, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
+    "tsdf_gather_mesh": (_I, [_VP, _VP, _I, _VP, _VP, _VP, _I64, _VP, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
+    "tsdf_group_create": (_I, [C.POINTER(Config), C.POINTER(C.c_int32), _I, C.POINTER(_VP)]),
+    "tsdf_group_destroy": (_I, [_VP]),
+    "tsdf_group_size": (_I, [_VP, C.POINTER(_I)]),
+    "tsdf_group_slab": (_I, [_VP, _I, C.POINTER(_VP)]),
+    "tsdf_group_peer_access": (_I, [_VP, C.POINTER(_I)]),
+    "tsdf_group_integrate": (_I, [_VP, _VP, _VP, _VP, _VP, _F]),
+    "tsdf_group_integrate_async": (_I, [_VP, _VP, _VP, _VP, _VP, _F]),
+    "tsdf_group_sync": (_I, [_VP]),
+    "tsdf_group_reset": (_I, [_VP]),
+    "tsdf_group_get_stats": (_I, [_VP, C.POINTER(Stats)]),
+    "tsdf_group_download": (_I, [_VP, _VP, _VP, _VP]),
+    "tsdf_group_extract_points": (_I, [_VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
+    "tsdf_group_extract_mesh": (_I, [_VP, _VP, _VP, _VP, _I64, _VP, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
+    "tsdf_group_release_scratch": (_I, [_VP]),
+    "tsdf_group_save_ply": (_I, [_VP, C.c_char_p, _I, _F, _F]),
+    "tsdf_group_save_bin": (_I, [_VP, C.c_char_p]),
+    "tsdf_group_save_mesh_ply": (_I, [_VP, C.c_char_p]),
     "tsdf_host_alloc": (_I, [C.POINTER(_VP), C.c_size_t]),
     "tsdf_host_free": (_I, [_VP]),
     "tsdf_device_alloc": (_I, [_I, C.POINTER(_VP), C.c_size_t]),
@@ -109,6 +127,8 @@ SIGNATURES = {
     "tsdf_timer_start": (_I, [_VP]),
     "tsdf_timer_stop": (_I, [_VP, C.POINTER(_F)]),
     "tsdf_launch_count": (_I, [C.POINTER(_I64)]),
+    "tsdf_trace_enable": (_I, [_VP, _I]),
+    "tsdf_trace_read": (_I, [_VP, _VP, _I, C.POINTER(_I)]),
     "tsdf_kernel_timing": (_I, [_VP, _I]),
     "tsdf_kernel_timing_read": (_I, [_VP, C.POINTER(C.c_double), C.POINTER(_I64), _I]),
     "tsdf_selftest_exactmath": (_I, [_I, _I64, C.c_uint64, C.POINTER(_I64)]),

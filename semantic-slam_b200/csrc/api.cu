@@ -164,18 +164,22 @@ static void free_vol(tsdf_vol* v) {
   DeviceGuard g(v->cfg.device);
   if (v->s_compute) cudaStreamSynchronize(v->s_compute);
   if (v->s_copy) cudaStreamSynchronize(v->s_copy);
-  for (FrameSlot& s : v->slot) {
+  auto free_slot = [](FrameSlot& s) {
     if (s.h_pinned) cudaFreeHost(s.h_pinned);
     if (s.d_raw) cudaFree(s.d_raw);
     if (s.d_frame) cudaFree(s.d_frame);
     if (s.uploaded) cudaEventDestroy(s.uploaded);
     if (s.consumed) cudaEventDestroy(s.consumed);
-  }
+  };
+  for (FrameSlot& s : v->slot) free_slot(s);
+  for (FrameSlot& s : v->bslot) free_slot(s);
   cudaFree(v->d_tsdf); cudaFree(v->d_weight); cudaFree(v->d_color);
   cudaFree(v->d_written); cudaFree(v->d_scratch); cudaFree(v->d_mesh);
+  v->out.release();
   if (v->h_written) cudaFreeHost(v->h_written);
   for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1, v->ev_t0, v->ev_t1}) if (e) cudaEventDestroy(e);
   for (cudaEvent_t e : v->kev) cudaEventDestroy(e);
+  for (cudaEvent_t e : v->tev) cudaEventDestroy(e);
   if (v->s_compute) cudaStreamDestroy(v->s_compute);
   if (v->s_copy) cudaStreamDestroy(v->s_copy);
   delete v;
@@ -239,6 +243,11 @@ extern "C" int tsdf_create(const tsdf_config* cfg, tsdf_vol** out) {
 }
 
 extern "C" int tsdf_destroy(tsdf_vol* v) {
+  if (v && v->attached) {
+    // its frame slots are exported to / mapped by the other ranks of a communicator
+    tsdf_set_error("tsdf_destroy: the volume is attached to a tsdf_comm; call tsdf_comm_destroy first");
+    return TSDF_E_INVALID;
+  }
   free_vol(v);
   return TSDF_OK;
 }
@@ -275,13 +284,15 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   if (!s.d_raw) {
     CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
     CU_CHECK(cudaMalloc(&s.d_frame, frame_alloc_bytes(v->cfg.im_h, v->cfg.im_w)));  // float4 per pixel (float when no colour) + tail
+    // tail = 0 from the start: preps that skip the memset rely on k_publish having cleared it
+    CU_CHECK(cudaMemset(frame_dmax_ptr(s.d_frame, px), 0, frame_tail_bytes(v->cfg.im_h, v->cfg.im_w)));
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
   }
   return TSDF_OK;
 }
 
-int ensure_frame_slot(tsdf_vol* v, int index) { return ensure_slot(v, v->slot[index]); }
+int ensure_bcast_slot(tsdf_vol* v, int index) { return ensure_slot(v, v->bslot[index]); }
 
 enum PtrKind { PTR_PAGEABLE, PTR_PINNED, PTR_DEVICE };
 static PtrKind ptr_kind(const void* p) {
@@ -292,10 +303,62 @@ static PtrKind ptr_kind(const void* p) {
   return PTR_PAGEABLE;
 }
 
+// ---- readback buffers ------------------------------------------------------------------------
+int OutBuffers::need_dev(int i, size_t bytes) {
+  if (bytes <= dcap[i]) return TSDF_OK;
+  if (d[i]) { cudaFree(d[i]); d[i] = nullptr; dcap[i] = 0; }
+  const size_t want = bytes + bytes / 4 + 4096;   // grow with slack: successive calls rarely re-allocate
+  CU_CHECK(cudaMalloc(&d[i], want));
+  dcap[i] = want;
+  return TSDF_OK;
+}
+int OutBuffers::need_host(size_t bytes) {
+  if (bytes <= hcap) return TSDF_OK;
+  if (h) { cudaFreeHost(h); h = nullptr; hcap = 0; }
+  CU_CHECK(cudaHostAlloc(&h, bytes, cudaHostAllocDefault));
+  hcap = bytes;
+  return TSDF_OK;
+}
+void OutBuffers::release() {
+  for (int i = 0; i < 4; ++i) { if (d[i]) cudaFree(d[i]); d[i] = nullptr; dcap[i] = 0; }
+  if (h) cudaFreeHost(h);
+  h = nullptr; hcap = 0;
+}
+
+int copy_to_host(OutBuffers* ob, void* dst, const void* d_src, size_t bytes, cudaStream_t st) {
+  if (!bytes) return TSDF_OK;
+  if (ptr_kind(dst) == PTR_PINNED) {
+    CU_CHECK(cudaMemcpyAsync(dst, d_src, bytes, cudaMemcpyDeviceToHost, st));   // the CALLER syncs `st`
+    return TSDF_OK;
+  }
+  // pageable destination: D2H into pinned staging at full PCIe rate, chunk i+1 in flight while the
+  // host copies chunk i out (cudaMemcpy to pageable memory does the same at a fraction of the rate)
+  constexpr size_t kChunk = 4u << 20;
+  int rc = ob->need_host(2 * kChunk);
+  if (rc) return rc;
+  static thread_local cudaEvent_t ev[2] = {nullptr, nullptr};
+  for (int i = 0; i < 2; ++i) if (!ev[i]) CU_CHECK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+  const size_t n_chunks = (bytes + kChunk - 1) / kChunk;
+  auto issue = [&](size_t c) -> cudaError_t {
+    const size_t off = c * kChunk, len = std::min(kChunk, bytes - off);
+    cudaError_t e = cudaMemcpyAsync(static_cast<char*>(ob->h) + (c & 1) * kChunk, static_cast<const char*>(d_src) + off, len,
+                                    cudaMemcpyDeviceToHost, st);
+    return e != cudaSuccess ? e : cudaEventRecord(ev[c & 1], st);
+  };
+  CU_CHECK(issue(0));
+  for (size_t c = 0; c < n_chunks; ++c) {
+    CU_CHECK(cudaEventSynchronize(ev[c & 1]));
+    if (c + 1 < n_chunks) CU_CHECK(issue(c + 1));   // lands in the other half
+    const size_t off = c * kChunk, len = std::min(kChunk, bytes - off);
+    memcpy(static_cast<char*>(dst) + off, static_cast<const char*>(ob->h) + (c & 1) * kChunk, len);
+  }
+  return TSDF_OK;
+}
+
 // Moves `bytes` from src (any kind) to where the prep kernel can read it; returns the device
 // pointer to read from.  Pageable data goes through the slot's pinned buffer.
-static int to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
-                     const void** d_out, bool into_slot = false) {
+int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
+                    const void** d_out, bool into_slot) {
   PtrKind k = ptr_kind(src);
   char* dst = reinterpret_cast<char*>(s.d_raw) + raw_off;
   if (k == PTR_DEVICE) {
@@ -318,7 +381,7 @@ static int to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, s
 
 int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
                 int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot,
-                const float* K) {
+                const float* K, bool clear_tail) {
   FrameSlot& s = v->slot[slot_index];
   int rc = ensure_slot(v, s);
   if (rc) return rc;
@@ -332,15 +395,15 @@ int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, f
   const float intr[4] = {k[0], k[2], k[4], k[5]};
   const void* d_depth = nullptr;
   const void* d_rgb = nullptr;
-  rc = to_device(v, s, depth, dbytes, 0, &d_depth);
+  rc = frame_to_device(v, s, depth, dbytes, 0, &d_depth, false);
   if (rc) return rc;
   if (want_color && rgb) {
-    rc = to_device(v, s, rgb, px * 3, ((px * 4 + 63) / 64) * 64, &d_rgb);
+    rc = frame_to_device(v, s, rgb, px * 3, ((px * 4 + 63) / 64) * 64, &d_rgb, false);
     if (rc) return rc;
   }
   rc = launch_frame_prep(d_depth, depth_fmt, depth_scale, sub_c, sub_r,
                          reinterpret_cast<const uint8_t*>(d_rgb), nullptr, v->cfg.im_h, v->cfg.im_w,
-                         v->cfg.max_depth, want_color, intr, s.d_frame, v->s_copy);
+                         v->cfg.max_depth, want_color, intr, s.d_frame, v->s_copy, clear_tail);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(s.uploaded, v->s_copy));
   *out_slot = &s;
@@ -362,6 +425,7 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
   out->fx = k[0]; out->cx = k[2]; out->fy = k[4]; out->cy = k[5];
   out->obs_weight = obs_weight;
   out->pad_ = 0;
+  out->skip = v->comm_skip;
   out->mb_x0 = 0; out->mb_y0 = 0; out->mb_x1 = v->cfg.im_w - 1; out->mb_y1 = v->cfg.im_h - 1;
   out->img = d_frame;
   out->dmax = frame_dmax_ptr(d_frame, frame_pixels(v->cfg));
@@ -389,7 +453,7 @@ int check_obs_weight(float obs_weight) {
 }
 
 // Launches the integrate kernel for nf prepared frames and records stats/events.
-static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
+int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
   if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
   cudaEvent_t k0 = v->ev_k0, k1 = v->ev_k1;
@@ -407,10 +471,15 @@ static int submit(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool
   }
   v->wmode_ok = account_weights(v, fp, nf);
   CU_CHECK(cudaEventRecord(k0, v->s_compute));
+  trace_mark(v, 2, v->s_compute);
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(k1, v->s_compute));
-  rc = launch_publish(v, false, v->s_compute);
+  trace_mark(v, 3, v->s_compute);
+  // single-frame submissions: the publish kernel also zeroes the consumed slot's max-depth tiles, so
+  // the next prep into it runs without a memset (handles under A/B tooling keep the frame intact:
+  // tsdf_bench_kernel re-launches on it)
+  rc = launch_publish(v, false, v->s_compute, (nf == 1 && !v->dev_hold) ? slots[0]->d_frame : nullptr);
   if (rc) return rc;
   for (int i = 0; i < nf; ++i) {
     CU_CHECK(cudaEventRecord(slots[i]->consumed, v->s_compute));
@@ -438,15 +507,17 @@ extern "C" int tsdf_integrate_raw_async(tsdf_vol* v, const void* depth, int dept
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   FrameSlot* s = nullptr;
+  trace_mark(v, 0, v->s_copy);
   CU_CHECK(cudaEventRecord(v->ev_u0, v->s_copy));
   int rc = stage_frame(v, (int)(v->seq % 3), depth, depth_fmt, depth_scale, sub_c < 1 ? 1 : sub_c,
-                       sub_r < 1 ? 1 : sub_r, rgb, color, &s, K);
+                       sub_r < 1 ? 1 : sub_r, rgb, color, &s, K, /*clear_tail=*/v->dev_hold);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(v->ev_u1, v->s_copy));
+  trace_mark(v, 1, v->s_copy);
   ++v->seq;
   FrameP fp;
   make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
-  return submit(v, &s, &fp, 1, color);
+  return submit_frames(v, &s, &fp, 1, color);
 }
 
 extern "C" int tsdf_integrate_async(tsdf_vol* v, const float* depth, const uint8_t* rgb,
@@ -482,7 +553,7 @@ extern "C" int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth
       make_frame_params(v, K, T_wc + 16 * f, obs_weight, slots[i]->d_frame, &fp[i]);
     }
     ++v->mseq;
-    int rc = submit(v, slots, fp, nf, color);
+    int rc = submit_frames(v, slots, fp, nf, color);
     if (rc) return rc;
     done += nf;
   }
@@ -495,7 +566,13 @@ extern "C" int tsdf_sync(tsdf_vol* v) {
   CU_CHECK(cudaStreamSynchronize(v->s_copy));
   CU_CHECK(cudaStreamSynchronize(v->s_compute));
   for (FrameSlot& s : v->slot) s.in_flight = false;
+  for (FrameSlot& s : v->bslot) s.in_flight = false;
   v->last_written = (int64_t)*v->h_written;
+  if (v->comm_err && *v->comm_err) {
+    tsdf_set_error("frame distribution: a peer-pull wait timed out (code %d): a rank is gone or stalled; the "
+                   "frames behind it were NOT integrated on this rank", *v->comm_err);
+    return TSDF_E_NCCL;
+  }
   return TSDF_OK;
 }
 
@@ -525,6 +602,7 @@ extern "C" int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s) {
 extern "C" int tsdf_set_variant(tsdf_vol* v, int variant) {
   REQUIRE(v, "null handle");
   v->variant = variant;
+  v->dev_hold = true;   // A/B tooling re-launches on the last prepared frame: keep its tail intact
   return TSDF_OK;
 }
 
@@ -637,7 +715,10 @@ extern "C" int tsdf_extract_points_device(tsdf_vol* v, int predicate, float tsdf
   DeviceGuard g(v->cfg.device);
   int rc = tsdf_sync(v);
   if (rc) return rc;
-  return extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, cap, count);
+  rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, cap, count);
+  if (rc) return rc;
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  return TSDF_OK;
 }
 
 extern "C" int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
@@ -657,22 +738,22 @@ extern "C" int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh
     return TSDF_E_CAPACITY;
   }
   if (n == 0) return TSDF_OK;
-  float* d_xyz = nullptr; uint8_t* d_rgb = nullptr; int64_t* d_idx = nullptr;
-  auto cleanup = [&]() { cudaFree(d_xyz); cudaFree(d_rgb); cudaFree(d_idx); };
-  cudaError_t e = cudaSuccess;
-  if (xyz) e = cudaMalloc(&d_xyz, (size_t)n * 12);
-  if (e == cudaSuccess && rgb) e = cudaMalloc(&d_rgb, (size_t)n * 3);
-  if (e == cudaSuccess && idx) e = cudaMalloc(&d_idx, (size_t)n * 8);
-  if (e != cudaSuccess) { cleanup(); tsdf_set_error("extract: output alloc: %s", cudaGetErrorString(e)); return TSDF_E_NOMEM; }
+  // outputs live in the handle's grow-only device buffers; each array goes to the caller with its own
+  // asynchronous copy (straight into pinned memory, or through the pinned staging area)
+  OutBuffers& ob = v->out;
+  if (xyz && (rc = ob.need_dev(0, (size_t)n * 12))) return rc;
+  if (rgb && (rc = ob.need_dev(1, (size_t)n * 3))) return rc;
+  if (idx && (rc = ob.need_dev(2, (size_t)n * 8))) return rc;
+  float* d_xyz = xyz ? static_cast<float*>(ob.d[0]) : nullptr;
+  uint8_t* d_rgb = rgb ? static_cast<uint8_t*>(ob.d[1]) : nullptr;
+  int64_t* d_idx = idx ? static_cast<int64_t*>(ob.d[2]) : nullptr;
   rc = extract_device(v, predicate, tsdf_thresh, weight_thresh, d_xyz, d_rgb, d_idx, n, &n);
-  if (!rc) {
-    if (xyz) e = cudaMemcpy(xyz, d_xyz, (size_t)n * 12, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess && rgb) e = cudaMemcpy(rgb, d_rgb, (size_t)n * 3, cudaMemcpyDeviceToHost);
-    if (e == cudaSuccess && idx) e = cudaMemcpy(idx, d_idx, (size_t)n * 8, cudaMemcpyDeviceToHost);
-    if (e != cudaSuccess) { tsdf_set_error("extract: D2H: %s", cudaGetErrorString(e)); rc = TSDF_E_CUDA; }
-  }
-  cleanup();
-  return rc;
+  if (rc) return rc;
+  if (xyz && (rc = copy_to_host(&ob, xyz, d_xyz, (size_t)n * 12, v->s_compute))) return rc;
+  if (rgb && (rc = copy_to_host(&ob, rgb, d_rgb, (size_t)n * 3, v->s_compute))) return rc;
+  if (idx && (rc = copy_to_host(&ob, idx, d_idx, (size_t)n * 8, v->s_compute))) return rc;
+  CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  return TSDF_OK;
 }
 
 // ---- mesh readback (plugin SaveMesh, src/TSDFfusion.py.in:48-53) -------------------------------
@@ -706,26 +787,25 @@ extern "C" int tsdf_extract_mesh(tsdf_vol* v, float* verts, float* norms, uint8_
     tsdf_set_error("tsdf_extract_mesh: face capacity %lld < %lld", (long long)fcap, (long long)nf);
     return TSDF_E_CAPACITY;
   }
-  float* d_v = nullptr; float* d_n = nullptr; uint8_t* d_c = nullptr; int32_t* d_f = nullptr;
-  auto cleanup = [&]() { cudaFree(d_v); cudaFree(d_n); cudaFree(d_c); cudaFree(d_f); };
-  cudaError_t e = cudaSuccess;
-  if (verts && nv) e = cudaMalloc(&d_v, (size_t)nv * 12);
-  if (e == cudaSuccess && norms && nv) e = cudaMalloc(&d_n, (size_t)nv * 12);
-  if (e == cudaSuccess && colors && nv) e = cudaMalloc(&d_c, (size_t)nv * 3);
-  if (e == cudaSuccess && faces && nf) e = cudaMalloc(&d_f, (size_t)nf * 12);
-  if (e != cudaSuccess) { cleanup(); tsdf_set_error("mesh: output alloc: %s", cudaGetErrorString(e)); return TSDF_E_NOMEM; }
+  OutBuffers& ob = v->out;
+  if (verts && nv && (rc = ob.need_dev(0, (size_t)nv * 12))) return rc;
+  if (norms && nv && (rc = ob.need_dev(1, (size_t)nv * 12))) return rc;
+  if (colors && nv && (rc = ob.need_dev(2, (size_t)nv * 3))) return rc;
+  if (faces && nf && (rc = ob.need_dev(3, (size_t)nf * 12))) return rc;
+  float* d_v = (verts && nv) ? static_cast<float*>(ob.d[0]) : nullptr;
+  float* d_n = (norms && nv) ? static_cast<float*>(ob.d[1]) : nullptr;
+  uint8_t* d_c = (colors && nv) ? static_cast<uint8_t*>(ob.d[2]) : nullptr;
+  int32_t* d_f = (faces && nf) ? static_cast<int32_t*>(ob.d[3]) : nullptr;
   if (d_v || d_n || d_c || d_f) {
     rc = mesh_device(v, d_v, d_n, d_c, nv, d_f, nf, &nv, &nf);
-    if (!rc) {
-      if (d_v) e = cudaMemcpy(verts, d_v, (size_t)nv * 12, cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess && d_n) e = cudaMemcpy(norms, d_n, (size_t)nv * 12, cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess && d_c) e = cudaMemcpy(colors, d_c, (size_t)nv * 3, cudaMemcpyDeviceToHost);
-      if (e == cudaSuccess && d_f) e = cudaMemcpy(faces, d_f, (size_t)nf * 12, cudaMemcpyDeviceToHost);
-      if (e != cudaSuccess) { tsdf_set_error("mesh: D2H: %s", cudaGetErrorString(e)); rc = TSDF_E_CUDA; }
-    }
+    if (rc) return rc;
+    if (d_v && (rc = copy_to_host(&ob, verts, d_v, (size_t)nv * 12, v->s_compute))) return rc;
+    if (d_n && (rc = copy_to_host(&ob, norms, d_n, (size_t)nv * 12, v->s_compute))) return rc;
+    if (d_c && (rc = copy_to_host(&ob, colors, d_c, (size_t)nv * 3, v->s_compute))) return rc;
+    if (d_f && (rc = copy_to_host(&ob, faces, d_f, (size_t)nf * 12, v->s_compute))) return rc;
+    CU_CHECK(cudaStreamSynchronize(v->s_compute));
   }
-  cleanup();
-  return rc;
+  return TSDF_OK;
 }
 
 // fusion.meshwrite: ascii PLY, "%f %f %f %f %f %f %d %d %d" per vertex, "3 %d %d %d" per face.
@@ -742,6 +822,11 @@ extern "C" int tsdf_save_mesh_ply(tsdf_vol* v, const char* path) {
     rc = tsdf_extract_mesh(v, verts.data(), norms.data(), cols.data(), nv, faces.data(), nf, &nv, &nf);
     if (rc) return rc;
   }
+  return write_mesh_ply(path, verts.data(), norms.data(), cols.data(), nv, faces.data(), nf);
+}
+
+int write_mesh_ply(const char* path, const float* verts, const float* norms, const uint8_t* cols, int64_t nv,
+                   const int32_t* faces, int64_t nf) {
   FILE* fp = fopen(path, "w");
   if (!fp) { tsdf_set_error("tsdf_save_mesh_ply: cannot open %s", path); return TSDF_E_IO; }
   fprintf(fp, "ply\nformat ascii 1.0\nelement vertex %d\n", (int)nv);
@@ -771,6 +856,10 @@ extern "C" int tsdf_save_ply(tsdf_vol* v, const char* path, int predicate, float
     rc = tsdf_extract_points(v, predicate, tsdf_thresh, weight_thresh, xyz.data(), nullptr, nullptr, n, &n);
     if (rc) return rc;
   }
+  return write_points_ply(path, xyz.data(), n);
+}
+
+int write_points_ply(const char* path, const float* xyz, int64_t n) {
   FILE* fp = fopen(path, "w");
   if (!fp) { tsdf_set_error("tsdf_save_ply: cannot open %s", path); return TSDF_E_IO; }
   fprintf(fp, "ply\n");
@@ -780,7 +869,7 @@ extern "C" int tsdf_save_ply(tsdf_vol* v, const char* path, int predicate, float
   fprintf(fp, "property float y\n");
   fprintf(fp, "property float z\n");
   fprintf(fp, "end_header\n");
-  size_t wr = fwrite(xyz.data(), sizeof(float), (size_t)n * 3, fp);
+  size_t wr = fwrite(xyz, sizeof(float), (size_t)n * 3, fp);
   fclose(fp);
   if (wr != (size_t)n * 3) { tsdf_set_error("tsdf_save_ply: short write"); return TSDF_E_IO; }
   return TSDF_OK;
@@ -793,15 +882,18 @@ extern "C" int tsdf_save_bin(tsdf_vol* v, const char* path) {
   std::vector<float> t((size_t)v->n_local);
   int rc = tsdf_download(v, t.data(), nullptr, nullptr, 0);
   if (rc) return rc;
+  return write_bin(path, v->cfg, t.data(), t.size());
+}
+
+int write_bin(const char* path, const tsdf_config& c, const float* tsdf, size_t n) {
   FILE* fp = fopen(path, "wb");
   if (!fp) { tsdf_set_error("tsdf_save_bin: cannot open %s", path); return TSDF_E_IO; }
-  const tsdf_config& c = v->cfg;
   float h[8] = {(float)c.dim_x, (float)c.dim_y, (float)c.dim_z, c.origin[0], c.origin[1], c.origin[2],
                 c.voxel_size, c.trunc_margin};
   size_t wr = fwrite(h, sizeof(float), 8, fp);
-  wr += fwrite(t.data(), sizeof(float), t.size(), fp);
+  wr += fwrite(tsdf, sizeof(float), n, fp);
   fclose(fp);
-  if (wr != 8 + t.size()) { tsdf_set_error("tsdf_save_bin: short write"); return TSDF_E_IO; }
+  if (wr != 8 + n) { tsdf_set_error("tsdf_save_bin: short write"); return TSDF_E_IO; }
   return TSDF_OK;
 }
 
@@ -889,56 +981,6 @@ extern "C" int tsdf_memcpy_d2h(int device, void* dst, const void* src, size_t by
   DeviceGuard g(device);
   CU_CHECK(cudaMemcpy(dst, src, bytes, cudaMemcpyDeviceToHost));
   return TSDF_OK;
-}
-
-// ---- helpers for comm.cu: frame staging split around the NCCL broadcast ------------------------
-// bcast_stage picks the next single-frame slot, moves the root's images to the device (or
-// takes them where they already are) and tells comm.cu what to broadcast into the slot's raw
-// buffer; bcast_finish preps the slot and launches the integrate.
-int bcast_stage(tsdf_vol* v, bool is_root, const float* depth, const uint8_t* rgb, bool color,
-                FrameSlot** slot, void** d_depth, void** d_rgb, const void** send_depth,
-                const void** send_rgb, bool into_slot) {
-  FrameSlot& s = v->slot[v->seq % 3];
-  int rc = ensure_slot(v, s);
-  if (rc) return rc;
-  if (s.in_flight) {
-    CU_CHECK(cudaEventSynchronize(s.consumed));
-    s.in_flight = false;
-  }
-  const size_t px = frame_pixels(v->cfg);
-  const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
-  *d_depth = s.d_raw;
-  *d_rgb = reinterpret_cast<char*>(s.d_raw) + rgb_off;
-  *send_depth = *d_depth;
-  *send_rgb = *d_rgb;
-  if (is_root) {
-    rc = to_device(v, s, depth, px * 4, 0, send_depth, into_slot);   // device inputs are sent from where they are
-    if (rc) return rc;
-    if (color) {
-      rc = to_device(v, s, rgb, px * 3, rgb_off, send_rgb, into_slot);
-      if (rc) return rc;
-    }
-  }
-  *slot = &s;
-  return TSDF_OK;
-}
-
-int bcast_finish(tsdf_vol* v, FrameSlot* s, bool color, const float* K, const float* T_wc,
-                 float obs_weight, const void* src_raw, int (*after_prep)(void*, cudaStream_t), void* after_arg) {
-  const size_t px = frame_pixels(v->cfg);
-  const size_t rgb_off = ((px * 4 + 63) / 64) * 64;
-  const void* raw = src_raw ? src_raw : s->d_raw;   // peer-pull: the root's raw slot through NVLink
-  int rc = launch_frame_prep(raw, TSDF_DEPTH_F32, 1.0f, 1, 1,
-                             color ? reinterpret_cast<const uint8_t*>(raw) + rgb_off : nullptr,
-                             nullptr, v->cfg.im_h, v->cfg.im_w, v->cfg.max_depth, color, nullptr, s->d_frame,
-                             v->s_copy);
-  if (rc) return rc;
-  if (after_prep && (rc = after_prep(after_arg, v->s_copy))) return rc;
-  CU_CHECK(cudaEventRecord(s->uploaded, v->s_copy));
-  ++v->seq;
-  FrameP fp;
-  make_frame_params(v, K, T_wc, obs_weight, s->d_frame, &fp);
-  return submit(v, &s, &fp, 1, color);
 }
 
 // ---- pose ingest ------------------------------------------------------------
@@ -1091,6 +1133,49 @@ extern "C" int tsdf_read_associations(const char* path, double* t_rgb, double* t
   fclose(f);
   if (rc == TSDF_OK) *n_lines = n;
   return rc;
+}
+
+// ---- per-frame timeline (evidence for the multi-GPU step chain) --------------------
+int trace_mark(tsdf_vol* v, int which, cudaStream_t st) {
+  if (!v->tracing) return TSDF_OK;
+  if (which == 0) {   // a new frame: four fresh slots
+    v->tev_used = (v->tev_used + 3) / 4 * 4;
+    while (v->tev.size() < v->tev_used + 4) {
+      cudaEvent_t e;
+      CU_CHECK(cudaEventCreate(&e));
+      v->tev.push_back(e);
+    }
+    v->tev_used += 4;
+  }
+  if (v->tev_used < 4) return TSDF_OK;
+  CU_CHECK(cudaEventRecord(v->tev[v->tev_used - 4 + which], st));
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_trace_enable(tsdf_vol* v, int enable) {
+  REQUIRE(v, "null handle");
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  v->tracing = enable != 0;
+  v->tev_used = 0;
+  return TSDF_OK;
+}
+
+extern "C" int tsdf_trace_read(tsdf_vol* v, float* ms4, int cap_frames, int* n_frames) {
+  REQUIRE(v && n_frames, "null argument");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  const int n = (int)(v->tev_used / 4);
+  *n_frames = n;
+  if (!ms4 || n == 0) return TSDF_OK;
+  for (int f = 0; f < n && f < cap_frames; ++f)
+    for (int k = 0; k < 4; ++k) {
+      float ms = 0;
+      if (cudaEventElapsedTime(&ms, v->tev[0], v->tev[4 * f + k]) != cudaSuccess) { cudaGetLastError(); ms = -1.0f; }
+      ms4[4 * f + k] = ms;
+    }
+  return TSDF_OK;
 }
 
 // ---- measurement hooks ---------------------------------------------------------------------------

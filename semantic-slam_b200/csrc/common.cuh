@@ -57,6 +57,8 @@ struct FrameP {       // one camera frame
   float fx, cx, fy, cy;  // K[0],K[2],K[4],K[5], src/tsdf.cu:41-42
   float obs_weight;
   int pad_;
+  const int* skip;    // device word that is non-zero when this frame must NOT be integrated (a peer-pull
+                      // wait timed out: the prepared frame is stale), or null — see comm.cu
   int mb_x0, mb_y0, mb_x1, mb_y1;  // pixel rectangle (inclusive) outside which the frame is known to be
                                    // invalid for this launch: the instance's mask box, else the image
   const void* img;    // prepared frame: float depth[H*W]  or  float4 {depth, c0, c1, c2}[H*W]
@@ -91,6 +93,23 @@ struct BatchDesc {    // one active instance of a batched launch (lives in globa
 // Depth-only frames are a plain float image.
 
 // ---- host-side handle -------------------------------------------------------------------
+// Grow-only buffers of the readback calls (points, mesh, gather): device arrays the emit kernels
+// write and one pinned host staging area for pageable destinations; kept between calls by their owner
+// (the reference-style "count, allocate, emit" sequence must not pay cudaMalloc/cudaFree per call).
+struct OutBuffers {
+  void* d[4] = {nullptr, nullptr, nullptr, nullptr};
+  size_t dcap[4] = {0, 0, 0, 0};
+  void* h = nullptr;       // pinned
+  size_t hcap = 0;
+  int need_dev(int i, size_t bytes);    // TSDF status; contents are NOT preserved when it grows
+  int need_host(size_t bytes);
+  void release();
+};
+// Device -> caller's host array on `st`: straight cudaMemcpyAsync when dst is pinned, else through
+// the pinned staging area in double-buffered chunks (then the data is in dst on return).  A pinned
+// destination is only ENQUEUED: the caller synchronises `st` after its last copy.
+int copy_to_host(OutBuffers* ob, void* dst, const void* d_src, size_t bytes, cudaStream_t st);
+
 struct FrameSlot {
   void* h_pinned = nullptr;   // staging for pageable inputs (depth + rgb)
   void* d_raw = nullptr;      // raw upload target (depth fp32|u16 + rgb u8)
@@ -100,6 +119,9 @@ struct FrameSlot {
   bool in_flight = false;
 };
 
+constexpr int kBcastSlots = 6;  // frame ring of the distributed (multi-GPU) integrate calls
+
+struct tsdf_comm;
 struct tsdf_vol {
   tsdf_config cfg;
   int dzl = 0;                 // local slices
@@ -118,12 +140,21 @@ struct tsdf_vol {
   cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_u0 = nullptr, ev_u1 = nullptr;
   // slots 0..2: single-frame ring; 3..3+2*kMaxFusedFrames: two groups for fused launches
   FrameSlot slot[3 + kMaxFusedFrames * 2];
+  // ring of the distributed integrate calls (tsdf_integrate_bcast_async, tsdf_group_*): indexed by
+  // the distribution sequence number, never by `seq`, so single-frame calls may be interleaved
+  FrameSlot bslot[kBcastSlots];
+  // set while a communicator has this volume's frame slots exported / mapped: tsdf_destroy refuses
+  // (the peers may still read them), tsdf_sync surfaces *comm_err (a timed-out peer-pull wait)
+  tsdf_comm* attached = nullptr;
+  const int* comm_err = nullptr;   // pinned host word of the attached communicator
+  const int* comm_skip = nullptr;  // its device twin (FrameP::skip)
   uint64_t seq = 0;            // single-frame submissions
   uint64_t mseq = 0;           // fused submissions
   int64_t frames = 0;
   int64_t last_written = 0;
   int64_t last_frames_in_launch = 1;
   int variant = 0;
+  bool dev_hold = false;       // set by tsdf_set_variant: prepared frames stay intact after their launch
   // integer-weight bookkeeping: true while every stored weight is provably an integer
   // (only obs_weight == 1 integrations since the last reset); w_bound >= max stored weight
   bool intw = true;
@@ -138,6 +169,12 @@ struct tsdf_vol {
   bool ktiming = false;
   std::vector<cudaEvent_t> kev;   // pairs
   size_t kev_used = 0;            // events recorded since reset (2 per launch)
+  // per-frame timeline (tsdf_trace_*): 4 events per frame {copy stream: first op enqueued, prepared
+  // frame ready; compute stream: integrate begins, integrate ends}
+  bool tracing = false;
+  std::vector<cudaEvent_t> tev;
+  size_t tev_used = 0;
+  OutBuffers out;              // readback outputs (tsdf_extract_points / tsdf_extract_mesh)
   // extraction scratch
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
@@ -178,10 +215,28 @@ inline float* frame_dmax_ptr(const void* d_frame, size_t px) {
   return reinterpret_cast<float*>(reinterpret_cast<char*>(const_cast<void*>(d_frame)) + px * 16);
 }
 
+// Peer-pull distribution fused into the prep kernel (comm.cu); all zero = plain prep.
+struct PrepSync {
+  const unsigned* wait_flag = nullptr;  // peer: spin until *wait_flag >= wait_target before reading the source
+  int wait_target = 0;
+  unsigned* ready_flag = nullptr;       // root: store ready_value at the head (its source is already in place:
+  unsigned ready_value = 0;             //       the H2D copies precede this kernel in stream order)
+  unsigned* done_flag = nullptr;        // peer: the last block to finish stores done_value (source consumed)
+  unsigned done_value = 0;
+  int ring = 0;                         // peer: slots in the root's ring; `ready` >= wait_target + ring at the
+                                        //       tail means the slot was overwritten while being read
+  unsigned* arrive = nullptr;           // device counter for the last-block detection (re-arms itself)
+  int* d_err = nullptr;                 // set to 1 on timeout (device word: FrameP::skip of this rank) ...
+  int* h_err = nullptr;                 // ... and its pinned host twin, read by the host API
+  unsigned long long timeout_ns = 0;
+};
+
 // ---- launchers implemented in the .cu files -----------------------------------------------
 // integrate.cu
 int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st);
-int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st);  // N_written -> pinned mirror, counter = 0
+// N_written -> pinned mirror, counter = 0; optionally zeroes the tail (max-depth tiles) of the frame
+// slot the launch before it consumed, so that the next prep into that slot needs no memset
+int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear = nullptr);
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st);
 void fill_grid_params(const tsdf_vol* v, bool color, GridP* g);
@@ -190,7 +245,7 @@ bool account_weights(tsdf_vol* v, const FrameP* fp, int nf);  // updates intw/w_
 int launch_frame_prep(const void* d_depth, int depth_fmt, float depth_scale, int sub_c, int sub_r,
                       const uint8_t* d_rgb, const uint8_t* d_mask, int H, int W, float max_depth,
                       bool with_color, const float intr[4] /* fx,cx,fy,cy: RANGE formats only */,
-                      void* d_frame, cudaStream_t st);
+                      void* d_frame, cudaStream_t st, bool clear_tail = true, const PrepSync* sync = nullptr);
 int launch_fill(float* p, float val, int64_t n, cudaStream_t st);
 int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, int W, float fx,
                            float cx, float fy, float cy, float* d_out3, cudaStream_t st);
@@ -198,6 +253,10 @@ int launch_instance_origin(const float* d_depth, const uint8_t* d_mask, int H, i
 int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh, float* d_xyz,
                    uint8_t* d_rgb, int64_t* d_idx, int64_t cap, int64_t* count);
 int ensure_scratch(tsdf_vol* v, size_t bytes);
+// runs of records (run r = [offs[r], offs[r+1]), each ascending by index, indices distinct) -> one
+// ascending sequence; d_offs: nranks + 1 device entries
+int launch_merge_scatter(int64_t total, int nranks, const int64_t* d_offs, const float* g_xyz, const int64_t* g_idx,
+                         const uint8_t* g_rgb, float* o_xyz, int64_t* o_idx, uint8_t* o_rgb, cudaStream_t st);
 int launch_scan(const uint32_t* d_cnt, int64_t m, int64_t* d_off, int64_t* d_tot, cudaStream_t st,  // off[m] = total
                 const uint32_t* d_cnt_b = nullptr, int64_t* d_off_b = nullptr,                   // second triple,
                 int64_t* d_tot_b = nullptr,                                                       // same m
@@ -209,10 +268,21 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
                 int32_t* d_faces, int64_t fcap, int64_t* n_verts, int64_t* n_faces);
 
 // api.cpp helpers used elsewhere
+int write_points_ply(const char* path, const float* xyz, int64_t n);                       // src/tsdf.cu:186-216
+int write_bin(const char* path, const tsdf_config& c, const float* tsdf, size_t n);        // src/tsdf.cu:116-132
+int write_mesh_ply(const char* path, const float* verts, const float* norms, const uint8_t* cols, int64_t nv,
+                   const int32_t* faces, int64_t nf);                                      // fusion.meshwrite
+int trace_mark(tsdf_vol* v, int which, cudaStream_t st);   // no-op unless tsdf_trace_enable(v, 1)
 int check_obs_weight(float obs_weight);  // one validation for every integrate entry point
+int ensure_bcast_slot(tsdf_vol* v, int index);
+// moves `bytes` of a frame (pageable / pinned host or device memory) to where the prep kernel reads it
+int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
+                    const void** d_out, bool into_slot);
+// waits for the slots' uploads, launches the integrate kernel(s) + publish, records the events
+int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color);
 int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);
 int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
                       const void* d_frame, FrameP* out);
 int stage_frame(tsdf_vol* v, int slot_index, const void* depth, int depth_fmt, float depth_scale,
                 int sub_c, int sub_r, const uint8_t* rgb, bool want_color, FrameSlot** out_slot,
-                const float* K = nullptr);
+                const float* K = nullptr, bool clear_tail = true);

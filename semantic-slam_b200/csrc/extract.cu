@@ -9,6 +9,8 @@
 //   pass 2  k_emit : reads only the ballots; rank = popc of lower bits; writes xyz
 //                    (origin + (float)i*vs, src/tsdf.cu:206-208), GLOBAL reference index and
 //                    rgb (colour gathered for kept voxels only)
+#include <algorithm>
+
 #include "common.cuh"
 
 namespace {
@@ -332,6 +334,46 @@ int extract_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_t
   p.color = v->d_color;
   k_emit<<<(unsigned)n_tiles, kThreads, 0, st>>>(d_bal, d_off, p, d_xyz, d_rgb, d_idx);
   CU_LAUNCHED();
-  CU_CHECK(cudaStreamSynchronize(st));
+  return TSDF_OK;   // NOT synchronised: the caller's copies / sends follow on the same stream
+}
+
+// ---- merge of per-slab point runs (multi-GPU readback: comm.cu, group.cu) ------------------------
+namespace {
+// Records of all ranks sit rank after rank in G_* (rank r: [offs[r], offs[r+1])), each rank's run
+// ascending by GLOBAL reference index, all indices distinct.  The merged position of a record is its
+// position in its own run plus, for every other run, the number of records with a smaller index
+// (a binary search): no atomics, deterministic, ascending global order.
+__global__ void k_merge_scatter(int64_t total, int nranks, const int64_t* __restrict__ offs,
+                                const float* __restrict__ g_xyz, const int64_t* __restrict__ g_idx,
+                                const uint8_t* __restrict__ g_rgb, float* __restrict__ o_xyz,
+                                int64_t* __restrict__ o_idx, uint8_t* __restrict__ o_rgb) {
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < total; j += (int64_t)gridDim.x * blockDim.x) {
+    int r = 0;
+    while (r + 1 < nranks && j >= offs[r + 1]) ++r;
+    const int64_t key = g_idx[j];
+    int64_t pos = j - offs[r];
+    for (int q = 0; q < nranks; ++q) {
+      if (q == r) continue;
+      int64_t lo = offs[q], hi = offs[q + 1];
+      while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (g_idx[mid] < key) lo = mid + 1; else hi = mid;
+      }
+      pos += lo - offs[q];
+    }
+    o_idx[pos] = key;
+    o_xyz[3 * pos] = g_xyz[3 * j]; o_xyz[3 * pos + 1] = g_xyz[3 * j + 1]; o_xyz[3 * pos + 2] = g_xyz[3 * j + 2];
+    if (g_rgb) { o_rgb[3 * pos] = g_rgb[3 * j]; o_rgb[3 * pos + 1] = g_rgb[3 * j + 1]; o_rgb[3 * pos + 2] = g_rgb[3 * j + 2]; }
+  }
+}
+
+}  // namespace
+
+int launch_merge_scatter(int64_t total, int nranks, const int64_t* d_offs, const float* g_xyz, const int64_t* g_idx,
+                         const uint8_t* g_rgb, float* o_xyz, int64_t* o_idx, uint8_t* o_rgb, cudaStream_t st) {
+  if (total <= 0) return TSDF_OK;
+  const int blocks = (int)std::min<int64_t>((total + 255) / 256, 148 * 16);
+  k_merge_scatter<<<blocks, 256, 0, st>>>(total, nranks, d_offs, g_xyz, g_idx, g_rgb, o_xyz, o_idx, o_rgb);
+  CU_LAUNCHED();
   return TSDF_OK;
 }

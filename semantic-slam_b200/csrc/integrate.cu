@@ -340,6 +340,9 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   const int n_rows = g.n_mid * g.n_slow;
   const int row0 = blockIdx.x * rows_per_block;
   if (row0 >= n_rows) return;  // batched launches size the grid for the largest instance
+  // a peer-pull wait of this frame timed out (comm.cu): the prepared frame is stale, leave the
+  // volume untouched.  Grid-uniform; one L2-resident word.
+  if (P.f[0].skip != nullptr && *reinterpret_cast<const volatile int*>(P.f[0].skip) != 0) return;
 
   // ---- prologue 0 (sparse kernel): can ANY voxel of this block be touched? ----------------
   // The computed camera coordinates of voxel k of row (slow, mid) are e(slow, mid) + p_k (ZFAST)
@@ -694,10 +697,15 @@ k_integrate_batch(const BatchDesc* __restrict__ descs, int tpr_log2, int rows_pe
 // memory: this IS the step's 8-byte device->host read) and re-arms the counter, so the
 // compute stream carries no memset / memcpy operations between integrate launches.
 __global__ void k_publish(unsigned long long* __restrict__ written, unsigned long long* __restrict__ h_written,
-                          int accumulate) {
-  const unsigned long long n = *written;
-  *h_written = accumulate ? *h_written + n : n;
-  *written = 0ull;
+                          int accumulate, int* __restrict__ tail, int tail_words) {
+  if (threadIdx.x == 0) {
+    const unsigned long long n = *written;
+    *h_written = accumulate ? *h_written + n : n;
+    *written = 0ull;
+  }
+  // the launch before this one consumed the frame slot `tail` belongs to: zero its max-depth tiles
+  // now, so that the next prep into the slot needs no memset on the copy stream
+  for (int i = threadIdx.x; i < tail_words; i += blockDim.x) tail[i] = 0;
 }
 
 // Per-launch choices (no global state: handles may be driven from different host threads).
@@ -846,8 +854,10 @@ static bool slab_inside_every_frustum(const GridP& g, const FrameP* fr, int nf) 
   return true;
 }
 
-int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st) {
-  k_publish<<<1, 1, 0, st>>>(v->d_written, v->hd_written, accumulate ? 1 : 0);
+int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear) {
+  int* tail = d_frame_to_clear ? reinterpret_cast<int*>(frame_dmax_ptr(d_frame_to_clear, frame_pixels(v->cfg))) : nullptr;
+  const int words = tail ? (int)(frame_tail_bytes(v->cfg.im_h, v->cfg.im_w) / 4) : 0;
+  k_publish<<<1, tail ? 256 : 32, 0, st>>>(v->d_written, v->hd_written, accumulate ? 1 : 0, tail, words);
   CU_LAUNCHED();
   return TSDF_OK;
 }

@@ -94,7 +94,24 @@ class ShardedVolume:
         self.vol.sync()
         self._keep.clear()
 
-    def gather_points(self, pred=capi.PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, root=0, cap=None):
+    def gather_mesh(self, root=0):
+        """Collective: verts, faces, norms, colors of the WHOLE grid at the root (None elsewhere)."""
+        nv, nf = C.c_int64(0), C.c_int64(0)
+        args = (self.vol.h, self.comm, root)
+        check(self.lib.tsdf_gather_mesh(*args, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
+        if self.rank != root:
+            check(self.lib.tsdf_gather_mesh(*args, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
+            return None
+        nv, nf = nv.value, nf.value
+        verts = np.zeros((max(nv, 1), 3), np.float32)
+        norms = np.zeros((max(nv, 1), 3), np.float32)
+        cols = np.zeros((max(nv, 1), 3), np.uint8)
+        faces = np.zeros((max(nf, 1), 3), np.int32)
+        cv, cf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_gather_mesh(*args, ptr(verts), ptr(norms), ptr(cols), nv, ptr(faces), nf, C.byref(cv), C.byref(cf)))
+        return verts[:nv], faces[:nf], norms[:nv], cols[:nv]
+
+    def gather_points(self, pred=capi.PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, root=0, cap=None, pool=None):
         n = C.c_int64(0)
         if cap is None:  # collective sizing call first
             check(self.lib.tsdf_gather_points(self.vol.h, self.comm, root, pred, np.float32(tsdf_thresh),
@@ -105,9 +122,14 @@ class ShardedVolume:
                                               np.float32(weight_thresh), None, None, None, 0, C.byref(n)))
             return None, None, None, n.value
         cap = int(cap)
-        xyz = np.zeros((max(cap, 1), 3), np.float32)
-        rgb = np.zeros((max(cap, 1), 3), np.uint8)
-        idx = np.zeros(max(cap, 1), np.int64)
+        if pool is not None:
+            xyz = pool.array("xyz", (max(cap, 1), 3), np.float32)
+            rgb = pool.array("rgb", (max(cap, 1), 3), np.uint8)
+            idx = pool.array("idx", (max(cap, 1),), np.int64)
+        else:
+            xyz = np.zeros((max(cap, 1), 3), np.float32)
+            rgb = np.zeros((max(cap, 1), 3), np.uint8)
+            idx = np.zeros(max(cap, 1), np.int64)
         check(self.lib.tsdf_gather_points(self.vol.h, self.comm, root, pred, np.float32(tsdf_thresh),
                                           np.float32(weight_thresh), ptr(xyz), ptr(rgb), ptr(idx), cap, C.byref(n)))
         return xyz[:n.value], rgb[:n.value], idx[:n.value], n.value

@@ -134,8 +134,9 @@ def render(scene, K, hw, T_wc, rng, noise_sigma=0.0, hole_frac=0.0, max_range=np
 def s_full(dims, voxel_size, n_frames=4, seed=SEED_BASE, K=TUM3_K, hw=TUM3_HW, jitter=True, sphere=False):
     """Returns (origin[3], frames) with frames = list of (depth, rgb, T_wc).
     The volume is an axis-aligned box in the world frame, camera looks along +z.
-    sphere=True puts a sphere of radius 0.15 * min(L) (0.31 m at the 2.048 m bench volume) at the
-    volume centre: a surface for the readback leg; its interior and shadow are not written."""
+    sphere=True puts a sphere of radius 0.15 * min(L) (0.31 m at the 2.048 m bench volume) against the
+    far face of the volume: a surface for the readback leg; its interior and (short) shadow are not
+    written."""
     rng = np.random.default_rng(seed)
     Kf = np.asarray(K, float)
     H, W = hw
@@ -148,7 +149,8 @@ def s_full(dims, voxel_size, n_frames=4, seed=SEED_BASE, K=TUM3_K, hw=TUM3_HW, j
     wall_z = z_near + L[2] + 0.25
     scene = Scene().plane((0, 0, 1), wall_z)
     if sphere:
-        scene.sphere((0.0, 0.0, z_near + L[2] / 2), 0.15 * L.min())
+        r = 0.15 * L.min()
+        scene.sphere((0.0, 0.0, z_near + L[2] - 0.5 * r), r)   # near the far face: a short shadow
     frames = []
     for i in range(n_frames):
         if jitter and i > 0:

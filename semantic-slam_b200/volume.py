@@ -71,6 +71,35 @@ def device_count():
     return n.value if rc == capi.OK else 0
 
 
+class PinnedPool:
+    """Page-locked numpy arrays from tsdf_host_alloc, grown on demand and kept: readback calls copy
+    straight into them (cudaMemcpyAsync, no staging), uploads from them skip the staging copy."""
+
+    def __init__(self):
+        self.lib = capi.load()
+        self._bufs = {}   # name -> (ptr, nbytes)
+
+    def array(self, name, shape, dtype):
+        dtype = np.dtype(dtype)
+        need = max(1, int(np.prod(shape)) * dtype.itemsize)
+        ptr, cap = self._bufs.get(name, (None, 0))
+        if cap < need:
+            if ptr:
+                self.lib.tsdf_host_free(ptr)
+            p = C.c_void_p()
+            cap = need + need // 4
+            check(self.lib.tsdf_host_alloc(C.byref(p), cap))
+            ptr = p.value
+            self._bufs[name] = (ptr, cap)
+        raw = np.ctypeslib.as_array((C.c_uint8 * need).from_address(ptr))
+        return raw.view(dtype)[:int(np.prod(shape))].reshape(shape)
+
+    def close(self):
+        for ptr, _ in self._bufs.values():
+            self.lib.tsdf_host_free(ptr)
+        self._bufs = {}
+
+
 class Volume:
     """One `tsdf_vol*`.  Arrays returned by download() are in the semantics' reference order
     (TSDFCU: [z][y][x]; FUSIONPY: [x][y][z]) restricted to this handle's z-slab."""
@@ -195,6 +224,17 @@ class Volume:
         check(self.lib.tsdf_kernel_timing_read(self.h, C.byref(s), C.byref(n), int(reset)))
         return s.value, n.value
 
+    def trace_enable(self, enable=True):
+        check(self.lib.tsdf_trace_enable(self.h, int(enable)))
+
+    def trace_read(self):
+        """(n_frames, 4) ms relative to the first traced event: copy begin, frame ready, kernel begin, end."""
+        n = C.c_int(0)
+        check(self.lib.tsdf_trace_read(self.h, None, 0, C.byref(n)))
+        out = np.zeros((max(n.value, 1), 4), np.float32)
+        check(self.lib.tsdf_trace_read(self.h, ptr(out), n.value, C.byref(n)))
+        return out[:n.value]
+
     def set_variant(self, variant):
         check(self.lib.tsdf_set_variant(self.h, int(variant)))
 
@@ -231,11 +271,18 @@ class Volume:
                                            None, None, None, 0, C.byref(n)))
         return n.value
 
-    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
+    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, pool=None):
+        """pool: a PinnedPool -> the outputs are views of page-locked memory owned by the pool (valid
+        until the next call with the same pool): the D2H copies land in them directly."""
         n = self.extract_count(pred, tsdf_thresh, weight_thresh)
-        xyz = np.zeros((max(n, 1), 3), np.float32)
-        rgb = np.zeros((max(n, 1), 3), np.uint8)
-        idx = np.zeros(max(n, 1), np.int64)
+        if pool is not None:
+            xyz = pool.array("xyz", (max(n, 1), 3), np.float32)
+            rgb = pool.array("rgb", (max(n, 1), 3), np.uint8)
+            idx = pool.array("idx", (max(n, 1),), np.int64)
+        else:
+            xyz = np.zeros((max(n, 1), 3), np.float32)
+            rgb = np.zeros((max(n, 1), 3), np.uint8)
+            idx = np.zeros(max(n, 1), np.int64)
         cnt = C.c_int64(0)
         check(self.lib.tsdf_extract_points(self.h, pred, np.float32(tsdf_thresh), np.float32(weight_thresh),
                                            ptr(xyz), ptr(rgb), ptr(idx), n, C.byref(cnt)))
@@ -247,14 +294,20 @@ class Volume:
         check(self.lib.tsdf_extract_mesh(self.h, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
         return nv.value, nf.value
 
-    def extract_mesh(self):
+    def extract_mesh(self, pool=None):
         """Level-0 marching cubes on the device: verts (nv,3) f32, faces (nf,3) i32, norms (nv,3) f32,
         colors (nv,3) u8 — the tuple order of fusion.TSDFVolume.get_mesh()."""
         nv, nf = self.mesh_count()
-        verts = np.zeros((max(nv, 1), 3), np.float32)
-        norms = np.zeros((max(nv, 1), 3), np.float32)
-        cols = np.zeros((max(nv, 1), 3), np.uint8)
-        faces = np.zeros((max(nf, 1), 3), np.int32)
+        if pool is not None:
+            verts = pool.array("verts", (max(nv, 1), 3), np.float32)
+            norms = pool.array("norms", (max(nv, 1), 3), np.float32)
+            cols = pool.array("cols", (max(nv, 1), 3), np.uint8)
+            faces = pool.array("faces", (max(nf, 1), 3), np.int32)
+        else:
+            verts = np.zeros((max(nv, 1), 3), np.float32)
+            norms = np.zeros((max(nv, 1), 3), np.float32)
+            cols = np.zeros((max(nv, 1), 3), np.uint8)
+            faces = np.zeros((max(nf, 1), 3), np.int32)
         cv, cf = C.c_int64(0), C.c_int64(0)
         check(self.lib.tsdf_extract_mesh(self.h, ptr(verts), ptr(norms), ptr(cols), nv, ptr(faces), nf,
                                          C.byref(cv), C.byref(cf)))
@@ -272,6 +325,109 @@ class Volume:
 
     def load_bin(self, path):
         check(self.lib.tsdf_load_bin(self.h, path.encode()))
+
+
+class Group:
+    """One `tsdf_group*`: a whole grid as z-slabs over a device list, ONE process (the C++ host's
+    multi-GPU handle).  Arrays and point / mesh readbacks are those of one whole-grid Volume."""
+
+    def __init__(self, cfg, devices):
+        self.lib = capi.load()
+        self.h = C.c_void_p()
+        devs = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+        check(self.lib.tsdf_group_create(C.byref(cfg), devs, len(devices), C.byref(self.h)))
+        self.cfg, self.n = cfg, len(devices)
+        self._keep = []
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.tsdf_group_destroy(self.h)
+            self.h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    @property
+    def n_voxels(self):
+        return self.cfg.dim_x * self.cfg.dim_y * self.cfg.dim_z
+
+    def peer_access(self):
+        n = C.c_int(0)
+        check(self.lib.tsdf_group_peer_access(self.h, C.byref(n)))
+        return n.value
+
+    def integrate(self, depth, rgb, T_wc, K=None, obs_weight=1.0, sync=True):
+        if not isinstance(depth, (int, np.integer)):
+            depth = np.ascontiguousarray(depth, np.float32)
+        if rgb is not None and not isinstance(rgb, (int, np.integer)):
+            rgb = np.ascontiguousarray(rgb, np.uint8)
+        Kc = None if K is None else f32(K, 9)
+        T = f32(T_wc, 16)
+        self._keep.append((depth, rgb, Kc, T))
+        fn = self.lib.tsdf_group_integrate if sync else self.lib.tsdf_group_integrate_async
+        check(fn(self.h, ptr(depth), ptr(rgb), ptr(Kc), ptr(T), np.float32(obs_weight)))
+        if sync:
+            self._keep.clear()
+
+    def sync(self):
+        check(self.lib.tsdf_group_sync(self.h))
+        self._keep.clear()
+
+    def reset(self):
+        check(self.lib.tsdf_group_reset(self.h))
+
+    def stats(self):
+        s = Stats()
+        check(self.lib.tsdf_group_get_stats(self.h, C.byref(s)))
+        self._keep.clear()
+        return s
+
+    def download(self):
+        n = self.n_voxels
+        t, w = np.empty(n, np.float32), np.empty(n, np.float32)
+        c = np.empty(n, np.float32) if self.cfg.with_color else None
+        check(self.lib.tsdf_group_download(self.h, ptr(t), ptr(w), ptr(c)))
+        return t, w, c
+
+    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, pool=None):
+        n = C.c_int64(0)
+        args = (self.h, pred, np.float32(tsdf_thresh), np.float32(weight_thresh))
+        check(self.lib.tsdf_group_extract_points(*args, None, None, None, 0, C.byref(n)))
+        n = n.value
+        mk = (lambda name, shp, dt: pool.array(name, shp, dt)) if pool is not None else (lambda name, shp, dt: np.zeros(shp, dt))
+        xyz, rgb, idx = mk("xyz", (max(n, 1), 3), np.float32), mk("rgb", (max(n, 1), 3), np.uint8), mk("idx", (max(n, 1),), np.int64)
+        cnt = C.c_int64(0)
+        check(self.lib.tsdf_group_extract_points(*args, ptr(xyz), ptr(rgb), ptr(idx), n, C.byref(cnt)))
+        assert cnt.value == n
+        return xyz[:n], rgb[:n], idx[:n]
+
+    def extract_mesh(self):
+        nv, nf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_group_extract_mesh(self.h, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
+        nv, nf = nv.value, nf.value
+        verts = np.zeros((max(nv, 1), 3), np.float32)
+        norms = np.zeros((max(nv, 1), 3), np.float32)
+        cols = np.zeros((max(nv, 1), 3), np.uint8)
+        faces = np.zeros((max(nf, 1), 3), np.int32)
+        cv, cf = C.c_int64(0), C.c_int64(0)
+        check(self.lib.tsdf_group_extract_mesh(self.h, ptr(verts), ptr(norms), ptr(cols), nv, ptr(faces), nf,
+                                               C.byref(cv), C.byref(cf)))
+        return verts[:nv], faces[:nf], norms[:nv], cols[:nv]
+
+    def release_scratch(self):
+        check(self.lib.tsdf_group_release_scratch(self.h))
+
+    def save_ply(self, path, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9):
+        check(self.lib.tsdf_group_save_ply(self.h, path.encode(), pred, np.float32(tsdf_thresh), np.float32(weight_thresh)))
+
+    def save_bin(self, path):
+        check(self.lib.tsdf_group_save_bin(self.h, path.encode()))
+
+    def save_mesh_ply(self, path):
+        check(self.lib.tsdf_group_save_mesh_ply(self.h, path.encode()))
 
 
 class Batch:

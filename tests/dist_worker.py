@@ -33,19 +33,25 @@ def main():
         sv = pkg.dist.ShardedVolume(cfg, rank, world, local, uid)
         zr = (sv.vol.cfg.z_begin, sv.vol.cfg.z_end)
         assert zr == pkg.slab_range(dims[2], world, rank)
-        for d, rgb, T in frames:
-            if rank == 0:   # only the root holds the images; poses are control-plane metadata
+        # 10 distributed frames (the 6-slot ring wraps) with a plain single-handle integrate of a
+        # frame every rank holds in between: the distribution has its own ring and sequence number
+        seq = [frames[i % 4] for i in range(10)]
+        for i, (d, rgb, T) in enumerate(seq):
+            if i == 4:
+                sv.vol.integrate(d, rgb if color else None, T, sync=False)
+            elif rank == 0:   # only the root holds the images; poses are control-plane metadata
                 sv.integrate_bcast(d, rgb if color else None, T)
             else:
                 sv.integrate_bcast(None, None, T)
         sv.sync()
+        frames_run = seq
         want_nccl = os.environ.get("TSDF_B200_BCAST") == "nccl"
         assert not (want_nccl and sv.peer_pull())
         mode = "peer-pull" if sv.peer_pull() else "nccl"
         gt, gw, gc = sv.vol.download()
         p = o.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, sem, zr)
         t, w, c = o.new_volume(p, color)
-        for d, rgb, T in frames:
+        for d, rgb, T in frames_run:
             o.integrate(p, T.reshape(16), d, o.pack_color(rgb) if color else None, 1.0, t, w, c)
         assert w.max() >= 2, f"rank {rank}: slab {zr} saw nothing (scene does not reach it)"
         assert np.array_equal(gw, w), f"rank {rank}: weights differ"
@@ -53,16 +59,25 @@ def main():
         if color:
             assert np.array_equal(gc, c), f"rank {rank}: colour differs"
         xyz, rgbp, idx, n = sv.gather_points()
+        pool = pkg.PinnedPool()
+        xyz2, rgb2, idx2, n2 = sv.gather_points(pool=pool)      # straight into page-locked outputs
+        mesh = sv.gather_mesh() if color else None              # whole-grid mesh at the root
         if rank == 0:
             pw = o.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, sem)
             tw, ww, cw = o.new_volume(pw, color)
-            for d, rgb, T in frames:
+            for d, rgb, T in frames_run:
                 o.integrate(pw, T.reshape(16), d, o.pack_color(rgb) if color else None, 1.0, tw, ww, cw)
             oxyz, orgb, oidx = o.extract(pw, tw, ww, cw)
-            assert n == len(oidx) and np.array_equal(idx, oidx), "gathered index set differs"
+            assert n == len(oidx) > 1000 and np.array_equal(idx, oidx), "gathered index set differs"
             assert np.array_equal(xyz.view(np.uint32), oxyz.view(np.uint32))
+            assert n2 == n and np.array_equal(idx2, oidx) and np.array_equal(xyz2.view(np.uint32), oxyz.view(np.uint32))
             if color:
-                assert np.array_equal(rgbp, orgb)
+                assert np.array_equal(rgbp, orgb) and np.array_equal(rgb2, orgb)
+                om = o.mesh(pw, tw, cw)
+                assert len(om[1]) > 1000 and np.array_equal(mesh[1], om[1]), "gathered mesh faces differ"
+                assert np.array_equal(mesh[0].view(np.uint32), om[0].view(np.uint32)) and np.array_equal(mesh[3], om[3])
+                assert np.array_equal(mesh[2].view(np.uint32), om[2].view(np.uint32))
+        pool.close()
         sv.close()
         dist.barrier()
     # ---- instance volumes: sharded by instance, no data-path collective ----

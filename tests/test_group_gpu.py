@@ -1,0 +1,134 @@
+"""Single-process multi-GPU handle (tsdf_group, VERDICT r1 missing #3/#4): a whole grid as z-slabs
+over a device list behind ONE handle, against the whole-grid oracle — arrays, N_written, point
+readback (merged on the device to ascending reference index) and the mesh of the sharded volume
+(assembled on the root device, so it must equal the single-volume mesh bit for bit, order included).
+A device may be listed several times, which is how this runs on the driver's 1-GPU box; with >= 2
+GPUs the same tests run across devices, with and without peer access."""
+import numpy as np
+import pytest
+
+from conftest import bits
+from oracle.oracle import SEM_TSDFCU, SEM_FUSIONPY, PRED_NONZERO, PRED_ABS_LT
+
+pytestmark = pytest.mark.gpu
+
+
+def device_lists(pkg):
+    out = [[0, 0, 0]]
+    n = pkg.device_count()
+    if n >= 2:
+        out += [[0, 1], [1, 0, 1]]
+    if n >= 4:
+        out += [[0, 1, 2, 3]]
+    return out
+
+
+def run_oracle(oracle, dims, vs, origin, frames, sem, color, md):
+    p = oracle.params(dims, vs, np.float32(vs) * np.float32(5), origin, frames[0][0].shape,
+                      np.array([535.4, 0, 320.1, 0, 539.2, 247.6, 0, 0, 1], np.float32), md, sem)
+    t, w, c = oracle.new_volume(p, color)
+    n = 0
+    for d, rgb, T in frames:
+        n += oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb) if color else None, 1.0, t, w, c)
+    return p, t, w, c, n
+
+
+@pytest.mark.parametrize("sem,color", [(SEM_FUSIONPY, True), (SEM_TSDFCU, False)])
+@pytest.mark.parametrize("no_peer", [False, True])
+def test_group_equals_whole_grid_oracle(pkg, oracle, synth, sem, color, no_peer, monkeypatch, tmp_path):
+    dims, vs, md = (56, 40, 96), 0.04, 40.0
+    origin, frames = synth.s_corridor(dims, vs, n_frames=8, seed=5)   # 8 frames: the 6-slot ring wraps
+    p, t, w, c, n_o = run_oracle(oracle, dims, vs, origin, frames, sem, color, md)
+    if no_peer:
+        monkeypatch.setenv("TSDF_B200_GROUP_NO_PEER", "1")
+    for devs in device_lists(pkg):
+        if no_peer and len(set(devs)) == 1:
+            continue   # same device: nothing to stage
+        cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=md)
+        with pkg.Group(cfg, devs) as g:
+            if no_peer:
+                assert g.peer_access() == sum(1 for x in devs[1:] if x == devs[0])
+            for i, (d, rgb, T) in enumerate(frames):
+                g.integrate(d, rgb if color else None, T, sync=(i % 3 == 2))
+            g.sync()
+            gt, gw, gc = g.download()
+            assert np.array_equal(gw, w), f"{devs}: weights differ"
+            assert np.array_equal(bits(gt), bits(t)), f"{devs}: tsdf differs"
+            if color:
+                assert np.array_equal(gc, c)
+            for pred, tt, wt in ((PRED_NONZERO, 1.2, 0.9), (PRED_ABS_LT, 0.6, 1.5)):
+                gx, gr, gi = g.extract_points(pred, tt, wt)
+                ox, orr, oi = oracle.extract(p, t, w, c, pred, tt, wt)
+                assert len(oi) > 500 and np.array_equal(gi, oi) and np.array_equal(bits(gx), bits(ox))
+                if color:
+                    assert np.array_equal(gr, orr)
+            pool = pkg.PinnedPool()
+            gx, gr, gi = g.extract_points(PRED_NONZERO, 1.2, 0.9, pool=pool)   # straight into pinned memory
+            ox, orr, oi = oracle.extract(p, t, w, c, PRED_NONZERO, 1.2, 0.9)
+            assert np.array_equal(gi, oi) and np.array_equal(bits(gx), bits(ox))
+            pool.close()
+            if sem == SEM_FUSIONPY:
+                gm, om = g.extract_mesh(), oracle.mesh(p, t, c)
+                assert len(om[1]) > 1000 and np.array_equal(gm[1], om[1]) and np.array_equal(bits(gm[0]), bits(om[0]))
+                assert np.array_equal(bits(gm[2]), bits(om[2])) and np.array_equal(gm[3], om[3])
+                # one more frame: the cached assembly must be refreshed
+                d, rgb, T = frames[0]
+                g.integrate(d, rgb, T)
+                oracle.integrate(p, T.reshape(16), d, oracle.pack_color(rgb), 1.0, t, w, c)
+                gm, om = g.extract_mesh(), oracle.mesh(p, t, c)
+                assert np.array_equal(gm[1], om[1]) and np.array_equal(bits(gm[0]), bits(om[0])) and np.array_equal(gm[3], om[3])
+                g.release_scratch()
+            else:
+                pa, pb = str(tmp_path / "g.ply"), str(tmp_path / "o.ply")
+                g.save_ply(pa)
+                assert oracle.save_ply(pb, p, t, w)
+                assert open(pa, "rb").read() == open(pb, "rb").read()
+                ba, bb = str(tmp_path / "g.bin"), str(tmp_path / "o.bin")
+                g.save_bin(ba)
+                assert oracle.save_bin(bb, p, t)
+                assert open(ba, "rb").read() == open(bb, "rb").read()
+
+
+def test_group_stats_and_reset(pkg, oracle, synth):
+    dims, vs = (48, 40, 64), 0.04
+    origin, frames = synth.s_corridor(dims, vs, n_frames=2, seed=9)
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True, max_depth=40.0)
+    p, t, w, c, _ = run_oracle(oracle, dims, vs, origin, frames[:1], SEM_FUSIONPY, True, 40.0)
+    with pkg.Group(cfg, [0, 0]) as g:
+        d, rgb, T = frames[0]
+        g.integrate(d, rgb, T)
+        st = g.stats()
+        assert st.voxels_written == int((w > 0).sum()) and st.voxels_visited == int(np.prod(dims))
+        g.reset()
+        gt, gw, gc = g.download()
+        assert (gt == 1).all() and (gw == 0).all() and (gc == 0).all()
+        with pytest.raises(pkg.TsdfError):
+            g.integrate(d, rgb, T, obs_weight=0.0)
+    bad = pkg.make_config(dims, vs, origin, z_range=(0, 32))
+    with pytest.raises(pkg.TsdfError):
+        pkg.Group(bad, [0, 0])
+
+
+def test_single_volume_readback_into_pinned_and_pageable(pkg, oracle, synth):
+    """The two host destinations of the readback calls (straight D2H into tsdf_host_alloc memory;
+    pinned staging ring for pageable memory, > one 4 MB chunk) return the same bytes."""
+    dims, vs = (160, 128, 160), 0.02
+    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=21)
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+    with pkg.Volume(cfg) as vol:
+        for d, rgb, T in frames:
+            vol.integrate(d, rgb, T, sync=False)
+        a = vol.extract_points(PRED_NONZERO, 1.2, 0.9)
+        assert a[0].nbytes > 5 * (4 << 20)          # several staging chunks
+        pool = pkg.PinnedPool()
+        b = vol.extract_points(PRED_NONZERO, 1.2, 0.9, pool=pool)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y)
+        t, w, c = vol.download()
+        p = oracle.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, cfg.max_depth, SEM_FUSIONPY)
+        ox, orr, oi = oracle.extract(p, t, w, c)
+        assert np.array_equal(a[2], oi) and np.array_equal(bits(a[0]), bits(ox)) and np.array_equal(a[1], orr)
+        ma, mb = vol.extract_mesh(), vol.extract_mesh(pool=pool)
+        for x, y in zip(ma, mb):
+            assert np.array_equal(x, y)
+        pool.close()
