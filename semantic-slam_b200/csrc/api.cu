@@ -164,6 +164,9 @@ static void free_vol(tsdf_vol* v) {
   DeviceGuard g(v->cfg.device);
   if (v->s_compute) cudaStreamSynchronize(v->s_compute);
   if (v->s_copy) cudaStreamSynchronize(v->s_copy);
+  if (v->s_aux) cudaStreamSynchronize(v->s_aux);
+  for (cudaEvent_t e : v->ev_int_done) if (e) cudaEventDestroy(e);
+  for (cudaEvent_t e : v->ev_pub_done) if (e) cudaEventDestroy(e);
   auto free_slot = [](FrameSlot& s) {
     if (s.h_pinned) cudaFreeHost(s.h_pinned);
     if (s.d_raw) cudaFree(s.d_raw);
@@ -182,6 +185,7 @@ static void free_vol(tsdf_vol* v) {
   for (cudaEvent_t e : v->tev) cudaEventDestroy(e);
   if (v->s_compute) cudaStreamDestroy(v->s_compute);
   if (v->s_copy) cudaStreamDestroy(v->s_copy);
+  if (v->s_aux) cudaStreamDestroy(v->s_aux);
   delete v;
 }
 
@@ -209,8 +213,8 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaMalloc(&v->d_tsdf, bytes));
   CU_CHECK(cudaMalloc(&v->d_weight, bytes));
   if (c.with_color) CU_CHECK(cudaMalloc(&v->d_color, bytes));
-  CU_CHECK(cudaMalloc(&v->d_written, sizeof(unsigned long long)));
-  CU_CHECK(cudaMemset(v->d_written, 0, sizeof(unsigned long long)));
+  CU_CHECK(cudaMalloc(&v->d_written, sizeof(unsigned long long) * kWrittenRing));
+  CU_CHECK(cudaMemset(v->d_written, 0, sizeof(unsigned long long) * kWrittenRing));
   CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
   CU_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&v->hd_written), v->h_written, 0));
   *v->h_written = 0;
@@ -222,6 +226,11 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
   CU_CHECK(cudaStreamCreateWithPriority(&v->s_compute, cudaStreamNonBlocking, prio_least));
   CU_CHECK(cudaStreamCreateWithPriority(&v->s_copy, cudaStreamNonBlocking, prio_greatest));
+  CU_CHECK(cudaStreamCreateWithPriority(&v->s_aux, cudaStreamNonBlocking, prio_greatest));
+  for (int i = 0; i < kWrittenRing; ++i) {
+    CU_CHECK(cudaEventCreateWithFlags(&v->ev_int_done[i], cudaEventDisableTiming));
+    CU_CHECK(cudaEventCreateWithFlags(&v->ev_pub_done[i], cudaEventDisableTiming));
+  }
   CU_CHECK(cudaEventCreate(&v->ev_k0));
   CU_CHECK(cudaEventCreate(&v->ev_k1));
   CU_CHECK(cudaEventCreate(&v->ev_u0));
@@ -453,7 +462,7 @@ int check_obs_weight(float obs_weight) {
 }
 
 // Launches the integrate kernel for nf prepared frames and records stats/events.
-int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color) {
+int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color, bool accumulate) {
   if (v) ++v->epoch;  // voxel arrays change: invalidates the cached extraction mark pass
   for (int i = 0; i < nf; ++i) CU_CHECK(cudaStreamWaitEvent(v->s_compute, slots[i]->uploaded, 0));
   cudaEvent_t k0 = v->ev_k0, k1 = v->ev_k1;
@@ -470,21 +479,30 @@ int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool
     v->kev_used += 2;
   }
   v->wmode_ok = account_weights(v, fp, nf);
+  const int wi = (int)(v->lseq % kWrittenRing);
+  // this launch adds into counter wi: the publish of the launch that last used it must have re-armed it
+  if (v->lseq >= (uint64_t)kWrittenRing) CU_CHECK(cudaStreamWaitEvent(v->s_compute, v->ev_pub_done[wi], 0));
   CU_CHECK(cudaEventRecord(k0, v->s_compute));
   trace_mark(v, 2, v->s_compute);
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;
   CU_CHECK(cudaEventRecord(k1, v->s_compute));
   trace_mark(v, 3, v->s_compute);
-  // single-frame submissions: the publish kernel also zeroes the consumed slot's max-depth tiles, so
-  // the next prep into it runs without a memset (handles under A/B tooling keep the frame intact:
-  // tsdf_bench_kernel re-launches on it)
-  rc = launch_publish(v, false, v->s_compute, (nf == 1 && !v->dev_hold) ? slots[0]->d_frame : nullptr);
+  // publish on the aux stream, behind this launch: N_written -> pinned mirror (the step's 8-byte
+  // device->host result), counter re-armed; single-frame submissions also zero the consumed slot's
+  // max-depth tiles there, so the next prep into it runs without a memset (handles under A/B tooling
+  // keep the frame intact: tsdf_bench_kernel re-launches on it).  The compute stream carries
+  // integrate launches only.
+  CU_CHECK(cudaEventRecord(v->ev_int_done[wi], v->s_compute));
+  CU_CHECK(cudaStreamWaitEvent(v->s_aux, v->ev_int_done[wi], 0));
+  rc = launch_publish(v, accumulate, v->s_aux, (nf == 1 && !v->dev_hold) ? slots[0]->d_frame : nullptr);
   if (rc) return rc;
+  CU_CHECK(cudaEventRecord(v->ev_pub_done[wi], v->s_aux));
   for (int i = 0; i < nf; ++i) {
-    CU_CHECK(cudaEventRecord(slots[i]->consumed, v->s_compute));
+    CU_CHECK(cudaEventRecord(slots[i]->consumed, v->s_aux));
     slots[i]->in_flight = true;
   }
+  ++v->lseq;
   memcpy(v->last_frames, fp, sizeof(FrameP) * nf);
   v->last_nf = nf;
   v->last_color = color;
@@ -539,24 +557,28 @@ extern "C" int tsdf_integrate_multi_async(tsdf_vol* v, int k, const float* depth
   DeviceGuard g(v->cfg.device);
   const bool color = v->d_color != nullptr && rgb != nullptr;
   const size_t px = frame_pixels(v->cfg);
+  // Frames are staged and submitted two at a time, in frame order: two consecutive dense frames share
+  // one pass over the volume (k_integrate2, launch_integrate), and the host stages pair i + 1 (copy
+  // into the pinned ring, H2D, prep) while the GPU integrates pair i.  (Round 1 staged groups of up to
+  // 8 frames on the caller's thread before the group's first launch: 5.5 ms per frame at k = 8.)
   int done = 0;
-  while (done < k) {  // greedy split into fused launches of 8/4/2/1 frames, in frame order
-    int nf = (k - done >= 8) ? 8 : (k - done >= 4) ? 4 : (k - done >= 2) ? 2 : 1;
-    FrameSlot* slots[kMaxFusedFrames];
-    FrameP fp[kMaxFusedFrames];
-    const int group = (int)(v->mseq % 2);
+  while (done < k) {
+    const int nf = (k - done >= 2) ? 2 : 1;
+    FrameSlot* slots[2];
+    FrameP fp[2];
     for (int i = 0; i < nf; ++i) {
       const int f = done + i;
-      int rc = stage_frame(v, 3 + group * kMaxFusedFrames + i, depth + (size_t)f * px, TSDF_DEPTH_F32,
-                           1.0f, 1, 1, rgb ? rgb + (size_t)f * px * 3 : nullptr, color, &slots[i]);
+      const int si = 3 + (int)(v->mseq++ % (2 * kMaxFusedFrames));
+      int rc = stage_frame(v, si, depth + (size_t)f * px, TSDF_DEPTH_F32, 1.0f, 1, 1,
+                           rgb ? rgb + (size_t)f * px * 3 : nullptr, color, &slots[i]);
       if (rc) return rc;
       make_frame_params(v, K, T_wc + 16 * f, obs_weight, slots[i]->d_frame, &fp[i]);
     }
-    ++v->mseq;
-    int rc = submit_frames(v, slots, fp, nf, color);
+    int rc = submit_frames(v, slots, fp, nf, color, /*accumulate=*/done > 0);
     if (rc) return rc;
     done += nf;
   }
+  v->last_frames_in_launch = k;
   return TSDF_OK;
 }
 
@@ -565,6 +587,7 @@ extern "C" int tsdf_sync(tsdf_vol* v) {
   DeviceGuard g(v->cfg.device);
   CU_CHECK(cudaStreamSynchronize(v->s_copy));
   CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  CU_CHECK(cudaStreamSynchronize(v->s_aux));
   for (FrameSlot& s : v->slot) s.in_flight = false;
   for (FrameSlot& s : v->bslot) s.in_flight = false;
   v->last_written = (int64_t)*v->h_written;
@@ -623,6 +646,7 @@ extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
   rc = launch_publish(v, false, v->s_compute);
   if (rc) return rc;
   CU_CHECK(cudaStreamSynchronize(v->s_compute));
+  ++v->lseq;
   float ms = 0;
   CU_CHECK(cudaEventElapsedTime(&ms, v->ev_k0, v->ev_k1));
   *avg_ms = ms / iters;
@@ -1190,6 +1214,8 @@ extern "C" int tsdf_timer_stop(tsdf_vol* v, float* ms) {
   REQUIRE(v && ms, "null argument");
   DeviceGuard g(v->cfg.device);
   CU_CHECK(cudaStreamSynchronize(v->s_copy));   // everything staged so far is enqueued/finished
+  if (v->lseq > 0)   // ... and the last step's result has reached host memory
+    CU_CHECK(cudaStreamWaitEvent(v->s_compute, v->ev_pub_done[(v->lseq - 1) % kWrittenRing], 0));
   CU_CHECK(cudaEventRecord(v->ev_t1, v->s_compute));
   CU_CHECK(cudaEventSynchronize(v->ev_t1));
   CU_CHECK(cudaEventElapsedTime(ms, v->ev_t0, v->ev_t1));

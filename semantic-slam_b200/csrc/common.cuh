@@ -119,6 +119,7 @@ struct FrameSlot {
   bool in_flight = false;
 };
 
+constexpr int kWrittenRing = 4;
 constexpr int kBcastSlots = 6;  // frame ring of the distributed (multi-GPU) integrate calls
 
 struct tsdf_comm;
@@ -132,7 +133,15 @@ struct tsdf_vol {
   float* d_tsdf = nullptr;
   float* d_weight = nullptr;
   float* d_color = nullptr;
+  // exact N_written: a ring of kWrittenRing device counters, launch n adds into counter n % ring; the
+  // publish kernel of launch n runs on the AUX stream behind it (moves the count to the pinned mirror,
+  // re-arms the counter, zeroes the consumed slot's max-depth tiles), so consecutive integrate
+  // launches follow each other on the compute stream with nothing between them
   unsigned long long* d_written = nullptr;
+  uint64_t lseq = 0;                        // integrate launch groups submitted
+  cudaStream_t s_aux = nullptr;
+  cudaEvent_t ev_int_done[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_pub_done[4] = {nullptr, nullptr, nullptr, nullptr};
   unsigned long long* h_written = nullptr;  // pinned mirror (mapped: the kernel writes it)
   unsigned long long* hd_written = nullptr; // its device address
   cudaStream_t s_compute = nullptr;
@@ -236,7 +245,7 @@ struct PrepSync {
 int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cudaStream_t st);
 // N_written -> pinned mirror, counter = 0; optionally zeroes the tail (max-depth tiles) of the frame
 // slot the launch before it consumed, so that the next prep into that slot needs no memset
-int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear = nullptr);
+int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear = nullptr);  // counter lseq % ring
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st);
 void fill_grid_params(const tsdf_vol* v, bool color, GridP* g);
@@ -279,7 +288,7 @@ int ensure_bcast_slot(tsdf_vol* v, int index);
 int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
                     const void** d_out, bool into_slot);
 // waits for the slots' uploads, launches the integrate kernel(s) + publish, records the events
-int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color);
+int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool color, bool accumulate = false);
 int compose_cam2base(const tsdf_vol* v, const float* T_wc, float* c2b);
 int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, float obs_weight,
                       const void* d_frame, FrameP* out);

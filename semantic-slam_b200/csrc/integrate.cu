@@ -678,6 +678,124 @@ k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_bl
   integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE, CULL>(P, nullptr, tab, tpr_log2, rows_per_block, flags);
 }
 
+// ---------------------------------------------------------------------------------------
+// Two frames per volume pass (the off-line keyframe replay of
+// examples/label_instance_rgbd.cpp:79-110 hands the library many frames per volume).  Dense frames
+// only (the host checks that the slab projects inside both images, as for CULL = 0).  The voxel
+// state of a run is loaded ONCE at the top of the row — no validity to wait for on dense frames, and
+// the whole probe of frame 0 stands between the loads and their first use — then updated by frame 0
+// and by frame 1 in registers, in frame order (bit-identical to two passes), and stored once:
+// 12 B per update instead of 24.  Unlike the generic NF-frame form of integrate_body (measured
+// slower than NF passes: it keeps every frame's Hit live across the volume loads, 118-244
+// registers), a frame's probe results die in its own update, so the live set is one frame's.
+// ---------------------------------------------------------------------------------------
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+__global__ void __launch_bounds__(kThreads, 3)
+k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_block, int flags) {
+  constexpr int NT = ZFAST ? 1 : 2;
+  constexpr int VEC = 4;
+  __shared__ float4 tab[kMaxRowsPerBlock * 2 * NT];
+  const GridP& g = P.g;
+  const int pf = flags & 3;
+  const int n_rows = g.n_mid * g.n_slow;
+  const int row0 = blockIdx.x * rows_per_block;
+  if (row0 >= n_rows) return;
+  if (P.f[0].skip != nullptr && *reinterpret_cast<const volatile int*>(P.f[0].skip) != 0) return;
+  for (int lr = threadIdx.x; lr < rows_per_block; lr += kThreads) {
+    const int r = row0 + lr;
+    if (r < n_rows) {
+      const int slow = r / g.n_mid, mid = r - slow * g.n_mid;
+#pragma unroll
+      for (int f = 0; f < 2; ++f) {
+        float4 e0, e1;
+        row_terms<ZFAST>(g, P.f[f].c, slow, mid, e0, e1);
+        tab[(lr * 2 + f) * NT] = e0;
+        if constexpr (!ZFAST) tab[(lr * 2 + f) * NT + 1] = e1;
+      }
+    }
+  }
+  __syncthreads();
+  const int tpr = 1 << tpr_log2;
+  const int tf = threadIdx.x & (tpr - 1);
+  const int tr = threadIdx.x >> tpr_log2;
+  const int rp = kThreads >> tpr_log2;
+  const int f0 = (blockIdx.y * tpr + tf) * VEC;
+  const bool live = f0 < g.n_fast;
+  float q[2][3][VEC];   // fast-axis products of both frames (registers)
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) {
+    const float bfj = fast_coord<ZFAST>(g, f0 + j);
+#pragma unroll
+    for (int f = 0; f < 2; ++f) fast_terms<ZFAST>(P.f[f].c, bfj, q[f][0][j], q[f][1][j], q[f][2][j]);
+  }
+  unsigned int n_written = 0;
+  for (int lr = tr; live && lr < rows_per_block; lr += rp) {
+    const int r = row0 + lr;
+    if (r >= n_rows) break;
+    const int64_t base = (int64_t)r * g.n_fast + f0;
+    if (pf && lr + rp < rows_per_block && r + rp < n_rows) {
+      const int64_t pb = (int64_t)(r + rp) * g.n_fast + f0;
+      prefetch_line<true>(g.tsdf + pb, 1);
+      prefetch_line<true>(g.weight + pb, 1);
+      if constexpr (COLOR) prefetch_line<true>(g.color + pb, 1);
+    }
+    float t[VEC], w[VEC], col[VEC];
+    load_vec<VEC>(g.tsdf + base, t);
+    load_vec<VEC>(g.weight + base, w);
+    if constexpr (COLOR) load_vec<VEC>(g.color + base, col);
+    else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) col[j] = 0.0f;
+    }
+    bool any = false;
+#pragma unroll
+    for (int f = 0; f < 2; ++f) {
+      const float4 ea = tab[(lr * 2 + f) * NT];
+      float4 eb = ea;
+      if constexpr (!ZFAST) eb = tab[(lr * 2 + f) * NT + 1];
+      float camx[VEC], camy[VEC], camz[VEC];
+      bool odd = false;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        cam_coords<ZFAST>(ea, eb, q[f][0][j], q[f][1][j], q[f][2][j], camx[j], camy[j], camz[j]);
+        odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
+      }
+      Hit hit[VEC];
+      if (__builtin_expect(odd, 0)) {
+#pragma unroll
+        for (int j = 0; j < VEC; ++j)
+          hit[j] = probe_literal_cold<COLOR, LE_TRUNC, false>(P.f[f].img, P.f[f].fx, P.f[f].cx, P.f[f].fy, P.f[f].cy,
+                                                              g.trunc, g.W, g.H, nullptr, camx[j], camy[j], camz[j]);
+      } else {
+        Proj pr[VEC];
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true>(P.f[f], g, camx[j], camy[j], camz[j]);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false>(P.f[f], g, nullptr, pr[j], camz[j]);
+      }
+      const float obs = P.f[f].obs_weight;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        float nt = t[j], nw = w[j], nc = col[j];
+        update_voxel<COLOR, MATH_EXACT, WMODE>(nt, nw, nc, hit[j], obs);
+        const bool ok = hit[j].ok;
+        t[j] = ok ? nt : t[j];
+        w[j] = ok ? nw : w[j];
+        col[j] = ok ? nc : col[j];
+        n_written += ok ? 1u : 0u;
+        any = any || ok;
+      }
+    }
+    if (any) {
+      store_vec<VEC>(g.tsdf + base, t);
+      store_vec<VEC>(g.weight + base, w);
+      if constexpr (COLOR) store_vec<VEC>(g.color + base, col);
+    }
+  }
+  for (int o = 16; o > 0; o >>= 1) n_written += __shfl_down_sync(0xffffffffu, n_written, o);
+  if ((threadIdx.x & 31) == 0 && n_written) atomicAdd(g.written, (unsigned long long)n_written);
+}
+
 // Batched per-instance volumes (config 5): blockIdx.z selects a descriptor {grid, pose, mask}
 // from global memory; one launch covers every active instance.
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int VEC, int WMODE>
@@ -793,6 +911,35 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   return TSDF_OK;
 }
 
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
+  LaunchP<2> P;
+  P.g = g;
+  P.f[0] = frames[0];
+  P.f[1] = frames[1];
+  Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, 4, 1, o.rows_mult, kThreads);
+  if (o.balance) {
+    static const int occ = [] {
+      int n = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE>, kThreads, 0) != cudaSuccess) n = 0;
+      return n;
+    }();
+    balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
+  }
+  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, o.prefetch ? 1 : 0);
+  CU_LAUNCHED();
+  return TSDF_OK;
+}
+
+int launch_pair(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, const LaunchOpts& o, cudaStream_t st) {
+  if (zfast) {
+    if (color) return wmode == 1 ? launch_pair_t<true, true, false, 1>(g, fr, o, st) : launch_pair_t<true, true, false, 0>(g, fr, o, st);
+    return launch_pair_t<true, false, false, 0>(g, fr, o, st);
+  }
+  if (color) return wmode == 1 ? launch_pair_t<false, true, true, 1>(g, fr, o, st) : launch_pair_t<false, true, true, 0>(g, fr, o, st);
+  return launch_pair_t<false, false, true, 0>(g, fr, o, st);
+}
+
 // layout (and with it the truncation compare) x colour x integer-weight mode, for one NF/VEC/MATH
 template <int NF, int VEC, int MATH>
 int launch_sem(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, const LaunchOpts& o, cudaStream_t st) {
@@ -827,7 +974,7 @@ void fill_grid_params(const tsdf_vol* v, bool color, GridP* g) {
   g->h_lim = (float)c.im_h - 0.5f;
   g->W = c.im_w; g->H = c.im_h;
   g->tsdf = v->d_tsdf; g->weight = v->d_weight; g->color = color ? v->d_color : nullptr;
-  g->written = v->d_written;
+  g->written = v->d_written + (v->lseq % kWrittenRing);
 }
 
 // Host-side, double precision: do all 8 corner voxels of the slab project at least one pixel
@@ -857,7 +1004,7 @@ static bool slab_inside_every_frustum(const GridP& g, const FrameP* fr, int nf) 
 int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear) {
   int* tail = d_frame_to_clear ? reinterpret_cast<int*>(frame_dmax_ptr(d_frame_to_clear, frame_pixels(v->cfg))) : nullptr;
   const int words = tail ? (int)(frame_tail_bytes(v->cfg.im_h, v->cfg.im_w) / 4) : 0;
-  k_publish<<<1, tail ? 256 : 32, 0, st>>>(v->d_written, v->hd_written, accumulate ? 1 : 0, tail, words);
+  k_publish<<<1, tail ? 256 : 32, 0, st>>>(v->d_written + (v->lseq % kWrittenRing), v->hd_written, accumulate ? 1 : 0, tail, words);
   CU_LAUNCHED();
   return TSDF_OK;
 }
@@ -886,20 +1033,30 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   // (sparse kernel: 256-row blocks, i.e. x32 with a 256-entry row table, measured no better than
   // x16 once the block test was in place — S-kitti 0.134 vs 0.130 ms, S-real equal — so x16 stays)
   const int wmode = (color && v->wmode_ok) ? 1 : 0;
-  // One launch per frame, in frame order.  A fused k-frame pass (voxel state read once, updated k
-  // times in registers, written once) was built twice — unrolled over the frames (118-244
-  // registers) and as a non-unrolled frame loop (76 registers) — and measured on the 1024^3
-  // bench volume: 4.1-5.7 ms per frame against 3.9 ms for single launches.  The single-frame
-  // kernel already issues at ~76 % of peak next to its HBM stream, so a fused pass is bound by
-  // the per-voxel arithmetic, not by the traffic it saves, and pays for its longer live ranges
-  // with occupancy.  NF stays a template parameter of the kernel; only NF = 1 is instantiated.
-  for (int i = 0; i < nf; ++i) {
+  // Frames go in frame order.  Two consecutive DENSE frames (the slab projects inside both images, so
+  // the branch-free kernel applies) share one pass over the volume (k_integrate2: voxel state read
+  // and written once for two updates); anything else is one launch per frame.  The generic NF-frame
+  // form of integrate_body (every frame's probe results live across the volume loads) was measured
+  // slower than NF passes in round 1 — 4.1-5.7 ms per frame against 3.9 — and is not instantiated.
+  const bool pairs_ok = vec4 && !literal && (v->variant & (1 << 14)) == 0 && o.kernel != 2;
+  for (int i = 0; i < nf;) {
     int rc;
-    if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o, st)
-                           : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o, st);
-    else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o, st)
-                           : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o, st);
+    // (variant bit 6 forces the dense kernels whatever the geometry, bit 7 the sparse one, bit 14 no pairs)
+    if (pairs_ok && i + 1 < nf && !(v->variant & 128) &&
+        ((v->variant & 64) || slab_inside_every_frustum(g, frames + i, 2))) {
+      rc = launch_pair(v->zfast, color, wmode, g, frames + i, o, st);
+      if (rc) return rc;
+      i += 2;
+      continue;
+    }
+    LaunchOpts o1 = o;
+    if (!(v->variant & (64 | 128 | 1024))) o1.kernel = slab_inside_every_frustum(g, frames + i, 1) ? 0 : 1;
+    if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st)
+                           : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st);
+    else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o1, st)
+                           : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o1, st);
     if (rc) return rc;
+    ++i;
   }
   return TSDF_OK;
 }

@@ -38,13 +38,14 @@ def run_oracle(oracle, dims, vs, origin, frames, sem, color, md):
 def test_group_equals_whole_grid_oracle(pkg, oracle, synth, sem, color, no_peer, monkeypatch, tmp_path):
     dims, vs, md = (56, 40, 96), 0.04, 40.0
     origin, frames = synth.s_corridor(dims, vs, n_frames=8, seed=5)   # 8 frames: the 6-slot ring wraps
-    p, t, w, c, n_o = run_oracle(oracle, dims, vs, origin, frames, sem, color, md)
+    p, t0, w0, c0, n_o = run_oracle(oracle, dims, vs, origin, frames, sem, color, md)
     if no_peer:
         monkeypatch.setenv("TSDF_B200_GROUP_NO_PEER", "1")
     for devs in device_lists(pkg):
         if no_peer and len(set(devs)) == 1:
             continue   # same device: nothing to stage
         cfg = pkg.make_config(dims, vs, origin, semantics=sem, with_color=color, max_depth=md)
+        t, w, c = t0.copy(), w0.copy(), (c0.copy() if color else None)   # (the mesh leg integrates one more frame)
         with pkg.Group(cfg, devs) as g:
             if no_peer:
                 assert g.peer_access() == sum(1 for x in devs[1:] if x == devs[0])
