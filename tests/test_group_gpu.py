@@ -113,8 +113,8 @@ def test_group_stats_and_reset(pkg, oracle, synth):
 def test_single_volume_readback_into_pinned_and_pageable(pkg, oracle, synth):
     """The two host destinations of the readback calls (straight D2H into tsdf_host_alloc memory;
     pinned staging ring for pageable memory, > one 4 MB chunk) return the same bytes."""
-    dims, vs = (160, 128, 160), 0.02
-    origin, frames = synth.s_real(dims, vs, n_frames=3, seed=21)
+    dims, vs = (128, 128, 128), 0.016
+    origin, frames = synth.s_full(dims, vs, n_frames=3, sphere=True)    # ~2 M written voxels
     cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
     with pkg.Volume(cfg) as vol:
         for d, rgb, T in frames:
