@@ -9,6 +9,8 @@
 #include <algorithm>
 #include <limits>
 
+#include <cuda.h>   // CUtensorMap types only: the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
+
 #include "common.cuh"
 
 // ---- errors ------------------------------------------------------------------------------
@@ -288,6 +290,33 @@ extern "C" int tsdf_get_config(const tsdf_vol* v, tsdf_config* cfg) {
 // compute stream by events, so the upload of frame i+1 overlaps the integrate of frame i.
 // (The reference does two blocking cudaMemcpy from pageable memory per frame per object,
 // src/tsdf.cu:161-162.)
+// Tensor map of a prepared colour frame for the staged-tile variant of the sparse kernel
+// (integrate.cu, `Stage`): the float4 image as a 2-D [H][4W] fp32 tensor, box = 64 x 32 pixels.
+static bool encode_frame_tmap(const tsdf_vol* v, FrameSlot& s) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess) { cudaGetLastError(); p = nullptr; }
+    return reinterpret_cast<EncodeFn>(p);
+  }();
+  const int H = v->cfg.im_h, W = v->cfg.im_w;
+  if (!fn || !v->d_color || W < 64 || H < 32) return false;
+  static_assert(sizeof(CUtensorMap) == 128, "tensor map size");
+  const cuuint64_t gdim[2] = {(cuuint64_t)W * 4, (cuuint64_t)H};
+  const cuuint64_t gstride[1] = {(cuuint64_t)W * 16};
+  const cuuint32_t box[2] = {256, 32}, estr[2] = {1, 1};
+  CUtensorMap tm;
+  if (fn(&tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, s.d_frame, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+         CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+    return false;
+  memcpy(s.tmap, &tm, 128);
+  return true;
+}
+
 static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   const size_t px = frame_pixels(v->cfg);
   if (!s.d_raw) {
@@ -297,6 +326,7 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
     CU_CHECK(cudaMemset(frame_dmax_ptr(s.d_frame, px), 0, frame_tail_bytes(v->cfg.im_h, v->cfg.im_w)));
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
+    s.tmap_ok = encode_frame_tmap(v, s);
   }
   return TSDF_OK;
 }
@@ -435,6 +465,9 @@ int make_frame_params(const tsdf_vol* v, const float* K, const float* T_wc, floa
   out->obs_weight = obs_weight;
   out->pad_ = 0;
   out->skip = v->comm_skip;
+  out->h_tmap = nullptr;
+  for (const FrameSlot& fs : v->slot) if (fs.d_frame == d_frame && fs.tmap_ok) out->h_tmap = fs.tmap;
+  for (const FrameSlot& fs : v->bslot) if (fs.d_frame == d_frame && fs.tmap_ok) out->h_tmap = fs.tmap;
   out->mb_x0 = 0; out->mb_y0 = 0; out->mb_x1 = v->cfg.im_w - 1; out->mb_y1 = v->cfg.im_h - 1;
   out->img = d_frame;
   out->dmax = frame_dmax_ptr(d_frame, frame_pixels(v->cfg));

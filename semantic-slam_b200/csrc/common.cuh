@@ -61,6 +61,7 @@ struct FrameP {       // one camera frame
                       // wait timed out: the prepared frame is stale), or null — see comm.cu
   int mb_x0, mb_y0, mb_x1, mb_y1;  // pixel rectangle (inclusive) outside which the frame is known to be
                                    // invalid for this launch: the instance's mask box, else the image
+  const void* h_tmap; // HOST pointer: CUtensorMap of the prepared frame (128 B) or null; read by the launcher only
   const void* img;    // prepared frame: float depth[H*W]  or  float4 {depth, c0, c1, c2}[H*W]
   const float* dmax;  // largest depth of the prepared frame (+inf when it holds a NaN)
 };
@@ -114,6 +115,8 @@ struct FrameSlot {
   void* h_pinned = nullptr;   // staging for pageable inputs (depth + rgb)
   void* d_raw = nullptr;      // raw upload target (depth fp32|u16 + rgb u8)
   void* d_frame = nullptr;    // prepared frame consumed by the integrate kernel
+  alignas(64) unsigned char tmap[128];  // CUtensorMap over d_frame as [H][4W] floats, box 64 x 32 pixels (colour frames)
+  bool tmap_ok = false;
   cudaEvent_t uploaded = nullptr;  // recorded on the copy stream after prep
   cudaEvent_t consumed = nullptr;  // recorded on the compute stream after integrate
   bool in_flight = false;

@@ -28,6 +28,9 @@
 
 namespace {
 
+#ifndef KI_MINBLOCKS
+#define KI_MINBLOCKS 4   // (A/B builds: -DKI_MINBLOCKS=3 lets the dense kernel take 80 registers)
+#endif
 constexpr int kThreads = 256;
 constexpr int kMaxRowsPerBlock = 128;
 
@@ -75,6 +78,23 @@ __device__ __forceinline__ void store_vec(float* p, const float (&v)[VEC]) {
 // ---------------------------------------------------------------------------------------
 constexpr int MATH_EXACT = 0, MATH_LITERAL = 1;
 
+// ---------------------------------------------------------------------------------------
+// Staged image tile (north_star: "depth and color tiles are staged through shared memory or TMA").
+// When the pixel rectangle the block's voxel tile can project to (the block-level hull test computes
+// it) fits one TMA box of kStageW x kStageH pixels, one elected thread fetches that box of the
+// prepared frame into shared memory with cp.async.bulk.tensor.2d behind an mbarrier, and the block's
+// gathers read shared memory instead of L1/L2: same pixel index -> same bits (src/tsdf.cu:45).
+// Blocks whose rectangle does not fit keep the __ldg gather.  A/B variant (tsdf_set_variant bit 16):
+// on the C2 / C3 geometries 2 % / 1 % of the in-view blocks fit (a 128-voxel run along z spreads over
+// ~100-200 pixels of parallax), see DESIGN.md §4.1.
+// ---------------------------------------------------------------------------------------
+constexpr int kStageW = 64, kStageH = 32;                 // pixels; 64 * 32 * 16 B = 32 KB
+struct Stage {
+  const float4* tile;   // shared memory, [kStageH][kStageW]
+  int on, x0, y0;
+};
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+
 struct Hit {          // result of probing one voxel against one frame
   bool ok;
   float dist;         // fmin(1, diff/trunc)                                   :53
@@ -82,10 +102,13 @@ struct Hit {          // result of probing one voxel against one frame
 };
 
 template <bool COLOR, bool MASK>
-__device__ __forceinline__ float fetch(const FrameP& f, const uint8_t* mask, int pix, Hit& h) {  // h: caller's registers
+__device__ __forceinline__ float fetch(const FrameP& f, const uint8_t* mask, int pix, Hit& h, const Stage* st = nullptr,
+                                       int sidx = 0) {  // h: caller's registers
   float d;
   if constexpr (COLOR) {
-    float4 p = __ldg(reinterpret_cast<const float4*>(f.img) + pix);  // :45 + colour, one gather
+    float4 p;
+    if (st != nullptr && st->on) p = st->tile[sidx];   // staged box (block-uniform branch)
+    else p = __ldg(reinterpret_cast<const float4*>(f.img) + pix);  // :45 + colour, one gather
     d = p.x; h.c0 = p.y; h.c1 = p.z; h.c2 = p.w;
   } else {
     d = __ldg(reinterpret_cast<const float*>(f.img) + pix);
@@ -159,7 +182,8 @@ __device__ __forceinline__ Hit probe_exact(const FrameP& f, const GridP& g, cons
 // The same in two stages (CULL = true instantiation), so that a run
 // whose voxels all project outside the image stops before the gather.  Operands outside the
 // safe exponent window (never seen on real data) take the literal path (caller's job).
-struct Proj { bool ok; int pix; };
+struct Proj { bool ok; int pix; int px, py; };   // (px, py: only the staged-tile variant reads them)
+
 
 template <bool SELECT>
 __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, float camx, float camy, float camz) {
@@ -172,6 +196,7 @@ __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, f
   p.ok = inr && u > -0.5f && u < g.w_lim && v > -0.5f && v < g.h_lim;
   const int px = em::round_half_away_nonneg_int(u);
   const int py = em::round_half_away_nonneg_int(v);
+  p.px = px; p.py = py;
   // select, not branch: the rounding of an out-of-image u/v is harmless, and a branch here
   // would sit between the four gathers of a run
   if constexpr (SELECT) {
@@ -183,16 +208,20 @@ __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, f
   return p;
 }
 
-template <bool COLOR, bool LE_TRUNC, bool MASK>
+// RAW_DIFF: h.dist receives diff itself (:48); the caller turns it into :53's dist (update_run4).
+template <bool COLOR, bool LE_TRUNC, bool MASK, bool RAW_DIFF = false>
 __device__ __forceinline__ Hit sample_exact(const FrameP& f, const GridP& g, const uint8_t* mask, const Proj& p,
-                                            float camz) {
+                                            float camz, const Stage* st = nullptr) {
   Hit h;
-  const float d = fetch<COLOR, MASK>(f, mask, p.pix, h);
+  int sidx = 0;
+  if (st != nullptr && st->on && p.ok) sidx = (p.py - st->y0) * kStageW + (p.px - st->x0);
+  const float d = fetch<COLOR, MASK>(f, mask, p.pix, h, st, sidx);
   bool ok = p.ok && !(d <= 0.0f);                         // :46
   const float diff = d - camz;                            // :48
   if constexpr (LE_TRUNC) ok = ok && !(diff <= -g.trunc); // :49
   else                    ok = ok && !(diff < -g.trunc);
-  h.dist = fminf(1.0f, em::div_rn(diff, g.trunc, g.inv_trunc));  // :53
+  if constexpr (RAW_DIFF) h.dist = diff;
+  else                    h.dist = fminf(1.0f, em::div_rn(diff, g.trunc, g.inv_trunc));  // :53
   h.ok = ok;
   return h;
 }
@@ -209,7 +238,8 @@ __device__ __forceinline__ Hit sample_exact(const FrameP& f, const GridP& g, con
 // than the frame's largest depth plus the truncation).  Never true on NaN/Inf input.
 // ---------------------------------------------------------------------------------------
 __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, float xa, float ya, float za,
-                                               float xb, float yb, float zb, const int* __restrict__ tail) {
+                                               float xb, float yb, float zb, const int* __restrict__ tail,
+                                               int* rect = nullptr /* out: pxl, pxh, pyl, pyh when known */) {
   const float big = 3.0e38f;
   const bool fin = fabsf(xa) <= big && fabsf(ya) <= big && fabsf(za) <= big &&
                    fabsf(xb) <= big && fabsf(yb) <= big && fabsf(zb) <= big;
@@ -243,6 +273,7 @@ __device__ __forceinline__ bool box_is_skipped(const FrameP& f, const GridP& g, 
   const int pxh = min(g.W - 1, (int)floorf(__fadd_ru(fminf(umax, g.w_lim), 0.5f)));
   const int pyl = max(0, (int)floorf(__fadd_rd(fmaxf(vmin, -0.5f), 0.5f)));
   const int pyh = min(g.H - 1, (int)floorf(__fadd_ru(fminf(vmax, g.h_lim), 0.5f)));
+  if (rect) { rect[0] = pxl; rect[1] = pxh; rect[2] = pyl; rect[3] = pyh; }
   // (batched instances: the mask is 0 outside the instance's box, i.e. depth * 0 = invalid, :46)
   if (pxh < f.mb_x0 || pxl > f.mb_x1 || pyh < f.mb_y0 || pyl > f.mb_y1) return true;
   const int tw0 = tiles_across(g.W, kTile0Log2), th0 = tiles_across(g.H, kTile0Log2);
@@ -326,14 +357,71 @@ __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, con
   }
 }
 
+// The dense kernels' update of one run of 4 voxels by one frame, src/tsdf.cu:53-57 (+ colour), computed
+// for every voxel and selected by its ok flag (no divergence bookkeeping around ~60 instructions).
+// hit[j].dist holds the raw diff of :48.  Two exact short cuts for free space, where most updated
+// voxels of any frame lie (FREE; per thread, on the whole run):
+//   * diff >= trunc (or NaN) for every updated voxel: :53's fmin(1, diff / trunc) is 1 — RN division is
+//     monotone and trunc / trunc == 1, and fminf drops a NaN — so the four quotients are skipped;
+//   * then, with obs_weight == 1 (WMODE 1) and stored tsdf == 1: :57's (1 * w0 + 1) / (w0 + 1) is w1 / w1
+//     == 1 — the stored value stays, and the four tsdf quotients are skipped too.
+template <bool COLOR, int WMODE, bool FREE>
+__device__ __forceinline__ void update_run4(const GridP& g, const Hit (&hit)[4], float obs, float (&t)[4], float (&w)[4],
+                                            float (&col)[4], unsigned int& n_written, bool& any) {
+  bool far = FREE;
+  if constexpr (FREE) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) far = far && (!hit[j].ok || !(hit[j].dist < g.trunc));
+  }
+  float dist[4];
+  if (far) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dist[j] = 1.0f;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dist[j] = fminf(1.0f, em::div_rn(hit[j].dist, g.trunc, g.inv_trunc));   // :53
+  }
+  bool t_stays = FREE && WMODE == 1 && far;
+  if constexpr (FREE && WMODE == 1) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) t_stays = t_stays && (!hit[j].ok || t[j] == 1.0f);
+  }
+  float yw[4], w1[4];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    w1[j] = w[j] + obs;                                   // :55
+    if (COLOR || !t_stays) yw[j] = em::rcp_rn(w1[j]);
+  }
+  if (!t_stays) {
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float nt = em::div_rn(t[j] * w[j] + dist[j], w1[j], yw[j]);   // :57
+      t[j] = hit[j].ok ? nt : t[j];
+    }
+  }
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const bool ok = hit[j].ok;
+    if constexpr (COLOR) {
+      const float nc = WMODE == 1 ? em::blend_intw(col[j], hit[j].c0, hit[j].c1, hit[j].c2, w[j], yw[j])
+                                  : em::blend_exact(col[j], hit[j].c0, hit[j].c1, hit[j].c2, w[j], w1[j], yw[j]);
+      col[j] = ok ? nc : col[j];
+    }
+    w[j] = ok ? w1[j] : w[j];                             // :56
+    n_written += ok ? 1u : 0u;
+    any = any || ok;
+  }
+}
+
 // ZFAST : slab layout [x][y][zl]  (row = x*Dy + y, fast = zl)   — plugin surface
 // !ZFAST: slab layout [zl][y][x]  (row = zl*Dy + y, fast = x)   — class TSDF, src/tsdf.cu:52
 // Row table entry per frame (padded to 128-bit loads):
 //   ZFAST  {A0,A1,A2,-}                A_k = c[k]*t0 + c[4+k]*t1
 //   !ZFAST {Y0,Y1,Y2,-, Z0,Z1,Z2,-}    Y_k = c[4+k]*t1, Z_k = c[8+k]*t2
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, bool MASK, int MATH, int WMODE, int CULL>
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, bool MASK, int MATH, int WMODE, int CULL, bool STAGE = false>
 __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8_t* mask, float4* tab,
-                                               int tpr_log2, int rows_per_block, int flags) {
+                                               int tpr_log2, int rows_per_block, int flags,
+                                               const void* tmap = nullptr, float4* stage_tile = nullptr) {
   constexpr int NT = ZFAST ? 1 : 2;  // float4 per row per frame
   const GridP& g = P.g;
   const int pf = flags & 3;            // software prefetch: 0 off, 1 L2, 2 L1
@@ -356,7 +444,10 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   // warp instructions on S-kitti), lets a block outside the frustum, behind the camera or behind
   // everything the frame sees leave at the row-table barrier.
   __shared__ int blk_skip;
+  __shared__ int stage_xy[3];                      // on, x0, y0
+  __shared__ __align__(8) unsigned long long stage_bar;
   const bool blk_test = CULL == 2 && NF == 1 && (flags & 4);
+  if constexpr (STAGE) { if (threadIdx.x == 0) stage_xy[0] = 0; }
   if constexpr (CULL == 2 && NF == 1) {
     if (blk_test && threadIdx.x < 32) {
       const int r_last = min(row0 + rows_per_block, n_rows) - 1;
@@ -414,9 +505,24 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
         }
       }
       // (a NaN planted above, or produced by the additions, fails box_is_skipped's finiteness test)
+      int rect[4] = {0, -1, 0, -1};
       const bool skip = box_is_skipped(P.f[0], g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
-                                       reinterpret_cast<const int*>(P.f[0].dmax));
+                                       reinterpret_cast<const int*>(P.f[0].dmax), STAGE ? rect : nullptr);
       if (threadIdx.x == 0) blk_skip = skip;
+      if constexpr (STAGE) {
+        // every pixel a voxel of this block can read lies in rect: if it fits one box, fetch the box
+        if (threadIdx.x == 0 && !skip && rect[1] >= rect[0] && rect[3] >= rect[2] &&
+            rect[1] - rect[0] < kStageW && rect[3] - rect[2] < kStageH) {
+          const unsigned bar = smem_u32(&stage_bar), dst = smem_u32(stage_tile);
+          asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+          asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+          asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(kStageW * kStageH * 16) : "memory");
+          asm volatile(
+              "cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+              ::"r"(dst), "l"(tmap), "r"(4 * rect[0]), "r"(rect[2]), "r"(bar) : "memory");
+          stage_xy[0] = 1; stage_xy[1] = rect[0]; stage_xy[2] = rect[2];
+        }
+      }
     }
   }
 
@@ -440,6 +546,19 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   __syncthreads();
   if constexpr (CULL == 2 && NF == 1)
     if (blk_test && blk_skip) return;   // block-uniform
+  Stage stg;
+  stg.tile = stage_tile; stg.on = 0; stg.x0 = 0; stg.y0 = 0;
+  if constexpr (STAGE) {
+    if (stage_xy[0]) {   // block-uniform: wait for the box (phase 0 of the barrier)
+      const unsigned bar = smem_u32(&stage_bar);
+      unsigned done = 0;
+      while (!done) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(done) : "r"(bar) : "memory");
+      }
+      stg.on = 1; stg.x0 = stage_xy[1]; stg.y0 = stage_xy[2];
+    }
+  }
 
   // ---- this thread's run on the fast axis -----------------------------------------------
   const int tpr = 1 << tpr_log2;
@@ -560,6 +679,9 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     }
     Hit hit[NF][VEC];
     bool any = false;
+    // dense kernel, 4-wide runs: the probes leave the raw diff in Hit::dist and update_run4 finishes :53
+    constexpr bool kRun4 = CULL == 0 && VEC == 4 && MATH == MATH_EXACT && NF == 1;
+    bool raw_diff = kRun4;
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
       const float4* e = tab + (lr * NF + f) * NT;
@@ -591,6 +713,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
 #pragma unroll
         for (int j = 0; j < VEC; ++j) odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
         if (__builtin_expect(odd, 0)) {
+          raw_diff = false;
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
             hit[f][j] = probe_literal_cold<COLOR, LE_TRUNC, MASK>(P.f[f].img, P.f[f].fx, P.f[f].cx, P.f[f].fy, P.f[f].cy,
@@ -611,7 +734,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           if (CULL == 0 || in_image) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-              hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, pr[j], camz[j]);
+              hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK, kRun4>(P.f[f], g, mask, pr[j], camz[j], STAGE ? &stg : nullptr);
               any = any || hit[f][j].ok;
             }
           } else {
@@ -640,7 +763,21 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       // is computed unconditionally and selected — no divergence bookkeeping around 60
       // instructions.  Sparse frames keep the branch: measured (S-real / S-kitti, round-robin)
       // the select form costs 7-16 % there, and a per-run hybrid of the two 6 %.
-      if constexpr (CULL == 0) {
+      if constexpr (kRun4) {
+        if (raw_diff) {
+          bool any2 = false;
+          if (flags & 8) update_run4<COLOR, WMODE, false>(g, hit[f], obs, t, w, col, n_written, any2);   // A/B: no free-space short cuts
+          else           update_run4<COLOR, WMODE, true>(g, hit[f], obs, t, w, col, n_written, any2);
+        } else {
+#pragma unroll
+          for (int j = 0; j < VEC; ++j) {
+            if (hit[f][j].ok) {
+              update_voxel<COLOR, MATH, WMODE>(t[j], w[j], col[j], hit[f][j], obs);
+              ++n_written;
+            }
+          }
+        }
+      } else if constexpr (CULL == 0) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
           float nt = t[j], nw = w[j], nc = col[j];
@@ -672,10 +809,23 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
 }
 
 template <bool ZFAST, bool COLOR, bool LE_TRUNC, int NF, int VEC, int MATH, int WMODE, int CULL>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)   // 64 registers: four blocks per SM keep the HBM stream fed
 k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_block, int flags) {
   __shared__ float4 tab[kMaxRowsPerBlock * NF * (ZFAST ? 1 : 2)];
   integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE, CULL>(P, nullptr, tab, tpr_log2, rows_per_block, flags);
+}
+
+struct TmapParam { alignas(64) unsigned char bytes[128]; };   // a CUtensorMap, by value (param space)
+
+// Sparse-frame kernel with the staged image tile (A/B variant, see `Stage`): colour frames, 4-wide runs.
+template <bool ZFAST, bool LE_TRUNC, int WMODE>
+__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)
+k_integrate_staged(const __grid_constant__ LaunchP<1> P, const __grid_constant__ TmapParam tm, int tpr_log2,
+                   int rows_per_block, int flags) {
+  __shared__ float4 tab[kMaxRowsPerBlock * (ZFAST ? 1 : 2)];
+  extern __shared__ __align__(128) unsigned char stage_raw[];
+  integrate_body<ZFAST, true, LE_TRUNC, 1, 4, false, MATH_EXACT, WMODE, 2, true>(
+      P, nullptr, tab, tpr_log2, rows_per_block, flags, &tm, reinterpret_cast<float4*>(stage_raw));
 }
 
 // ---------------------------------------------------------------------------------------
@@ -771,19 +921,22 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
 #pragma unroll
         for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true>(P.f[f], g, camx[j], camy[j], camz[j]);
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false>(P.f[f], g, nullptr, pr[j], camz[j]);
+        for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false, true>(P.f[f], g, nullptr, pr[j], camz[j]);
       }
       const float obs = P.f[f].obs_weight;
+      if (__builtin_expect(odd, 0)) {
 #pragma unroll
-      for (int j = 0; j < VEC; ++j) {
-        float nt = t[j], nw = w[j], nc = col[j];
-        update_voxel<COLOR, MATH_EXACT, WMODE>(nt, nw, nc, hit[j], obs);
-        const bool ok = hit[j].ok;
-        t[j] = ok ? nt : t[j];
-        w[j] = ok ? nw : w[j];
-        col[j] = ok ? nc : col[j];
-        n_written += ok ? 1u : 0u;
-        any = any || ok;
+        for (int j = 0; j < VEC; ++j) {
+          if (hit[j].ok) {
+            update_voxel<COLOR, MATH_EXACT, WMODE>(t[j], w[j], col[j], hit[j], obs);
+            ++n_written;
+            any = true;
+          }
+        }
+      } else if (flags & 8) {
+        update_run4<COLOR, WMODE, false>(g, hit, obs, t, w, col, n_written, any);
+      } else {
+        update_run4<COLOR, WMODE, true>(g, hit, obs, t, w, col, n_written, any);
       }
     }
     if (any) {
@@ -834,6 +987,8 @@ struct LaunchOpts {
   bool balance = true; // dense kernel, few waves: size the blocks so that the grid fills whole waves
   bool compact = true;    // sparse kernel: compact block tiles (one warp per row segment)
   bool block_test = true; // sparse kernel: block-level hull test before the per-warp tests
+  bool free_fast = true;  // dense kernels: exact free-space short cuts of update_run4
+  const void* tmap = nullptr;  // sparse kernel: CUtensorMap of the prepared frame => staged image tile (A/B)
 };
 
 struct Geometry { int tpr_log2, rows_per_block; dim3 grid; };
@@ -904,8 +1059,22 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
     }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
+  if constexpr (COLOR && NF == 1 && VEC == 4 && MATH == MATH_EXACT) {
+    if (o.kernel == 1 && o.tmap != nullptr && o.block_test) {
+      TmapParam tm;
+      memcpy(tm.bytes, o.tmap, 128);
+      constexpr int kStageBytes = kStageW * kStageH * 16;
+      static const bool attr_ok = cudaFuncSetAttribute(k_integrate_staged<ZFAST, LE_TRUNC, WMODE>,
+                                                       cudaFuncAttributeMaxDynamicSharedMemorySize, kStageBytes) == cudaSuccess;
+      if (attr_ok) {
+        k_integrate_staged<ZFAST, LE_TRUNC, WMODE><<<q.grid, kThreads, kStageBytes, st>>>(P, tm, q.tpr_log2, q.rows_per_block, pf | 4);
+        CU_LAUNCHED();
+        return TSDF_OK;
+      }
+    }
+  }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
-  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.free_fast ? 0 : 8));
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
   CU_LAUNCHED();
   return TSDF_OK;
@@ -926,7 +1095,7 @@ int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cud
     }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
-  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, o.prefetch ? 1 : 0);
+  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, (o.prefetch ? 1 : 0) | (o.free_fast ? 0 : 8));
   CU_LAUNCHED();
   return TSDF_OK;
 }
@@ -1023,6 +1192,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   o.balance = (v->variant & 2048) == 0;
   o.compact = (v->variant & 4096) == 0;      // bit12: old block shape (row-major, up to 256 threads per row)
   o.block_test = (v->variant & 8192) == 0;   // bit13: block-level hull test off
+  o.free_fast = (v->variant & 32768) == 0;   // bit15: free-space short cuts of the dense kernels off
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
@@ -1050,6 +1220,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
       continue;
     }
     LaunchOpts o1 = o;
+    o1.tmap = (v->variant & 65536) ? frames[i].h_tmap : nullptr;   // bit16: staged image tile (A/B)
     if (!(v->variant & (64 | 128 | 1024))) o1.kernel = slab_inside_every_frustum(g, frames + i, 1) ? 0 : 1;
     if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st)
                            : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st);

@@ -115,3 +115,47 @@ def test_kitti_shaped_config3(pkg, oracle, synth):
         sl = (slice(None), slice(None), slice(*zr))
         assert np.array_equal(sw, w3[sl].reshape(-1)) and np.array_equal(bits(st), bits(t3[sl].reshape(-1)))
         assert np.array_equal(sc, c3[sl].reshape(-1))
+
+
+STAGED = 65536   # tsdf_set_variant bit 16: staged image tile (TMA box in shared memory) in the sparse kernel
+
+
+@pytest.mark.parametrize("sem", [SEM_FUSIONPY, SEM_TSDFCU])
+def test_staged_image_tile_reads_the_same_pixels(pkg, oracle, synth, sem):
+    """The staged variant of the sparse kernel (cp.async.bulk.tensor.2d box of the prepared frame in
+    shared memory when a block's pixel rectangle fits 64 x 32 pixels) must gather the same bits as the
+    __ldg path (src/tsdf.cu:45: same pixel index -> same value).  Two geometries: a small far volume
+    whose block tiles all fit the box (straddling the sphere's surface and its shadow), and random
+    poses around a larger volume where almost none fits (the fallback inside the same kernel)."""
+    big = (512, 512, 512)
+    _, frames = synth.s_full(big, 0.004, n_frames=3, sphere=True)
+    z_near = float(_[2])
+    r = 0.15 * 2.048
+    dims, vs = (128, 128, 128), 0.001
+    origin = np.array([-0.064 + 0.11, -0.064 - 0.05, z_near + 2.048 - 1.5 * r - 0.064], np.float32)
+    cases = [(dims, vs, origin, frames)]
+    d2, v2 = (160, 24, 288), 0.02
+    rng = np.random.default_rng(77)
+    ext = np.array(d2, np.float32) * v2
+    o2 = np.array([-ext[0] / 2, -ext[1] / 2, 0.5], np.float32)
+    center = o2 + ext / 2
+    scene = synth.room_scene(center, ext.max() * 0.45).sphere(tuple(center), float(ext.min()) * 0.3)
+    fr2 = []
+    for T in random_poses(synth, rng, center, float(ext.max()) * 0.6, 6):
+        d, rgb = synth.render(scene, synth.TUM3_K, synth.TUM3_HW, T, rng, noise_sigma=0.002, hole_frac=0.05)
+        fr2.append((d, rgb, T))
+    cases.append((d2, v2, o2, fr2))
+    for dm, vsz, org, frs in cases:
+        cfg = pkg.make_config(dm, vsz, org, semantics=sem, with_color=True, max_depth=20.0)
+        p, t, w, c, ow = oracle_run(oracle, dm, vsz, org, frs, sem, True, max_depth=20.0)
+        assert sum(ow) > 1000
+        a = run_gpu(pkg, cfg, frs, True, FORCE_CULL)
+        b = run_gpu(pkg, cfg, frs, True, FORCE_CULL | STAGED)
+        assert a[3] == b[3] == ow
+        for x, y in zip(a[:3], b[:3]):
+            assert np.array_equal(bits(x), bits(y))
+        assert_volume_equal(b[0], b[1], b[2], t, w, c)
+    # the far volume must not be trivially free space: the sphere's surface crosses it
+    dm, vsz, org, frs = cases[0]
+    p, t, w, c, ow = oracle_run(oracle, dm, vsz, org, frs, sem, True, max_depth=20.0)
+    assert (t < 0.5).any() and (w == 0).any() and (w == 3).any()
