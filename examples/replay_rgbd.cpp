@@ -13,17 +13,20 @@
 //   float  K[9], DepthMapFactor, fusion vol_bnds[6], fusion voxel_size
 //   per frame: float Twc[16]; uint16 depth[H*W]; uint8 rgb[H*W*3]
 //
-// usage: replay_rgbd <sequence.bin> <out_dir> [tsdf|fusion|both] [--raw]
+// usage: replay_rgbd <sequence.bin> <out_dir> [tsdf|fusion|both] [--raw | --devices 0,1,...]
 //   tsdf   -> <out_dir>/tsdf<id>.ply, tsdf<id>.bin (written by ~TSDF, src/tsdf.cu:107-132),
 //             weights.f32 (the public mirror voxel_grid_weight)
 //   fusion -> <out_dir>/fusion_tsdf.f32, fusion_color.f32, fusion_points.ply, fusion_mesh.ply
 //             (SaveMesh of the plugin, src/TSDFfusion.py.in:48-53)
 //   --raw  -> hand the u16 image to tsdf_integrate_raw_async (subsampling + scaling on the GPU)
+//   --devices a,b,.. -> the TSDFfusion volume as z-slabs over that device list, one process, no Python
+//             (a device may repeat); the output files must not change
 // exit codes: 0 ok, 1 usage / file error, 2 library error (e.g. no CUDA device: no CPU fallback)
 #include <unistd.h>
 
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
@@ -105,6 +108,15 @@ int main(int argc, char** argv) {
   }
   const std::string mode = argc > 3 ? argv[3] : "both";
   const bool raw = argc > 4 && !strcmp(argv[4], "--raw");
+  std::vector<int> devices(1, 0);
+  if (argc > 5 && !strcmp(argv[4], "--devices")) {
+    devices.clear();
+    for (const char* p = argv[5]; *p;) {
+      devices.push_back(atoi(p));
+      while (*p && *p != ',') ++p;
+      if (*p == ',') ++p;
+    }
+  }
   Sequence s;
   if (!load(argv[1], s) || s.n < 1) {
     fprintf(stderr, "cannot read sequence %s\n", argv[1]);
@@ -138,7 +150,7 @@ int main(int argc, char** argv) {
     }
     if (mode == "fusion" || mode == "both") {
       std::vector<double> bnds(s.bnds, s.bnds + 6);
-      TSDFfusion fusion(bnds, (double)s.fusion_vs, s.H, s.W);
+      TSDFfusion fusion(bnds, (double)s.fusion_vs, s.H, s.W, devices);
       fusion.SetIntrinsics(s.K);
       for (int i = 0; i < s.n; ++i) {
         preprocess(s, s.depth[i], depth);

@@ -38,14 +38,27 @@ class TSDFfusion {
   /// fusion.TSDFVolume(vol_bnds, voxel_size): dims = ceil(extent / voxel_size), trunc = 5 voxels.
   TSDFfusion(const std::vector<double>& vol_bnds /* xmin,xmax,ymin,ymax,zmin,zmax */, double voxel_size,
              int im_h = 480, int im_w = 640, int device = 0)
-      : vol_(nullptr) {
+      : TSDFfusion(vol_bnds, voxel_size, im_h, im_w, std::vector<int>(1, device)) {}
+
+  /// The same volume cut into z-slabs over a DEVICE LIST, still one object in one process (the
+  /// reference is a single process, src/Engine.cpp:105): slab i lives on devices[i], every frame is
+  /// staged once and read by the other GPUs over NVLink (tsdf_group_*).  Results — volume, point
+  /// cloud, mesh — are those of the single-device object.  One entry = the single-device path.
+  TSDFfusion(const std::vector<double>& vol_bnds, double voxel_size, int im_h, int im_w, const std::vector<int>& devices)
+      : vol_(nullptr), grp_(nullptr) {
     if (vol_bnds.size() != 6) throw std::invalid_argument("TSDFfusion: vol_bnds needs 6 values");
+    if (devices.empty()) throw std::invalid_argument("TSDFfusion: empty device list");
     tsdf_config cfg;
     check(tsdf_config_from_bounds(vol_bnds.data(), voxel_size, &cfg), "tsdf_config_from_bounds");
     cfg.im_h = im_h;
     cfg.im_w = im_w;
-    cfg.device = device;
-    check(tsdf_create(&cfg, &vol_), "tsdf_create");
+    cfg.device = devices[0];
+    if (devices.size() == 1) {
+      check(tsdf_create(&cfg, &vol_), "tsdf_create");
+    } else {
+      std::vector<int32_t> d(devices.begin(), devices.end());
+      check(tsdf_group_create(&cfg, d.data(), (int)d.size(), &grp_), "tsdf_group_create");
+    }
     cfg_ = cfg;
     for (int i = 0; i < 16; ++i) pose_[i] = (i % 5 == 0) ? 1.0f : 0.0f;
     const float K[9] = {535.4f, 0, 320.1f, 0, 539.2f, 247.6f, 0, 0, 1};  // src/TSDFfusion.py.in:21
@@ -54,6 +67,7 @@ class TSDFfusion {
 
   ~TSDFfusion() {
     if (vol_) tsdf_destroy(vol_);
+    if (grp_) tsdf_group_destroy(grp_);
   }
   TSDFfusion(const TSDFfusion&) = delete;
   TSDFfusion& operator=(const TSDFfusion&) = delete;
@@ -64,13 +78,15 @@ class TSDFfusion {
   /// tsdf_vol.integrate(color_image, depth_im, cam_intr, cam_pose, obs_weight=1.) —
   /// src/TSDFfusion.py.in:43.  rgb: H*W*3 u8, depth: H*W fp32 metres, cam_pose: row-major Twc.
   void Integrate(const uint8_t* rgb, const float* depth, const float cam_pose[16], float obs_weight = 1.0f) {
-    check(tsdf_integrate(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate");
+    if (grp_) check(tsdf_group_integrate(grp_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_group_integrate");
+    else      check(tsdf_integrate(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate");
   }
   /// Non-blocking variant; inputs are borrowed until Sync().
   void IntegrateAsync(const uint8_t* rgb, const float* depth, const float cam_pose[16], float obs_weight = 1.0f) {
-    check(tsdf_integrate_async(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate_async");
+    if (grp_) check(tsdf_group_integrate_async(grp_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_group_integrate_async");
+    else      check(tsdf_integrate_async(vol_, depth, rgb, K_, cam_pose, obs_weight), "tsdf_integrate_async");
   }
-  void Sync() { check(tsdf_sync(vol_), "tsdf_sync"); }
+  void Sync() { check(grp_ ? tsdf_group_sync(grp_) : tsdf_sync(vol_), "tsdf_sync"); }
 
 #ifdef TSDF_B200_WITH_OPENCV
   /// The reference's signature (include/TSDFfusion.hpp:49); pose = last SetPose().
@@ -97,44 +113,48 @@ class TSDFfusion {
   int64_t GetMesh(std::vector<float>& verts, std::vector<int32_t>& faces, std::vector<float>& norms,
                   std::vector<uint8_t>& colors) {
     int64_t nv = 0, nf = 0;
-    check(tsdf_extract_mesh(vol_, nullptr, nullptr, nullptr, 0, nullptr, 0, &nv, &nf), "mesh count");
+    check(mesh(nullptr, nullptr, nullptr, 0, nullptr, 0, &nv, &nf), "mesh count");
     verts.resize((size_t)nv * 3);
     norms.resize((size_t)nv * 3);
     colors.resize((size_t)nv * 3);
     faces.resize((size_t)nf * 3);
-    if (nv)
-      check(tsdf_extract_mesh(vol_, verts.data(), norms.data(), colors.data(), nv, faces.data(), nf, &nv, &nf),
-            "tsdf_extract_mesh");
+    if (nv) check(mesh(verts.data(), norms.data(), colors.data(), nv, faces.data(), nf, &nv, &nf), "tsdf_extract_mesh");
     return nv;
   }
   /// SaveMesh(file_name) (src/TSDFfusion.py.in:48-53): get_mesh() + fusion.meshwrite.  The reference
   /// ignores file_name and always writes "mesh.ply" (:53); here the name is honoured.
   void SaveMesh(const std::string& file_name) {
-    check(tsdf_save_mesh_ply(vol_, file_name.c_str()), "tsdf_save_mesh_ply");
+    check(grp_ ? tsdf_group_save_mesh_ply(grp_, file_name.c_str()) : tsdf_save_mesh_ply(vol_, file_name.c_str()),
+          "tsdf_save_mesh_ply");
   }
 
   /// Point-cloud readback (surface voxels as xyz + rgb) beside the mesh — returns the point count.
   int64_t GetPointCloud(std::vector<float>& xyz, std::vector<uint8_t>& rgb, float tsdf_thresh = 1.2f,
                         float weight_thresh = 0.9f, int predicate = TSDF_PRED_NONZERO) {
     int64_t n = 0;
-    check(tsdf_extract_points(vol_, predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, nullptr, 0, &n), "count");
+    check(points(predicate, tsdf_thresh, weight_thresh, nullptr, nullptr, 0, &n), "count");
     xyz.resize((size_t)n * 3);
     rgb.resize((size_t)n * 3);
-    if (n) check(tsdf_extract_points(vol_, predicate, tsdf_thresh, weight_thresh, xyz.data(), rgb.data(), nullptr, n, &n), "extract");
+    if (n) check(points(predicate, tsdf_thresh, weight_thresh, xyz.data(), rgb.data(), n, &n), "extract");
     return n;
   }
   void SavePointCloud(const std::string& file_name, float tsdf_thresh = 1.2f, float weight_thresh = 0.9f) {
-    check(tsdf_save_ply(vol_, file_name.c_str(), TSDF_PRED_NONZERO, tsdf_thresh, weight_thresh), "tsdf_save_ply");
+    check(grp_ ? tsdf_group_save_ply(grp_, file_name.c_str(), TSDF_PRED_NONZERO, tsdf_thresh, weight_thresh)
+               : tsdf_save_ply(vol_, file_name.c_str(), TSDF_PRED_NONZERO, tsdf_thresh, weight_thresh),
+          "tsdf_save_ply");
   }
   /// get_volume(): tsdf and colour arrays in numpy C order of [Dx,Dy,Dz].
   void GetVolume(std::vector<float>& tsdf, std::vector<float>& color) {
     size_t n = (size_t)cfg_.dim_x * cfg_.dim_y * cfg_.dim_z;
     tsdf.resize(n);
     color.resize(n);
-    check(tsdf_download(vol_, tsdf.data(), nullptr, color.data(), 0), "tsdf_download");
+    check(grp_ ? tsdf_group_download(grp_, tsdf.data(), nullptr, color.data())
+               : tsdf_download(vol_, tsdf.data(), nullptr, color.data(), 0),
+          "tsdf_download");
   }
   const tsdf_config& config() const { return cfg_; }
-  tsdf_vol* handle() { return vol_; }
+  tsdf_vol* handle() { return vol_; }        ///< single-device object (null on a device list)
+  tsdf_group* group() { return grp_; }       ///< device-list object (null on a single device)
 
  private:
   static std::vector<double> default_bounds() { return {0, 10, 0, 10, 0, 10}; }
@@ -142,7 +162,16 @@ class TSDFfusion {
     // the reference throws std::runtime_error on import/lookup failure (src/TSDFfusion.cpp:62-68,79-85)
     if (rc != TSDF_OK) throw std::runtime_error(std::string("TSDFfusion: ") + what + ": " + tsdf_last_error());
   }
+  int mesh(float* v, float* n, uint8_t* c, int64_t vcap, int32_t* f, int64_t fcap, int64_t* nv, int64_t* nf) {
+    return grp_ ? tsdf_group_extract_mesh(grp_, v, n, c, vcap, f, fcap, nv, nf)
+                : tsdf_extract_mesh(vol_, v, n, c, vcap, f, fcap, nv, nf);
+  }
+  int points(int pred, float tt, float wt, float* xyz, uint8_t* rgb, int64_t cap, int64_t* n) {
+    return grp_ ? tsdf_group_extract_points(grp_, pred, tt, wt, xyz, rgb, nullptr, cap, n)
+                : tsdf_extract_points(vol_, pred, tt, wt, xyz, rgb, nullptr, cap, n);
+  }
   tsdf_vol* vol_;
+  tsdf_group* grp_ = nullptr;
   tsdf_config cfg_;
   float pose_[16];
   float K_[9];

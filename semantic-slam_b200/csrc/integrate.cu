@@ -933,10 +933,11 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
             any = true;
           }
         }
-      } else if (flags & 8) {
-        update_run4<COLOR, WMODE, false>(g, hit, obs, t, w, col, n_written, any);
       } else {
-        update_run4<COLOR, WMODE, true>(g, hit, obs, t, w, col, n_written, any);
+        // (no free-space short cuts here: measured round-robin on the B200 they cost the two-frame
+        // kernel 2-3 % — 4.08 vs 3.99 ms per frame at 1024^3, profiles/r2_v2_pair_ab.jsonl — while
+        // the single-frame kernel gains 4 % from them, profiles/r2_v2_free_ab.jsonl)
+        update_run4<COLOR, WMODE, false>(g, hit, obs, t, w, col, n_written, any);
       }
     }
     if (any) {
@@ -1095,7 +1096,7 @@ int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cud
     }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
-  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, (o.prefetch ? 1 : 0) | (o.free_fast ? 0 : 8));
+  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, o.prefetch ? 1 : 0);
   CU_LAUNCHED();
   return TSDF_OK;
 }

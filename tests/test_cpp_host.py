@@ -111,6 +111,28 @@ def test_cpp_replay_matches_oracle(replay_bin, synth, oracle, tmp_path, raw):
     assert (tmp_path / "o2_mesh.ply").read_bytes() == (tmp_path / "fusion_mesh.ply").read_bytes()
 
 
+@pytest.mark.gpu
+def test_cpp_replay_on_a_device_list_writes_the_same_files(replay_bin, synth, pkg, tmp_path):
+    """`TSDFfusion(bnds, vs, h, w, devices)`: the C++ host drives N z-slabs in ONE process (no Python,
+    no torchrun in the loop) and every output file — volume, colour, point cloud, mesh — equals the
+    single-device run's, byte for byte.  [0,0,0] on a 1-GPU box, across devices where there are more."""
+    make_sequence(synth, tmp_path / "seq.bin")
+    lists = ["0,0,0"] + (["0,1", "1,0,1"] if pkg.device_count() >= 2 else [])
+    ref = tmp_path / "single"
+    ref.mkdir()
+    r = subprocess.run([replay_bin, str(tmp_path / "seq.bin"), str(ref), "fusion"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    for k, devs in enumerate(lists):
+        out = tmp_path / f"slabs{k}"
+        out.mkdir()
+        r = subprocess.run([replay_bin, str(tmp_path / "seq.bin"), str(out), "fusion", "--devices", devs],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+        for name in ("fusion_tsdf.f32", "fusion_color.f32", "fusion_points.ply", "fusion_mesh.ply"):
+            assert (out / name).read_bytes() == (ref / name).read_bytes(), f"{devs}: {name} differs"
+        assert (out / "fusion_mesh.ply").stat().st_size > 10000
+
+
 @pytest.fixture(scope="module")
 def cvmat_bin(pkg, tmp_path_factory):
     """tests/cpp/cvmat_overloads.cpp against the mock <opencv2/core.hpp> (OpenCV headers are absent
