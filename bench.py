@@ -640,10 +640,14 @@ def extras(pkg, line, frames, origin, vol=None):
                 ref.close()
                 cfg = pkg.make_config((dim,) * 3, vs_r, o_r, semantics=pkg.SEM_TSDFCU, with_color=False, max_depth=1e9)
                 with pkg.Volume(cfg) as vr:
-                    vr.set_variant(0)   # A/B tooling handle: bench_kernel re-launches on the prepared frame
                     vr.integrate(fr_r[0][0], None, fr_r[0][2])
-                    vr.bench_kernel(3)
-                    ms_own = min(vr.bench_kernel(5) for _ in range(3))
+                    # kernel alone: per-launch CUDA events (tsdf_kernel_timing) over a few frames
+                    vr.kernel_timing(True)
+                    for i in range(6):
+                        vr.integrate(fr_r[i % 2][0], None, fr_r[i % 2][2], sync=False)
+                    ks, kn = vr.kernel_timing_read()
+                    vr.kernel_timing(False)
+                    ms_own = ks / max(kn, 1)
                     # the drop-in call itself: blocking Integrate(depth, pose) from pageable host memory,
                     # like the reference's (upload + kernel + wait), host wall clock
                     calls = []

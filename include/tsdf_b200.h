@@ -395,20 +395,11 @@ int tsdf_read_associations(const char* path, double* t_rgb, double* t_depth, cha
                            char* depth_names, int name_stride, int cap, int* n_lines);
 
 /* ---- measurement hooks (used by bench.py; no effect on results) ------------ */
-/* Times `iters` back-to-back launches of the integrate kernel on the frame
- * last uploaded to the handle (volume state keeps evolving) with CUDA events
- * on the handle's stream; returns average ms per launch.                    */
-int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms);
-/* Selects a kernel variant for A/B evidence (0 = default).                  */
-int tsdf_set_variant(tsdf_vol* v, int variant);
 /* Device-side stopwatch on the handle's compute stream (CUDA events): start
  * records now; stop records after everything enqueued so far, waits for it
  * and returns the elapsed ms.  bench.py brackets its timed region with it.  */
 int tsdf_timer_start(tsdf_vol* v);
 int tsdf_timer_stop(tsdf_vol* v, float* ms);
-/* Per-launch timing of the integrate kernel: when enabled every launch is
- * bracketed by its own CUDA event pair on the launching stream; read returns
- * the summed kernel ms and the number of launches since the last reset.     */
 /* Number of kernels this library has launched in this process so far (every <<<>>> of
  * libtsdf_b200.so, all handles, all devices): the bench's `gpu_launches` is a difference of two
  * reads around its timed window.                                              */
@@ -420,14 +411,28 @@ int tsdf_launch_count(int64_t* n);
  * multi-GPU step analysis in DESIGN.md §5.                                        */
 int tsdf_trace_enable(tsdf_vol* v, int enable);
 int tsdf_trace_read(tsdf_vol* v, float* ms4, int cap_frames, int* n_frames);
+/* Per-launch timing of the integrate kernel: when enabled every launch is
+ * bracketed by its own CUDA event pair on the launching stream; read returns
+ * the summed kernel ms and the number of launches since the last reset.     */
 int tsdf_kernel_timing(tsdf_vol* v, int enable);
 int tsdf_kernel_timing_read(tsdf_vol* v, double* sum_ms, int64_t* launches, int reset);
 
+#ifdef TSDF_B200_DEV
+/* ---- development hooks: ONLY in libtsdf_b200_dev.so (built with -DTSDF_B200_DEV) ------------
+ * The product library does not export them and carries no A/B kernel instantiations.          */
+/* Times `iters` back-to-back launches of the integrate kernel on the frame
+ * last uploaded to the handle (volume state keeps evolving) with CUDA events
+ * on the handle's stream; returns average ms per launch.                    */
+int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms);
+/* Selects a kernel variant for A/B evidence (0 = what the product runs); bits in
+ * csrc/integrate.cu launch_integrate and csrc/mesh.cu.                     */
+int tsdf_set_variant(tsdf_vol* v, int variant);
 /* Validation hook: brute-forces the exact-arithmetic forms of the hot loop (shared
  * reciprocal + Markstein division, round-down magic rounding, colour blends) against the
  * IEEE operators on the device.  fails[0..4] = mismatches of {reciprocal, quotient, rounding,
  * general colour blend, integer-weight colour blend (exhaustive)}; all must be 0.  */
 int tsdf_selftest_exactmath(int device, int64_t iters_per_thread, uint64_t seed, int64_t fails[5]);
+#endif /* TSDF_B200_DEV */
 
 #ifdef __cplusplus
 }

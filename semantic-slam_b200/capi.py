@@ -12,6 +12,9 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 # TSDF_B200_LIB: A/B tooling only (tools/variants.py against an older build of the same ABI)
 LIB_PATH = os.environ.get("TSDF_B200_LIB") or os.path.join(HERE, "libtsdf_b200.so")
+# the same sources built with -DTSDF_B200_DEV: A/B kernel variants, tsdf_bench_kernel, the exact-math
+# self-test.  tools/ and the tests that force a code path select it; the product never does.
+DEV_LIB_PATH = os.environ.get("TSDF_B200_DEV_LIB") or os.path.join(HERE, "libtsdf_b200_dev.so")
 
 OK, E_INVALID, E_CUDA, E_NOMEM, E_CAPACITY, E_IO, E_NCCL, E_SINGULAR, E_NODEVICE = range(9)
 SEM_TSDFCU, SEM_FUSIONPY = 0, 1
@@ -122,8 +125,6 @@ SIGNATURES = {
     "tsdf_read_trajectory_kitti": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
     "tsdf_read_frame_ids": (_I, [C.c_char_p, _VP, _I, C.POINTER(_I)]),
     "tsdf_read_associations": (_I, [C.c_char_p, _VP, _VP, _VP, _VP, _I, _I, C.POINTER(_I)]),
-    "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
-    "tsdf_set_variant": (_I, [_VP, _I]),
     "tsdf_timer_start": (_I, [_VP]),
     "tsdf_timer_stop": (_I, [_VP, C.POINTER(_F)]),
     "tsdf_launch_count": (_I, [C.POINTER(_I64)]),
@@ -131,28 +132,44 @@ SIGNATURES = {
     "tsdf_trace_read": (_I, [_VP, _VP, _I, C.POINTER(_I)]),
     "tsdf_kernel_timing": (_I, [_VP, _I]),
     "tsdf_kernel_timing_read": (_I, [_VP, C.POINTER(C.c_double), C.POINTER(_I64), _I]),
+}
+# exported by libtsdf_b200_dev.so only (include/tsdf_b200.h, #ifdef TSDF_B200_DEV)
+DEV_SIGNATURES = {
+    "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
+    "tsdf_set_variant": (_I, [_VP, _I]),
     "tsdf_selftest_exactmath": (_I, [_I, _I64, C.c_uint64, C.POINTER(_I64)]),
 }
 
-_lib = None
+_libs = {}
+_dev_selected = False
 
 
-def load():
-    """Loads the CUDA extension; raises loudly when it has not been built."""
-    global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.exists(LIB_PATH):
+def _open(path, sigs):
+    if not os.path.exists(path):
         raise RuntimeError(
-            f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            f"{path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
             "(make -C semantic-slam_b200/csrc). There is no CPU fallback.")
-    lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
-    for name, (res, args) in SIGNATURES.items():
+    lib = C.CDLL(path)   # RTLD_LOCAL; both libraries are linked -Bsymbolic and may coexist in one process
+    for name, (res, args) in sigs.items():
         fn = getattr(lib, name)
         fn.restype = res
         fn.argtypes = args
-    _lib = lib
     return lib
+
+
+def select(dev):
+    """Chooses which library load() returns from now on (objects already created keep theirs)."""
+    global _dev_selected
+    _dev_selected = bool(dev)
+
+
+def load(dev=None):
+    """Loads the CUDA extension; raises loudly when it has not been built.  dev=None: the library
+    chosen with select() (the product library unless a test / tool selected the dev build)."""
+    dev = _dev_selected if dev is None else bool(dev)
+    if dev not in _libs:
+        _libs[dev] = _open(DEV_LIB_PATH, {**SIGNATURES, **DEV_SIGNATURES}) if dev else _open(LIB_PATH, SIGNATURES)
+    return _libs[dev]
 
 
 class TsdfError(RuntimeError):

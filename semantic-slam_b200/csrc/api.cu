@@ -655,6 +655,7 @@ extern "C" int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s) {
   return TSDF_OK;
 }
 
+#ifdef TSDF_B200_DEV
 extern "C" int tsdf_set_variant(tsdf_vol* v, int variant) {
   REQUIRE(v, "null handle");
   v->variant = variant;
@@ -688,6 +689,7 @@ extern "C" int tsdf_bench_kernel(tsdf_vol* v, int iters, float* avg_ms) {
   v->last_written = (int64_t)*v->h_written;
   return TSDF_OK;
 }
+#endif  // TSDF_B200_DEV
 
 // ---- readback (K4, K5, K7) -------------------------------------------------------------------
 // Slab <-> host arrays in the semantics' reference order.  TSDFCU slab [zl][y][x] is one

@@ -84,7 +84,7 @@ constexpr int MATH_EXACT = 0, MATH_LITERAL = 1;
 // it) fits one TMA box of kStageW x kStageH pixels, one elected thread fetches that box of the
 // prepared frame into shared memory with cp.async.bulk.tensor.2d behind an mbarrier, and the block's
 // gathers read shared memory instead of L1/L2: same pixel index -> same bits (src/tsdf.cu:45).
-// Blocks whose rectangle does not fit keep the __ldg gather.  A/B variant (tsdf_set_variant bit 16):
+// Blocks whose rectangle does not fit keep the __ldg gather.  A/B variant (tsdf_set_variant bit 20, libtsdf_b200_dev.so only):
 // on the C2 / C3 geometries 2 % / 1 % of the in-view blocks fit (a 128-voxel run along z spreads over
 // ~100-200 pixels of parallax), see DESIGN.md §4.1.
 // ---------------------------------------------------------------------------------------
@@ -815,6 +815,7 @@ k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_bl
   integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE, CULL>(P, nullptr, tab, tpr_log2, rows_per_block, flags);
 }
 
+#ifdef TSDF_B200_DEV
 struct TmapParam { alignas(64) unsigned char bytes[128]; };   // a CUtensorMap, by value (param space)
 
 // Sparse-frame kernel with the staged image tile (A/B variant, see `Stage`): colour frames, 4-wide runs.
@@ -827,6 +828,7 @@ k_integrate_staged(const __grid_constant__ LaunchP<1> P, const __grid_constant__
   integrate_body<ZFAST, true, LE_TRUNC, 1, 4, false, MATH_EXACT, WMODE, 2, true>(
       P, nullptr, tab, tpr_log2, rows_per_block, flags, &tm, reinterpret_cast<float4*>(stage_raw));
 }
+#endif  // TSDF_B200_DEV
 
 // ---------------------------------------------------------------------------------------
 // Two frames per volume pass (the off-line keyframe replay of
@@ -1060,6 +1062,7 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
     }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
+#ifdef TSDF_B200_DEV
   if constexpr (COLOR && NF == 1 && VEC == 4 && MATH == MATH_EXACT) {
     if (o.kernel == 1 && o.tmap != nullptr && o.block_test) {
       TmapParam tm;
@@ -1074,9 +1077,12 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
       }
     }
   }
+#endif
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
   else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.free_fast ? 0 : 8));
+#ifdef TSDF_B200_DEV
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+#endif
   CU_LAUNCHED();
   return TSDF_OK;
 }
@@ -1221,11 +1227,14 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
       continue;
     }
     LaunchOpts o1 = o;
-    o1.tmap = (v->variant & 65536) ? frames[i].h_tmap : nullptr;   // bit16: staged image tile (A/B)
+    o1.tmap = (v->variant & (1 << 20)) ? frames[i].h_tmap : nullptr;   // bit20: staged image tile (A/B)
     if (!(v->variant & (64 | 128 | 1024))) o1.kernel = slab_inside_every_frustum(g, frames + i, 1) ? 0 : 1;
+#ifdef TSDF_B200_DEV
     if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st)
                            : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st);
-    else         rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o1, st)
+    else
+#endif
+                 rc = vec4 ? launch_sem<1, 4, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o1, st)
                            : launch_sem<1, 1, MATH_EXACT>(v->zfast, color, wmode, g, frames + i, o1, st);
     if (rc) return rc;
     ++i;

@@ -658,7 +658,7 @@ int mesh_device(tsdf_vol* v, float* d_verts, float* d_norms, uint8_t* d_cols, in
   fill_mesh_params(v, &p);
   if (!(v->mesh_valid && v->mesh_epoch == v->epoch)) {
     v->mesh_valid = false;
-    // bit 16 of the A/B variant forces the scalar pass (tools/variants.py, tests)
+    // bit 16 of the A/B variant forces the scalar pass (tools/, tests; variant is 0 in the product library)
     const bool vec4 = p.n_fast % 4 == 0 && (v->variant & 65536) == 0;
     const bool vec8 = vec4 && p.n_fast % 8 == 0 && (v->variant & 262144) == 0;  // bit 18: 4-wide sweep
     if (vec8 && p.zfast)

@@ -19,11 +19,20 @@ def pytest_configure(config):
 def pkg():
     """The product package; builds the extension when the .so is missing (CPU box)."""
     p = importlib.import_module("semantic-slam_b200")
-    if not os.path.exists(p.capi.LIB_PATH):
+    if not os.path.exists(p.capi.LIB_PATH) or not os.path.exists(p.capi.DEV_LIB_PATH):
         import __graft_entry__ as g
         g.build()
     p.load()
     return p
+
+
+@pytest.fixture
+def dev_lib(pkg):
+    """Tests that force a code path (tsdf_set_variant) run against libtsdf_b200_dev.so: objects created
+    while this fixture is active bind to it."""
+    pkg.capi.select(dev=True)
+    yield pkg
+    pkg.capi.select(dev=False)
 
 
 @pytest.fixture(scope="session")

@@ -11,20 +11,35 @@ import pytest
 from conftest import ROOT, bits
 
 
-def header_functions():
+def header_functions(dev):
+    """Functions declared in the header; dev=True: only those inside #ifdef TSDF_B200_DEV, else the rest."""
     src = open(os.path.join(ROOT, "include", "tsdf_b200.h")).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(tsdf_[a-z0-9_]+)\s*\(", src)))
+    m = re.search(r"#ifdef TSDF_B200_DEV(.*?)#endif", src, flags=re.S)
+    part = m.group(1) if dev else src.replace(m.group(0), "")
+    return sorted(set(re.findall(r"\b(tsdf_[a-z0-9_]+)\s*\(", part)))
 
 
 def test_library_exports_every_declared_symbol(pkg):
-    lib = pkg.load()
-    names = header_functions()
-    assert len(names) >= 45
+    lib = pkg.load(dev=False)
+    names = header_functions(dev=False)
+    assert len(names) >= 65
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/tsdf_b200.h but not exported"
     assert set(names) == set(pkg.capi.SIGNATURES), "ctypes stub and header disagree"
     assert lib.tsdf_version() == 100
+
+
+def test_dev_hooks_are_not_in_the_product_library(pkg):
+    """A/B variants, tsdf_bench_kernel and the exact-math self-test ship only in libtsdf_b200_dev.so."""
+    dev_names = header_functions(dev=True)
+    assert set(dev_names) == set(pkg.capi.DEV_SIGNATURES) and len(dev_names) == 3
+    prod, dev = pkg.load(dev=False), pkg.load(dev=True)
+    for n in dev_names:
+        assert not hasattr(prod, n), f"{n} exported by the product library"
+        assert hasattr(dev, n)
+    for n in header_functions(dev=False):
+        assert hasattr(dev, n)
 
 
 def test_config_struct_layout(pkg):

@@ -10,7 +10,7 @@ from conftest import bits
 from oracle.oracle import SEM_TSDFCU, SEM_FUSIONPY
 from test_parity_gpu import oracle_run, assert_volume_equal
 
-pytestmark = pytest.mark.gpu
+pytestmark = [pytest.mark.gpu, pytest.mark.usefixtures("dev_lib")]   # variants: libtsdf_b200_dev.so
 NO_CULL, FORCE_CULL = 64, 128   # tsdf_set_variant bits (default: chosen per launch by the host)
 
 
@@ -117,7 +117,7 @@ def test_kitti_shaped_config3(pkg, oracle, synth):
         assert np.array_equal(sc, c3[sl].reshape(-1))
 
 
-STAGED = 65536   # tsdf_set_variant bit 16: staged image tile (TMA box in shared memory) in the sparse kernel
+STAGED = 1 << 20   # tsdf_set_variant bit 20: staged image tile (TMA box in shared memory) in the sparse kernel
 
 
 @pytest.mark.parametrize("sem", [SEM_FUSIONPY, SEM_TSDFCU])

@@ -249,7 +249,7 @@ def test_gpu_mesh_capacity_and_device_outputs(pkg):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("sem", [SEM_FUSIONPY, SEM_TSDFCU])
-def test_gpu_mesh_scalar_and_vector_sweeps_agree(pkg, oracle, sem):
+def test_gpu_mesh_scalar_and_vector_sweeps_agree(pkg, oracle, sem, dev_lib):
     """Fast axes that are a multiple of 8 / of 4 take k_mc_mark8 / k_mc_mark4 (a thread owns 8 / 4 voxels);
     variant bit 16 forces the scalar sweep, bit 18 the 4-wide one.  Both must give the oracle's mesh — also where a 128-voxel
     chunk straddles rows (fast axis 36) and where the volume ends inside a tile."""

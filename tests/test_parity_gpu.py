@@ -469,7 +469,7 @@ def test_full_size_properties_c1(pkg, synth):
             assert np.array_equal(rgb, np.stack([cc & 255, (cc >> 8) & 255, cc >> 16], 1).astype(np.uint8))
 
 
-def test_full_size_properties_c2(pkg, synth):
+def test_full_size_properties_c2(pkg, synth, dev_lib):
     """BASELINE config 2 size (512^3, 1 cm, fr3_office keyframe poses) through size-independent
     properties: k frames fused into one pass == k single passes (bit for bit, all three arrays),
     the segment cull never changes a result, and N_written adds up."""
@@ -563,7 +563,7 @@ def test_against_reference_gpu_kernel(pkg, oracle, synth):
 
 
 @pytest.mark.parametrize("sem", [SEM_TSDFCU, SEM_FUSIONPY])
-def test_more_than_2_31_voxels(pkg, oracle, synth, sem):
+def test_more_than_2_31_voxels(pkg, oracle, synth, sem, dev_lib):
     """Maximum sizes: a 1280 x 1280 x 1536 grid (2.52 G voxels > 2^31; 20-30 GB of HBM) — every
     linear index, byte offset and extraction index must be 64-bit.  The volume is too large to
     mirror on the host, so windows of the storage order (tsdf_download_range) are compared bit for

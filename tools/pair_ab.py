@@ -7,6 +7,7 @@ import ctypes as C, importlib, json, os, sys
 import numpy as np
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 pkg = importlib.import_module("semantic-slam_b200")
+pkg.capi.select(dev=True)   # A/B variants live in libtsdf_b200_dev.so only
 synth, lib, check = pkg.synth, pkg.load(), pkg.capi.check
 scene = sys.argv[1] if len(sys.argv) > 1 else "full"
 dim = int(sys.argv[2]) if len(sys.argv) > 2 else 1024
