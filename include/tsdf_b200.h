@@ -432,6 +432,10 @@ int tsdf_set_variant(tsdf_vol* v, int variant);
  * IEEE operators on the device.  fails[0..4] = mismatches of {reciprocal, quotient, rounding,
  * general colour blend, integer-weight colour blend (exhaustive)}; all must be 0.  */
 int tsdf_selftest_exactmath(int device, int64_t iters_per_thread, uint64_t seed, int64_t fails[5]);
+/* Work counters of the sparse integrate kernel since the last enable: out[0..6] = {blocks, blocks
+ * skipped by the block-level hull test, warp row segments visited, segments culled by the warp test,
+ * runs (4 voxels) projected, runs gathered, runs with an update}; enable != 0 (re)arms them.   */
+int tsdf_debug_counters(tsdf_vol* v, int enable, uint64_t* out);
 #endif /* TSDF_B200_DEV */
 
 #ifdef __cplusplus

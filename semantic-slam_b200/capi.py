@@ -138,6 +138,7 @@ DEV_SIGNATURES = {
     "tsdf_bench_kernel": (_I, [_VP, _I, C.POINTER(_F)]),
     "tsdf_set_variant": (_I, [_VP, _I]),
     "tsdf_selftest_exactmath": (_I, [_I, _I64, C.c_uint64, C.POINTER(_I64)]),
+    "tsdf_debug_counters": (_I, [_VP, _I, _VP]),
 }
 
 _libs = {}

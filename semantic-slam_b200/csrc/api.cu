@@ -181,6 +181,7 @@ static void free_vol(tsdf_vol* v) {
   cudaFree(v->d_tsdf); cudaFree(v->d_weight); cudaFree(v->d_color);
   cudaFree(v->d_written); cudaFree(v->d_scratch); cudaFree(v->d_mesh);
   v->out.release();
+  cudaFree(v->d_dbg);
   if (v->h_written) cudaFreeHost(v->h_written);
   for (cudaEvent_t e : {v->ev_k0, v->ev_k1, v->ev_u0, v->ev_u1, v->ev_t0, v->ev_t1}) if (e) cudaEventDestroy(e);
   for (cudaEvent_t e : v->kev) cudaEventDestroy(e);
@@ -656,6 +657,28 @@ extern "C" int tsdf_get_stats(tsdf_vol* v, tsdf_stats* s) {
 }
 
 #ifdef TSDF_B200_DEV
+// Work counters of the sparse kernel: {blocks, blocks skipped by the hull test, warp row segments,
+// segments culled by the warp test, runs projected, runs gathered, runs with an update, -}.
+// enable allocates / zeroes them; out (8 values) may be null.
+extern "C" int tsdf_debug_counters(tsdf_vol* v, int enable, uint64_t* out) {
+  REQUIRE(v, "null handle");
+  DeviceGuard g(v->cfg.device);
+  int rc = tsdf_sync(v);
+  if (rc) return rc;
+  if (out) {
+    if (v->d_dbg) CU_CHECK(cudaMemcpy(out, v->d_dbg, 64, cudaMemcpyDeviceToHost));
+    else memset(out, 0, 64);
+  }
+  if (enable) {
+    if (!v->d_dbg) CU_CHECK(cudaMalloc(&v->d_dbg, 64));
+    CU_CHECK(cudaMemset(v->d_dbg, 0, 64));
+  } else if (v->d_dbg) {
+    cudaFree(v->d_dbg);
+    v->d_dbg = nullptr;
+  }
+  return TSDF_OK;
+}
+
 extern "C" int tsdf_set_variant(tsdf_vol* v, int variant) {
   REQUIRE(v, "null handle");
   v->variant = variant;

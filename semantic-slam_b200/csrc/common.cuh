@@ -81,6 +81,7 @@ struct GridP {        // one volume slab
   float* weight;
   float* color;                  // may be null
   unsigned long long* written;   // device counter (exact N_written)
+  unsigned long long* dbg;       // dev build only: 8 work counters of the sparse kernel (tsdf_debug_counters), else null
 };
 
 struct BatchDesc {    // one active instance of a batched launch (lives in global memory)
@@ -166,6 +167,7 @@ struct tsdf_vol {
   int64_t last_written = 0;
   int64_t last_frames_in_launch = 1;
   int variant = 0;
+  unsigned long long* d_dbg = nullptr;   // dev build: work counters of the sparse kernel
   bool dev_hold = false;       // set by tsdf_set_variant: prepared frames stay intact after their launch
   // integer-weight bookkeeping: true while every stored weight is provably an integer
   // (only obs_weight == 1 integrations since the last reset); w_bound >= max stored weight

@@ -544,8 +544,15 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     }
   }
   __syncthreads();
-  if constexpr (CULL == 2 && NF == 1)
+#ifdef TSDF_B200_DEV
+#define DBG_ADD(k, n) do { if (g.dbg) atomicAdd(g.dbg + (k), (unsigned long long)(n)); } while (0)
+#else
+#define DBG_ADD(k, n) do { } while (0)
+#endif
+  if constexpr (CULL == 2 && NF == 1) {
+    if (threadIdx.x == 0) { DBG_ADD(0, 1); if (blk_test && blk_skip) DBG_ADD(1, 1); }
     if (blk_test && blk_skip) return;   // block-uniform
+  }
   Stage stg;
   stg.tile = stage_tile; stg.on = 0; stg.x0 = 0; stg.y0 = 0;
   if constexpr (STAGE) {
@@ -661,6 +668,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     const int r = row0 + lr;
     if (r >= n_rows) break;
     if constexpr (CULL != 0) {
+      if ((threadIdx.x & 31) == 0) { DBG_ADD(2, 1); if (rowmask & 1ull) DBG_ADD(3, 1); }
       if (rowmask & 1ull) { any_prev = false; continue; }
     }
     if (pf) {
@@ -731,6 +739,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           // CULL == 2 (sparse frames): a run that projects outside the image stops before the
           // gather.  CULL == 0 (dense frames): no early-out, the run is branch-free from here, so
           // the four gathers issue back to back.
+          if constexpr (CULL == 2) { DBG_ADD(4, 1); if (in_image) DBG_ADD(5, 1); }
           if (CULL == 0 || in_image) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
@@ -745,6 +754,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       }
     }
     any_prev = any;
+    if constexpr (CULL == 2) { if (any) DBG_ADD(6, 1); }
     if (!any) continue;  // no volume traffic for a run with no update
 
     const int64_t base = (int64_t)r * g.n_fast + f0;
@@ -1151,6 +1161,7 @@ void fill_grid_params(const tsdf_vol* v, bool color, GridP* g) {
   g->W = c.im_w; g->H = c.im_h;
   g->tsdf = v->d_tsdf; g->weight = v->d_weight; g->color = color ? v->d_color : nullptr;
   g->written = v->d_written + (v->lseq % kWrittenRing);
+  g->dbg = v->d_dbg;
 }
 
 // Host-side, double precision: do all 8 corner voxels of the slab project at least one pixel

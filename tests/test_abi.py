@@ -33,7 +33,7 @@ def test_library_exports_every_declared_symbol(pkg):
 def test_dev_hooks_are_not_in_the_product_library(pkg):
     """A/B variants, tsdf_bench_kernel and the exact-math self-test ship only in libtsdf_b200_dev.so."""
     dev_names = header_functions(dev=True)
-    assert set(dev_names) == set(pkg.capi.DEV_SIGNATURES) and len(dev_names) == 3
+    assert set(dev_names) == set(pkg.capi.DEV_SIGNATURES) and len(dev_names) == 4
     prod, dev = pkg.load(dev=False), pkg.load(dev=True)
     for n in dev_names:
         assert not hasattr(prod, n), f"{n} exported by the product library"
