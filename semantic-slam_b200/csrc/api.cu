@@ -360,6 +360,8 @@ int OutBuffers::need_host(size_t bytes) {
   return TSDF_OK;
 }
 void OutBuffers::release() {
+  for (int i = 0; i < 2; ++i) { if (ev[i]) cudaEventDestroy(ev[i]); ev[i] = nullptr; }
+  ev_dev = -1;
   for (int i = 0; i < 4; ++i) { if (d[i]) cudaFree(d[i]); d[i] = nullptr; dcap[i] = 0; }
   if (h) cudaFreeHost(h);
   h = nullptr; hcap = 0;
@@ -376,8 +378,18 @@ int copy_to_host(OutBuffers* ob, void* dst, const void* d_src, size_t bytes, cud
   constexpr size_t kChunk = 4u << 20;
   int rc = ob->need_host(2 * kChunk);
   if (rc) return rc;
-  static thread_local cudaEvent_t ev[2] = {nullptr, nullptr};
-  for (int i = 0; i < 2; ++i) if (!ev[i]) CU_CHECK(cudaEventCreateWithFlags(&ev[i], cudaEventDisableTiming));
+  // events belong to a device: (re)create them on the one `st` lives on (= the current device)
+  int cur = 0;
+  CU_CHECK(cudaGetDevice(&cur));
+  if (ob->ev_dev != cur) {
+    for (int i = 0; i < 2; ++i) {
+      if (ob->ev[i]) cudaEventDestroy(ob->ev[i]);
+      ob->ev[i] = nullptr;
+      CU_CHECK(cudaEventCreateWithFlags(&ob->ev[i], cudaEventDisableTiming));
+    }
+    ob->ev_dev = cur;
+  }
+  cudaEvent_t* ev = ob->ev;
   const size_t n_chunks = (bytes + kChunk - 1) / kChunk;
   auto issue = [&](size_t c) -> cudaError_t {
     const size_t off = c * kChunk, len = std::min(kChunk, bytes - off);

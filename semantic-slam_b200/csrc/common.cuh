@@ -18,6 +18,7 @@ void tsdf_set_error(const char* fmt, ...);  // thread-local, printf style
   do {                                                                                    \
     cudaError_t e__ = (expr);                                                             \
     if (e__ != cudaSuccess) {                                                             \
+      cudaGetLastError(); /* clear it: a later launch check must not report this failure */ \
       tsdf_set_error("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e__)); \
       return e__ == cudaErrorMemoryAllocation ? TSDF_E_NOMEM : TSDF_E_CUDA;               \
     }                                                                                     \
@@ -103,6 +104,8 @@ struct OutBuffers {
   size_t dcap[4] = {0, 0, 0, 0};
   void* h = nullptr;       // pinned
   size_t hcap = 0;
+  cudaEvent_t ev[2] = {nullptr, nullptr};   // chunk-landed events of the staged copy (device of first use)
+  int ev_dev = -1;
   int need_dev(int i, size_t bytes);    // TSDF status; contents are NOT preserved when it grows
   int need_host(size_t bytes);
   void release();
