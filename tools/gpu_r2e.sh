@@ -4,7 +4,7 @@
 # single-process group throughput.
 O=gpurun_out/r2e; mkdir -p $O
 nvidia-smi -L > $O/gpus.txt
-timeout 1500 python -m pytest tests/test_multigpu.py tests/test_group_gpu.py tests/test_cpp_host.py -m gpu -v --timeout 600 > $O/pytest_multigpu.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
+timeout 700 python -m pytest tests/test_multigpu.py tests/test_group_gpu.py tests/test_cpp_host.py -m gpu -v --timeout 300 > $O/pytest_multigpu.log 2>&1; echo "pytest rc=$?" | tee -a $O/rc.txt
 grep -E "PASSED|FAILED|SKIPPED|passed|failed|dist_worker" $O/pytest_multigpu.log | tail -30
 bench() { # N tag env...
   N=$1; tag=$2; shift; shift
@@ -21,20 +21,11 @@ except Exception as e: print(sys.argv[1], 'ERR', e)
 PY
 }
 bench 8 n8 TSDF_BENCH_TRACE=r2e
-bench 8 n8b X=1
 bench 4 n4 X=1
-bench 2 n2 X=1
 timeout 300 python bench.py --steps 20 --warmup 5 --no-extras > $O/bench_n1.json 2> $O/bench_n1.err; echo "bench n1 rc=$?" | tee -a $O/rc.txt
 python - <<'PY'
 import json
 d=json.loads([l for l in open('gpurun_out/r2e/bench_n1.json') if l.startswith('{')][-1])
 print('n1', round(d['value'],1), d['ms_per_step'], 'kernel', d['roofline']['kernel_ms'], 'frac', d['roofline']['frac'], d['clocks'])
 PY
-timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29833 \
-  bench.py --impl reference --gpus 2 --steps 4 --warmup 1 > $O/bench_ref_torchrun.json 2> $O/bench_ref_torchrun.err; echo "ref rc=$?" | tee -a $O/rc.txt
-python - <<'PY'
-import json
-d=json.loads([l for l in open('gpurun_out/r2e/bench_ref_torchrun.json') if l.startswith('{')][-1])
-print('ref under torchrun', d['value'], d['ms_per_step'], d['cpu_baseline']['cores'], d['cpu_baseline']['omp_num_threads_env'])
-PY
-for n in 8 4 2; do timeout 300 python tools/group_bench.py $n 40 2>&1 | tail -1 | tee -a $O/group_bench.jsonl; done
+for n in 8; do timeout 300 python tools/group_bench.py $n 40 2>&1 | tail -1 | tee -a $O/group_bench.jsonl; done
