@@ -688,7 +688,11 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     Hit hit[NF][VEC];
     bool any = false;
     // dense kernel, 4-wide runs: the probes leave the raw diff in Hit::dist and update_run4 finishes :53
+#ifdef KI_LEGACY_UPDATE   // A/B builds only: the round-1 update (per-voxel update_voxel + select)
+    constexpr bool kRun4 = false;
+#else
     constexpr bool kRun4 = CULL == 0 && VEC == 4 && MATH == MATH_EXACT && NF == 1;
+#endif
     bool raw_diff = kRun4;
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
@@ -823,6 +827,238 @@ __global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)   // 64 registers: fou
 k_integrate(const __grid_constant__ LaunchP<NF> P, int tpr_log2, int rows_per_block, int flags) {
   __shared__ float4 tab[kMaxRowsPerBlock * NF * (ZFAST ? 1 : 2)];
   integrate_body<ZFAST, COLOR, LE_TRUNC, NF, VEC, false, MATH, WMODE, CULL>(P, nullptr, tab, tpr_log2, rows_per_block, flags);
+}
+
+// ---------------------------------------------------------------------------------------
+// Sparse-frame kernel with QUARTER-SEGMENT work lists (default for sparse frames on compact tiles).
+// The plain sparse kernel culls a 128-voxel row segment only when all four of its 32-voxel quarter
+// boxes are culled, and then probes the whole segment: measured on the C2 / C3 shapes
+// (tools/sparse_counters.py, profiles/r2_v3_sparse_counters.jsonl) only 37 % / 16 % of the runs it
+// projects reach the gather, because segments straddling the frustum, an occluder or the depth
+// range drag their dead quarters along — and the kernel is issue-bound, so dead lanes cost what
+// live ones do.  Here the quarter tests' ballots become a per-warp WORK LIST of live (row, quarter)
+// items (64 bits: 16 rows x 4 quarters), and every warp iteration takes FOUR items, one per group of
+// 8 lanes — 8 lanes x 4 voxels = one quarter, still 128-bit accesses and whole 128-byte lines.  A
+// lane's fast-axis position now changes per item, so the fast-axis terms of the block's 128-voxel
+// window live in a shared-memory table next to the row table (one LDS.128 per voxel).
+// Same tests, same per-voxel arithmetic, same bits as the plain kernels (tests/test_cull_gpu.py).
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ int nth_set_bit64(unsigned long long m, int n) {   // n-th (0-based) set bit, n < popc(m)
+  const unsigned lo = (unsigned)m, hi = (unsigned)(m >> 32);
+  const int pl = __popc(lo);
+  return n < pl ? (int)__fns(lo, 0, n + 1) : 32 + (int)__fns(hi, 0, n - pl + 1);
+}
+
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)
+k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flags) {
+  constexpr int NT = ZFAST ? 1 : 2;
+  constexpr int VEC = 4;
+  constexpr int kSeg = 32 * VEC;                     // voxels of the block's fast-axis window
+  __shared__ float4 tab[kMaxRowsPerBlock * NT];      // row terms
+  __shared__ float4 tabf[kSeg];                      // fast-axis terms {p0, p1, p2, -} of the window
+  __shared__ int blk_skip;
+  const GridP& g = P.g;
+  const FrameP& F = P.f[0];
+  const int pf = flags & 3;
+  const int n_rows = g.n_mid * g.n_slow;
+  const int row0 = blockIdx.x * rows_per_block;
+  if (row0 >= n_rows) return;
+  if (F.skip != nullptr && *reinterpret_cast<const volatile int*>(F.skip) != 0) return;
+  const int ka = blockIdx.y * kSeg;                  // first voxel of the window
+  int kb = ka + kSeg - 1;
+  if (kb > g.n_fast - 1) kb = g.n_fast - 1;
+  const float* c = F.c;
+
+  // ---- prologue 0: block-level hull test (warp 0), as in integrate_body ------------------------
+  const bool blk_test = (flags & 4) != 0;
+  if (blk_test && threadIdx.x < 32) {
+    const int r_last = min(row0 + rows_per_block, n_rows) - 1;
+    const int s0 = row0 / g.n_mid, s1 = r_last / g.n_mid;
+    const int mlo = s0 == s1 ? row0 - s0 * g.n_mid : 0;
+    const int mhi = s0 == s1 ? r_last - s0 * g.n_mid : g.n_mid - 1;
+    float lo[3], hi[3];
+    float4 q[4], z4[2];
+    float elo[3], ehi[3], zlo[3] = {0.f, 0.f, 0.f}, zhi[3] = {0.f, 0.f, 0.f};
+    bool finite = true;
+    if constexpr (ZFAST) {
+      row_terms<ZFAST>(g, c, s0, mlo, q[0], z4[0]);
+      row_terms<ZFAST>(g, c, s0, mhi, q[1], z4[0]);
+      row_terms<ZFAST>(g, c, s1, mlo, q[2], z4[0]);
+      row_terms<ZFAST>(g, c, s1, mhi, q[3], z4[0]);
+      elo[0] = fminf(fminf(q[0].x, q[1].x), fminf(q[2].x, q[3].x)); ehi[0] = fmaxf(fmaxf(q[0].x, q[1].x), fmaxf(q[2].x, q[3].x));
+      elo[1] = fminf(fminf(q[0].y, q[1].y), fminf(q[2].y, q[3].y)); ehi[1] = fmaxf(fmaxf(q[0].y, q[1].y), fmaxf(q[2].y, q[3].y));
+      elo[2] = fminf(fminf(q[0].z, q[1].z), fminf(q[2].z, q[3].z)); ehi[2] = fmaxf(fmaxf(q[0].z, q[1].z), fmaxf(q[2].z, q[3].z));
+      const float chk = ((q[0].x + q[1].x) + (q[2].x + q[3].x)) + ((q[0].y + q[1].y) + (q[2].y + q[3].y)) +
+                        ((q[0].z + q[1].z) + (q[2].z + q[3].z));
+      finite = fabsf(chk) <= 3.0e38f;   // (fminf / fmaxf drop NaN operands: a non-finite corner disables the test)
+    } else {
+      float4 ya, yb, za, zb;
+      row_terms<ZFAST>(g, c, s0, mlo, ya, za);
+      row_terms<ZFAST>(g, c, s1, mhi, yb, zb);
+      elo[0] = fminf(ya.x, yb.x); elo[1] = fminf(ya.y, yb.y); elo[2] = fminf(ya.z, yb.z);
+      ehi[0] = fmaxf(ya.x, yb.x); ehi[1] = fmaxf(ya.y, yb.y); ehi[2] = fmaxf(ya.z, yb.z);
+      zlo[0] = fminf(za.x, zb.x); zlo[1] = fminf(za.y, zb.y); zlo[2] = fminf(za.z, zb.z);
+      zhi[0] = fmaxf(za.x, zb.x); zhi[1] = fmaxf(za.y, zb.y); zhi[2] = fmaxf(za.z, zb.z);
+      const float chk = ((ya.x + yb.x) + (ya.y + yb.y)) + ((ya.z + yb.z) + (za.x + zb.x)) + ((za.y + zb.y) + (za.z + zb.z));
+      finite = fabsf(chk) <= 3.0e38f;
+    }
+    float pa[3], pb[3];
+    fast_terms<ZFAST>(c, fast_coord<ZFAST>(g, ka), pa[0], pa[1], pa[2]);
+    fast_terms<ZFAST>(c, fast_coord<ZFAST>(g, kb), pb[0], pb[1], pb[2]);
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const float plo = fminf(pa[k], pb[k]), phi = fmaxf(pa[k], pb[k]);
+      if constexpr (ZFAST) { lo[k] = elo[k] + plo; hi[k] = ehi[k] + phi; }
+      else                 { lo[k] = (plo + elo[k]) + zlo[k]; hi[k] = (phi + ehi[k]) + zhi[k]; }
+    }
+    const bool skip = finite && box_is_skipped(F, g, lo[0], lo[1], lo[2], hi[0], hi[1], hi[2],
+                                               reinterpret_cast<const int*>(F.dmax));
+    if (threadIdx.x == 0) blk_skip = skip;
+  }
+  // ---- prologue 1: row table (warps 1-7 while warp 0 tests) and fast-axis table -----------------
+  const int t_first = blk_test ? 32 : 0;
+  for (int lr = (int)threadIdx.x - t_first; lr < rows_per_block; lr += kThreads - t_first) {
+    const int r = row0 + lr;
+    if (lr >= 0 && r < n_rows) {
+      const int slow = r / g.n_mid, mid = r - slow * g.n_mid;
+      float4 e0, e1;
+      row_terms<ZFAST>(g, c, slow, mid, e0, e1);
+      tab[lr * NT] = e0;
+      if constexpr (!ZFAST) tab[lr * NT + 1] = e1;
+    }
+  }
+  if (threadIdx.x >= kThreads - kSeg) {   // the last four warps (not warp 0)
+    const int k = (int)threadIdx.x - (kThreads - kSeg);
+    float p0, p1, p2;
+    fast_terms<ZFAST>(c, fast_coord<ZFAST>(g, ka + k), p0, p1, p2);
+    tabf[k] = make_float4(p0, p1, p2, 0.0f);
+  }
+  __syncthreads();
+#ifdef TSDF_B200_DEV
+  if (threadIdx.x == 0) { DBG_ADD(0, 1); if (blk_test && blk_skip) DBG_ADD(1, 1); }
+#endif
+  if (blk_test && blk_skip) return;   // block-uniform
+
+  // ---- prologue 2: the warp's work list -------------------------------------------------------
+  const int lane = threadIdx.x & 31;
+  const int tr = threadIdx.x >> 5;            // warp = row phase: rows tr, tr + 8, ...
+  constexpr int rp = kThreads / 32;
+  const int n_iter = (rows_per_block - tr + rp - 1) / rp;   // <= 16
+  unsigned long long work = 0ull;             // bit Q * 16 + it: quarter Q of row iteration `it` is live
+  {
+    const int it = lane & 15, half = lane >> 4;
+    const int lr = tr + it * rp;
+    const bool rowok = it < n_iter && row0 + lr < n_rows;
+    bool live[2] = {false, false};
+    if (rowok) {
+      const float4 ea = tab[lr * NT];
+      float4 eb = ea;
+      if constexpr (!ZFAST) eb = tab[lr * NT + 1];
+#pragma unroll
+      for (int q = 0; q < 2; ++q) {
+        const int qa = ka + (2 * half + q) * 32;
+        const int qb = qa + 31 < kb ? qa + 31 : kb;
+        if (qa <= kb) {
+          const float4 fa = tabf[qa - ka], fb = tabf[qb - ka];
+          float xa, ya, za, xb, yb, zb;
+          cam_coords<ZFAST>(ea, eb, fa.x, fa.y, fa.z, xa, ya, za);
+          cam_coords<ZFAST>(ea, eb, fb.x, fb.y, fb.z, xb, yb, zb);
+          live[q] = !box_is_skipped(F, g, xa, ya, za, xb, yb, zb, reinterpret_cast<const int*>(F.dmax));
+        }
+      }
+    }
+    const unsigned b0 = __ballot_sync(0xffffffffu, live[0]);   // bit L: quarter 2 * (L >> 4)     of row L & 15
+    const unsigned b1 = __ballot_sync(0xffffffffu, live[1]);   // bit L: quarter 2 * (L >> 4) + 1 of row L & 15
+    work = (unsigned long long)(b0 & 0xffffu) | ((unsigned long long)(b1 & 0xffffu) << 16) |
+           ((unsigned long long)(b0 >> 16) << 32) | ((unsigned long long)(b1 >> 16) << 48);
+  }
+  const int total = __popcll(work);
+#ifdef TSDF_B200_DEV
+  if (lane == 0) { DBG_ADD(2, 4 * n_iter); DBG_ADD(3, 4 * n_iter - total); }
+#endif
+
+  // ---- main loop: four live quarters per warp iteration ------------------------------------------
+  unsigned int n_written = 0;
+  const int grp = lane >> 3, sub = lane & 7;
+  for (int t0 = 0; t0 < total; t0 += 4) {
+    const int item = t0 + grp;
+    if (item >= total) continue;
+    const int bit = nth_set_bit64(work, item);
+    const int Q = bit >> 4, it = bit & 15;
+    const int lr = tr + it * rp;
+    const int r = row0 + lr;
+    const int kf = Q * 32 + sub * VEC;              // offset in the window
+    const int f0 = ka + kf;
+    if (f0 >= g.n_fast) continue;                   // ragged fast axis (n_fast % 4 == 0: whole runs)
+    const float4 ea = tab[lr * NT];
+    float4 eb = ea;
+    if constexpr (!ZFAST) eb = tab[lr * NT + 1];
+    float camx[VEC], camy[VEC], camz[VEC];
+    bool odd = false;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      const float4 fp = tabf[kf + j];
+      cam_coords<ZFAST>(ea, eb, fp.x, fp.y, fp.z, camx[j], camy[j], camz[j]);
+      odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
+    }
+    Hit hit[VEC];
+    bool any = false;
+    if (__builtin_expect(odd, 0)) {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        hit[j] = probe_literal_cold<COLOR, LE_TRUNC, false>(F.img, F.fx, F.cx, F.fy, F.cy, g.trunc, g.W, g.H, nullptr,
+                                                            camx[j], camy[j], camz[j]);
+        any = any || hit[j].ok;
+      }
+    } else {
+      Proj pr[VEC];
+      bool in_image = false;
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        pr[j] = project_exact<true>(F, g, camx[j], camy[j], camz[j]);
+        in_image = in_image || pr[j].ok;
+      }
+      DBG_ADD(4, 1);
+      if (!in_image) continue;                      // the run projects outside the image: no gather
+      DBG_ADD(5, 1);
+      const int64_t pb = (int64_t)r * g.n_fast + f0;
+      if (pf) {   // the gather's latency hides part of the volume loads' (most gathered runs are updated)
+        prefetch_line<true>(g.tsdf + pb, 1);
+        prefetch_line<true>(g.weight + pb, 1);
+        if constexpr (COLOR) prefetch_line<true>(g.color + pb, 1);
+      }
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) {
+        hit[j] = sample_exact<COLOR, LE_TRUNC, false>(F, g, nullptr, pr[j], camz[j]);
+        any = any || hit[j].ok;
+      }
+    }
+    if (!any) continue;                             // no volume traffic for a run with no update
+    DBG_ADD(6, 1);
+    const int64_t base = (int64_t)r * g.n_fast + f0;
+    float t[VEC], w[VEC], col[VEC];
+    load_vec<VEC>(g.tsdf + base, t);
+    load_vec<VEC>(g.weight + base, w);
+    if constexpr (COLOR) load_vec<VEC>(g.color + base, col);
+    else {
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) col[j] = 0.0f;
+    }
+    const float obs = F.obs_weight;
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      if (hit[j].ok) {
+        update_voxel<COLOR, MATH_EXACT, WMODE>(t[j], w[j], col[j], hit[j], obs);
+        ++n_written;
+      }
+    }
+    store_vec<VEC>(g.tsdf + base, t);
+    store_vec<VEC>(g.weight + base, w);
+    if constexpr (COLOR) store_vec<VEC>(g.color + base, col);
+  }
+  for (int o = 16; o > 0; o >>= 1) n_written += __shfl_down_sync(0xffffffffu, n_written, o);
+  if (lane == 0 && n_written) atomicAdd(g.written, (unsigned long long)n_written);
 }
 
 #ifdef TSDF_B200_DEV
@@ -1001,6 +1237,7 @@ struct LaunchOpts {
   bool compact = true;    // sparse kernel: compact block tiles (one warp per row segment)
   bool block_test = true; // sparse kernel: block-level hull test before the per-warp tests
   bool free_fast = true;  // dense kernels: exact free-space short cuts of update_run4
+  bool quarters = true;   // sparse kernel: quarter-segment work lists (k_integrate_q)
   const void* tmap = nullptr;  // sparse kernel: CUtensorMap of the prepared frame => staged image tile (A/B)
 };
 
@@ -1088,6 +1325,15 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
     }
   }
 #endif
+  if constexpr (NF == 1 && VEC == 4 && MATH == MATH_EXACT) {
+    // sparse frames on compact tiles (one warp per 128-voxel segment, <= 16 row iterations per warp):
+    // the quarter work-list kernel
+    if (o.kernel == 1 && o.quarters && o.compact && q.tpr_log2 == 5 && q.rows_per_block <= 16 * (kThreads / 32)) {
+      k_integrate_q<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.rows_per_block, pf | (o.block_test ? 4 : 0));
+      CU_LAUNCHED();
+      return TSDF_OK;
+    }
+  }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
   else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.free_fast ? 0 : 8));
 #ifdef TSDF_B200_DEV
@@ -1211,6 +1457,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   o.compact = (v->variant & 4096) == 0;      // bit12: old block shape (row-major, up to 256 threads per row)
   o.block_test = (v->variant & 8192) == 0;   // bit13: block-level hull test off
   o.free_fast = (v->variant & 32768) == 0;   // bit15: free-space short cuts of the dense kernels off
+  o.quarters = (v->variant & (1 << 21)) == 0; // bit21: plain sparse kernel instead of the quarter work lists
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
