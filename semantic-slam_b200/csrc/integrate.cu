@@ -208,8 +208,7 @@ __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, f
   return p;
 }
 
-// RAW_DIFF: h.dist receives diff itself (:48); the caller turns it into :53's dist (update_run4).
-template <bool COLOR, bool LE_TRUNC, bool MASK, bool RAW_DIFF = false>
+template <bool COLOR, bool LE_TRUNC, bool MASK>
 __device__ __forceinline__ Hit sample_exact(const FrameP& f, const GridP& g, const uint8_t* mask, const Proj& p,
                                             float camz, const Stage* st = nullptr) {
   Hit h;
@@ -220,8 +219,7 @@ __device__ __forceinline__ Hit sample_exact(const FrameP& f, const GridP& g, con
   const float diff = d - camz;                            // :48
   if constexpr (LE_TRUNC) ok = ok && !(diff <= -g.trunc); // :49
   else                    ok = ok && !(diff < -g.trunc);
-  if constexpr (RAW_DIFF) h.dist = diff;
-  else                    h.dist = fminf(1.0f, em::div_rn(diff, g.trunc, g.inv_trunc));  // :53
+  h.dist = fminf(1.0f, em::div_rn(diff, g.trunc, g.inv_trunc));  // :53
   h.ok = ok;
   return h;
 }
@@ -354,62 +352,6 @@ __device__ __forceinline__ void update_voxel(float& t, float& w, float& col, con
       if constexpr (WMODE == 1) col = em::blend_intw(col, h.c0, h.c1, h.c2, w0, yw);
       else                      col = em::blend_exact(col, h.c0, h.c1, h.c2, w0, w1, yw);
     }
-  }
-}
-
-// The dense kernels' update of one run of 4 voxels by one frame, src/tsdf.cu:53-57 (+ colour), computed
-// for every voxel and selected by its ok flag (no divergence bookkeeping around ~60 instructions).
-// hit[j].dist holds the raw diff of :48.  Two exact short cuts for free space, where most updated
-// voxels of any frame lie (FREE; per thread, on the whole run):
-//   * diff >= trunc (or NaN) for every updated voxel: :53's fmin(1, diff / trunc) is 1 — RN division is
-//     monotone and trunc / trunc == 1, and fminf drops a NaN — so the four quotients are skipped;
-//   * then, with obs_weight == 1 (WMODE 1) and stored tsdf == 1: :57's (1 * w0 + 1) / (w0 + 1) is w1 / w1
-//     == 1 — the stored value stays, and the four tsdf quotients are skipped too.
-template <bool COLOR, int WMODE, bool FREE>
-__device__ __forceinline__ void update_run4(const GridP& g, const Hit (&hit)[4], float obs, float (&t)[4], float (&w)[4],
-                                            float (&col)[4], unsigned int& n_written, bool& any) {
-  bool far = FREE;
-  if constexpr (FREE) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) far = far && (!hit[j].ok || !(hit[j].dist < g.trunc));
-  }
-  float dist[4];
-  if (far) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) dist[j] = 1.0f;
-  } else {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) dist[j] = fminf(1.0f, em::div_rn(hit[j].dist, g.trunc, g.inv_trunc));   // :53
-  }
-  bool t_stays = FREE && WMODE == 1 && far;
-  if constexpr (FREE && WMODE == 1) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) t_stays = t_stays && (!hit[j].ok || t[j] == 1.0f);
-  }
-  float yw[4], w1[4];
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    w1[j] = w[j] + obs;                                   // :55
-    if (COLOR || !t_stays) yw[j] = em::rcp_rn(w1[j]);
-  }
-  if (!t_stays) {
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float nt = em::div_rn(t[j] * w[j] + dist[j], w1[j], yw[j]);   // :57
-      t[j] = hit[j].ok ? nt : t[j];
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    const bool ok = hit[j].ok;
-    if constexpr (COLOR) {
-      const float nc = WMODE == 1 ? em::blend_intw(col[j], hit[j].c0, hit[j].c1, hit[j].c2, w[j], yw[j])
-                                  : em::blend_exact(col[j], hit[j].c0, hit[j].c1, hit[j].c2, w[j], w1[j], yw[j]);
-      col[j] = ok ? nc : col[j];
-    }
-    w[j] = ok ? w1[j] : w[j];                             // :56
-    n_written += ok ? 1u : 0u;
-    any = any || ok;
   }
 }
 
@@ -687,13 +629,6 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
     }
     Hit hit[NF][VEC];
     bool any = false;
-    // dense kernel, 4-wide runs: the probes leave the raw diff in Hit::dist and update_run4 finishes :53
-#ifdef KI_LEGACY_UPDATE   // A/B builds only: the round-1 update (per-voxel update_voxel + select)
-    constexpr bool kRun4 = false;
-#else
-    constexpr bool kRun4 = CULL == 0 && VEC == 4 && MATH == MATH_EXACT && NF == 1;
-#endif
-    bool raw_diff = kRun4;
 #pragma unroll
     for (int f = 0; f < NF; ++f) {
       const float4* e = tab + (lr * NF + f) * NT;
@@ -725,7 +660,6 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
 #pragma unroll
         for (int j = 0; j < VEC; ++j) odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
         if (__builtin_expect(odd, 0)) {
-          raw_diff = false;
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
             hit[f][j] = probe_literal_cold<COLOR, LE_TRUNC, MASK>(P.f[f].img, P.f[f].fx, P.f[f].cx, P.f[f].fy, P.f[f].cy,
@@ -747,7 +681,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           if (CULL == 0 || in_image) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
-              hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK, kRun4>(P.f[f], g, mask, pr[j], camz[j], STAGE ? &stg : nullptr);
+              hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, pr[j], camz[j], STAGE ? &stg : nullptr);
               any = any || hit[f][j].ok;
             }
           } else {
@@ -777,21 +711,11 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       // is computed unconditionally and selected — no divergence bookkeeping around 60
       // instructions.  Sparse frames keep the branch: measured (S-real / S-kitti, round-robin)
       // the select form costs 7-16 % there, and a per-run hybrid of the two 6 %.
-      if constexpr (kRun4) {
-        if (raw_diff) {
-          bool any2 = false;
-          if (flags & 8) update_run4<COLOR, WMODE, false>(g, hit[f], obs, t, w, col, n_written, any2);   // A/B: no free-space short cuts
-          else           update_run4<COLOR, WMODE, true>(g, hit[f], obs, t, w, col, n_written, any2);
-        } else {
-#pragma unroll
-          for (int j = 0; j < VEC; ++j) {
-            if (hit[f][j].ok) {
-              update_voxel<COLOR, MATH, WMODE>(t[j], w[j], col[j], hit[f][j], obs);
-              ++n_written;
-            }
-          }
-        }
-      } else if constexpr (CULL == 0) {
+      // (A per-run restructuring of this update with exact free-space short cuts — skip :53's quotient
+      // when diff >= trunc for the whole run, skip :57's when the stored tsdf is 1 as well — was built
+      // and measured in round 2: 8 % SLOWER at full clocks, profiles/r2_v3_dense_update_ab.jsonl; the
+      // kernel is HBM-bound and the extra control flow costs more than the arithmetic it saves.)
+      if constexpr (CULL == 0) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
           float nt = t[j], nw = w[j], nc = col[j];
@@ -979,12 +903,28 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
 #endif
 
   // ---- main loop: four live quarters per warp iteration ------------------------------------------
+  // The volume lines of the NEXT item are prefetched (L2) one iteration ahead: half of the probed runs
+  // are updated, and their loads would otherwise start only after the gather has decided validity
+  // (ncu of the first form: 2.4 long-scoreboard stall cycles per issue, issue-active 66 %).
   unsigned int n_written = 0;
   const int grp = lane >> 3, sub = lane & 7;
+  const bool ahead = (flags & 8) == 0;
+  int bit_next = grp < total ? nth_set_bit64(work, grp) : -1;
   for (int t0 = 0; t0 < total; t0 += 4) {
-    const int item = t0 + grp;
-    if (item >= total) continue;
-    const int bit = nth_set_bit64(work, item);
+    const int bit = bit_next;
+    {
+      const int nxt = t0 + 4 + grp;
+      bit_next = nxt < total ? nth_set_bit64(work, nxt) : -1;
+      if (ahead && pf && bit_next >= 0) {
+        const int64_t pn = (int64_t)(row0 + tr + (bit_next & 15) * rp) * g.n_fast + ka + (bit_next >> 4) * 32 + sub * VEC;
+        if (ka + (bit_next >> 4) * 32 + sub * VEC < g.n_fast) {
+          prefetch_line<true>(g.tsdf + pn, 1);
+          prefetch_line<true>(g.weight + pn, 1);
+          if constexpr (COLOR) prefetch_line<true>(g.color + pn, 1);
+        }
+      }
+    }
+    if (bit < 0) continue;
     const int Q = bit >> 4, it = bit & 15;
     const int lr = tr + it * rp;
     const int r = row0 + lr;
@@ -1023,7 +963,7 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
       if (!in_image) continue;                      // the run projects outside the image: no gather
       DBG_ADD(5, 1);
       const int64_t pb = (int64_t)r * g.n_fast + f0;
-      if (pf) {   // the gather's latency hides part of the volume loads' (most gathered runs are updated)
+      if (pf && (!ahead || t0 == 0)) {   // (first item, or A/B: prefetch only once the run is known to reach the gather)
         prefetch_line<true>(g.tsdf + pb, 1);
         prefetch_line<true>(g.weight + pb, 1);
         if constexpr (COLOR) prefetch_line<true>(g.color + pb, 1);
@@ -1169,23 +1109,19 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
 #pragma unroll
         for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true>(P.f[f], g, camx[j], camy[j], camz[j]);
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false, true>(P.f[f], g, nullptr, pr[j], camz[j]);
+        for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false>(P.f[f], g, nullptr, pr[j], camz[j]);
       }
       const float obs = P.f[f].obs_weight;
-      if (__builtin_expect(odd, 0)) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-          if (hit[j].ok) {
-            update_voxel<COLOR, MATH_EXACT, WMODE>(t[j], w[j], col[j], hit[j], obs);
-            ++n_written;
-            any = true;
-          }
-        }
-      } else {
-        // (no free-space short cuts here: measured round-robin on the B200 they cost the two-frame
-        // kernel 2-3 % — 4.08 vs 3.99 ms per frame at 1024^3, profiles/r2_v2_pair_ab.jsonl — while
-        // the single-frame kernel gains 4 % from them, profiles/r2_v2_free_ab.jsonl)
-        update_run4<COLOR, WMODE, false>(g, hit, obs, t, w, col, n_written, any);
+      for (int j = 0; j < VEC; ++j) {
+        float nt = t[j], nw = w[j], nc = col[j];
+        update_voxel<COLOR, MATH_EXACT, WMODE>(nt, nw, nc, hit[j], obs);
+        const bool ok = hit[j].ok;
+        t[j] = ok ? nt : t[j];
+        w[j] = ok ? nw : w[j];
+        col[j] = ok ? nc : col[j];
+        n_written += ok ? 1u : 0u;
+        any = any || ok;
       }
     }
     if (any) {
@@ -1236,8 +1172,8 @@ struct LaunchOpts {
   bool balance = true; // dense kernel, few waves: size the blocks so that the grid fills whole waves
   bool compact = true;    // sparse kernel: compact block tiles (one warp per row segment)
   bool block_test = true; // sparse kernel: block-level hull test before the per-warp tests
-  bool free_fast = true;  // dense kernels: exact free-space short cuts of update_run4
   bool quarters = true;   // sparse kernel: quarter-segment work lists (k_integrate_q)
+  bool ahead = true;      // ... with the next item's volume lines prefetched one iteration ahead
   const void* tmap = nullptr;  // sparse kernel: CUtensorMap of the prepared frame => staged image tile (A/B)
 };
 
@@ -1329,13 +1265,13 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
     // sparse frames on compact tiles (one warp per 128-voxel segment, <= 16 row iterations per warp):
     // the quarter work-list kernel
     if (o.kernel == 1 && o.quarters && o.compact && q.tpr_log2 == 5 && q.rows_per_block <= 16 * (kThreads / 32)) {
-      k_integrate_q<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.rows_per_block, pf | (o.block_test ? 4 : 0));
+      k_integrate_q<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.rows_per_block, pf | (o.block_test ? 4 : 0) | (o.ahead ? 0 : 8));
       CU_LAUNCHED();
       return TSDF_OK;
     }
   }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
-  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.free_fast ? 0 : 8));
+  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
 #ifdef TSDF_B200_DEV
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
 #endif
@@ -1456,8 +1392,8 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   o.balance = (v->variant & 2048) == 0;
   o.compact = (v->variant & 4096) == 0;      // bit12: old block shape (row-major, up to 256 threads per row)
   o.block_test = (v->variant & 8192) == 0;   // bit13: block-level hull test off
-  o.free_fast = (v->variant & 32768) == 0;   // bit15: free-space short cuts of the dense kernels off
   o.quarters = (v->variant & (1 << 21)) == 0; // bit21: plain sparse kernel instead of the quarter work lists
+  o.ahead = (v->variant & (1 << 22)) == 0;    // bit22: no prefetch one item ahead
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
