@@ -23,7 +23,7 @@ T = np.ascontiguousarray(np.stack([frames[i % 4][2].reshape(16) for i in range(k
 dd, dr = C.c_void_p(), C.c_void_p()
 check(lib.tsdf_device_alloc(0, C.byref(dd), depth.nbytes)); check(lib.tsdf_device_alloc(0, C.byref(dr), rgb.nbytes))
 check(lib.tsdf_memcpy_h2d(0, dd, depth.ctypes.data, depth.nbytes)); check(lib.tsdf_memcpy_h2d(0, dr, rgb.ctypes.data, rgb.nbytes))
-variants = {"pairs": 0, "singles": 1 << 14, "pairs_nofree": 1 << 15, "singles_nofree": (1 << 14) | (1 << 15)}
+variants = {"pairs": 0, "singles": 1 << 14}
 times = {n: [] for n in variants}
 with pkg.Volume(cfg) as vol:
     for rnd in range(R + 1):
