@@ -773,14 +773,14 @@ __device__ __forceinline__ int nth_set_bit64(unsigned long long m, int n) {   //
   return n < pl ? (int)__fns(lo, 0, n + 1) : 32 + (int)__fns(hi, 0, n - pl + 1);
 }
 
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
-__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)
-k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flags) {
+constexpr int kSegQ = 128;                           // voxels of a block's fast-axis window (32 runs of 4)
+
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE, bool MASK>
+__device__ __forceinline__ void integrate_q_body(const LaunchP<1>& P, const uint8_t* mask, float4* tab, float4* tabf,
+                                                 int rows_per_block, int flags) {
   constexpr int NT = ZFAST ? 1 : 2;
   constexpr int VEC = 4;
-  constexpr int kSeg = 32 * VEC;                     // voxels of the block's fast-axis window
-  __shared__ float4 tab[kMaxRowsPerBlock * NT];      // row terms
-  __shared__ float4 tabf[kSeg];                      // fast-axis terms {p0, p1, p2, -} of the window
+  constexpr int kSeg = kSegQ;
   __shared__ int blk_skip;
   const GridP& g = P.g;
   const FrameP& F = P.f[0];
@@ -903,28 +903,14 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
 #endif
 
   // ---- main loop: four live quarters per warp iteration ------------------------------------------
-  // The volume lines of the NEXT item are prefetched (L2) one iteration ahead: half of the probed runs
-  // are updated, and their loads would otherwise start only after the gather has decided validity
-  // (ncu of the first form: 2.4 long-scoreboard stall cycles per issue, issue-active 66 %).
+  // (Prefetching the NEXT item's volume lines one iteration ahead was tried: no gain — S-real 0.1559 vs
+  // 0.1567 ms, S-kitti 0.0943 vs 0.0925 ms, profiles/r2_v4_sparse_ab.jsonl — and is not kept.)
   unsigned int n_written = 0;
   const int grp = lane >> 3, sub = lane & 7;
-  const bool ahead = (flags & 8) == 0;
-  int bit_next = grp < total ? nth_set_bit64(work, grp) : -1;
   for (int t0 = 0; t0 < total; t0 += 4) {
-    const int bit = bit_next;
-    {
-      const int nxt = t0 + 4 + grp;
-      bit_next = nxt < total ? nth_set_bit64(work, nxt) : -1;
-      if (ahead && pf && bit_next >= 0) {
-        const int64_t pn = (int64_t)(row0 + tr + (bit_next & 15) * rp) * g.n_fast + ka + (bit_next >> 4) * 32 + sub * VEC;
-        if (ka + (bit_next >> 4) * 32 + sub * VEC < g.n_fast) {
-          prefetch_line<true>(g.tsdf + pn, 1);
-          prefetch_line<true>(g.weight + pn, 1);
-          if constexpr (COLOR) prefetch_line<true>(g.color + pn, 1);
-        }
-      }
-    }
-    if (bit < 0) continue;
+    const int item = t0 + grp;
+    if (item >= total) continue;
+    const int bit = nth_set_bit64(work, item);
     const int Q = bit >> 4, it = bit & 15;
     const int lr = tr + it * rp;
     const int r = row0 + lr;
@@ -947,8 +933,8 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
     if (__builtin_expect(odd, 0)) {
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        hit[j] = probe_literal_cold<COLOR, LE_TRUNC, false>(F.img, F.fx, F.cx, F.fy, F.cy, g.trunc, g.W, g.H, nullptr,
-                                                            camx[j], camy[j], camz[j]);
+        hit[j] = probe_literal_cold<COLOR, LE_TRUNC, MASK>(F.img, F.fx, F.cx, F.fy, F.cy, g.trunc, g.W, g.H, mask,
+                                                           camx[j], camy[j], camz[j]);
         any = any || hit[j].ok;
       }
     } else {
@@ -963,14 +949,14 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
       if (!in_image) continue;                      // the run projects outside the image: no gather
       DBG_ADD(5, 1);
       const int64_t pb = (int64_t)r * g.n_fast + f0;
-      if (pf && (!ahead || t0 == 0)) {   // (first item, or A/B: prefetch only once the run is known to reach the gather)
+      if (pf) {   // the gather's latency hides part of the volume loads' (most gathered runs are updated)
         prefetch_line<true>(g.tsdf + pb, 1);
         prefetch_line<true>(g.weight + pb, 1);
         if constexpr (COLOR) prefetch_line<true>(g.color + pb, 1);
       }
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
-        hit[j] = sample_exact<COLOR, LE_TRUNC, false>(F, g, nullptr, pr[j], camz[j]);
+        hit[j] = sample_exact<COLOR, LE_TRUNC, MASK>(F, g, mask, pr[j], camz[j]);
         any = any || hit[j].ok;
       }
     }
@@ -999,6 +985,29 @@ k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flag
   }
   for (int o = 16; o > 0; o >>= 1) n_written += __shfl_down_sync(0xffffffffu, n_written, o);
   if (lane == 0 && n_written) atomicAdd(g.written, (unsigned long long)n_written);
+}
+
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)
+k_integrate_q(const __grid_constant__ LaunchP<1> P, int rows_per_block, int flags) {
+  __shared__ float4 tab[kMaxRowsPerBlock * (ZFAST ? 1 : 2)];   // row terms
+  __shared__ float4 tabf[kSegQ];                                // fast-axis terms {p0, p1, p2, -} of the window
+  integrate_q_body<ZFAST, COLOR, LE_TRUNC, WMODE, false>(P, nullptr, tab, tabf, rows_per_block, flags);
+}
+
+// The same for batched per-instance volumes (config 5): blockIdx.z selects the descriptor.
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+__global__ void __launch_bounds__(kThreads, KI_MINBLOCKS)
+k_integrate_q_batch(const BatchDesc* __restrict__ descs, int rows_per_block, int flags) {
+  __shared__ float4 tab[kMaxRowsPerBlock * (ZFAST ? 1 : 2)];
+  __shared__ float4 tabf[kSegQ];
+  __shared__ LaunchP<1> P;
+  __shared__ const uint8_t* mask;
+  const BatchDesc& d = descs[blockIdx.z];
+  if (threadIdx.x == 0) { P.g = d.g; P.f[0] = d.f; mask = d.mask; }
+  __syncthreads();
+  if (mask) integrate_q_body<ZFAST, COLOR, LE_TRUNC, WMODE, true>(P, mask, tab, tabf, rows_per_block, flags);
+  else      integrate_q_body<ZFAST, COLOR, LE_TRUNC, WMODE, false>(P, nullptr, tab, tabf, rows_per_block, flags);
 }
 
 #ifdef TSDF_B200_DEV
@@ -1173,7 +1182,6 @@ struct LaunchOpts {
   bool compact = true;    // sparse kernel: compact block tiles (one warp per row segment)
   bool block_test = true; // sparse kernel: block-level hull test before the per-warp tests
   bool quarters = true;   // sparse kernel: quarter-segment work lists (k_integrate_q)
-  bool ahead = true;      // ... with the next item's volume lines prefetched one iteration ahead
   const void* tmap = nullptr;  // sparse kernel: CUtensorMap of the prepared frame => staged image tile (A/B)
 };
 
@@ -1265,7 +1273,7 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
     // sparse frames on compact tiles (one warp per 128-voxel segment, <= 16 row iterations per warp):
     // the quarter work-list kernel
     if (o.kernel == 1 && o.quarters && o.compact && q.tpr_log2 == 5 && q.rows_per_block <= 16 * (kThreads / 32)) {
-      k_integrate_q<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.rows_per_block, pf | (o.block_test ? 4 : 0) | (o.ahead ? 0 : 8));
+      k_integrate_q<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.rows_per_block, pf | (o.block_test ? 4 : 0));
       CU_LAUNCHED();
       return TSDF_OK;
     }
@@ -1393,7 +1401,6 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   o.compact = (v->variant & 4096) == 0;      // bit12: old block shape (row-major, up to 256 threads per row)
   o.block_test = (v->variant & 8192) == 0;   // bit13: block-level hull test off
   o.quarters = (v->variant & (1 << 21)) == 0; // bit21: plain sparse kernel instead of the quarter work lists
-  o.ahead = (v->variant & (1 << 22)) == 0;    // bit22: no prefetch one item ahead
   o.prefetch = (v->variant & 32) ? 0 : (((v->variant >> 1) & 3) ? ((v->variant >> 1) & 3) : 1);
   o.rows_mult = (v->variant & 8) ? 64 : ((v->variant & 16) ? 32 : ((v->variant & 256) ? 8 : ((v->variant & 512) ? 4 : 16)));
   // cull: forced off (bit 6) / on (bit 7), else on unless the host can show that the whole slab
@@ -1441,6 +1448,19 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
 int launch_integrate_batch(const BatchDesc* d_descs, int n_active, int max_fast, int max_rows,
                            bool zfast, bool color, bool vec4, int wmode, cudaStream_t st) {
   Geometry q = plan(max_fast, max_rows, vec4 ? 4 : 1, n_active);
+  if (vec4 && max_fast >= kSegQ) {
+    // compact tiles + quarter work lists (see k_integrate_q); an instance smaller than the grid's
+    // largest leaves its surplus blocks at the first test
+    Geometry qq = plan(max_fast, max_rows, 4, n_active, 16, 32);
+    if (qq.tpr_log2 == 5 && qq.rows_per_block <= 16 * (kThreads / 32)) {
+#define LQ(ZF, CO, LE, WM) k_integrate_q_batch<ZF, CO, LE, WM><<<qq.grid, kThreads, 0, st>>>(d_descs, qq.rows_per_block, 1 | 4)
+      if (zfast) { if (color) { if (wmode == 1) LQ(true, true, false, 1); else LQ(true, true, false, 0); } else LQ(true, false, false, 0); }
+      else       { if (color) { if (wmode == 1) LQ(false, true, true, 1); else LQ(false, true, true, 0); } else LQ(false, false, true, 0); }
+#undef LQ
+      CU_LAUNCHED();
+      return TSDF_OK;
+    }
+  }
 #define LB(ZF, CO, LE, V, WM) k_integrate_batch<ZF, CO, LE, V, WM><<<q.grid, kThreads, 0, st>>>(d_descs, q.tpr_log2, q.rows_per_block, 1 /* L2 prefetch */ | 4 /* block hull test */)
   if (zfast) {
     if (color) { if (wmode == 1) { if (vec4) LB(true, true, false, 4, 1); else LB(true, true, false, 1, 1); }

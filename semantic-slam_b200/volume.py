@@ -271,11 +271,15 @@ class Volume:
                                            None, None, None, 0, C.byref(n)))
         return n.value
 
-    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, pool=None):
+    def extract_points(self, pred=PRED_NONZERO, tsdf_thresh=1.2, weight_thresh=0.9, pool=None, out=None):
         """pool: a PinnedPool -> the outputs are views of page-locked memory owned by the pool (valid
-        until the next call with the same pool): the D2H copies land in them directly."""
+        until the next call with the same pool): the D2H copies land in them directly.
+        out: (xyz, rgb, idx) arrays of a previous call with the same point count to write into."""
         n = self.extract_count(pred, tsdf_thresh, weight_thresh)
-        if pool is not None:
+        if out is not None:
+            xyz, rgb, idx = out
+            assert len(idx) == n and xyz.shape == (n, 3) and rgb.shape == (n, 3)
+        elif pool is not None:
             xyz = pool.array("xyz", (max(n, 1), 3), np.float32)
             rgb = pool.array("rgb", (max(n, 1), 3), np.uint8)
             idx = pool.array("idx", (max(n, 1),), np.int64)
@@ -294,11 +298,14 @@ class Volume:
         check(self.lib.tsdf_extract_mesh(self.h, None, None, None, 0, None, 0, C.byref(nv), C.byref(nf)))
         return nv.value, nf.value
 
-    def extract_mesh(self, pool=None):
+    def extract_mesh(self, pool=None, out=None):
         """Level-0 marching cubes on the device: verts (nv,3) f32, faces (nf,3) i32, norms (nv,3) f32,
         colors (nv,3) u8 — the tuple order of fusion.TSDFVolume.get_mesh()."""
         nv, nf = self.mesh_count()
-        if pool is not None:
+        if out is not None:
+            verts, faces, norms, cols = out
+            assert verts.shape == (nv, 3) and faces.shape == (nf, 3)
+        elif pool is not None:
             verts = pool.array("verts", (max(nv, 1), 3), np.float32)
             norms = pool.array("norms", (max(nv, 1), 3), np.float32)
             cols = pool.array("cols", (max(nv, 1), 3), np.uint8)

@@ -355,11 +355,14 @@ def test_reference_class_mirrors(pkg, oracle, synth, tmp_path):
     tv.close()
 
 
-def test_batched_instances_match_per_instance_oracle(pkg, oracle, synth):
+@pytest.mark.parametrize("dims,vs", [((32, 32, 32), 0.02), ((128, 24, 40), 0.006), ((136, 16, 24), 0.006)])
+def test_batched_instances_match_per_instance_oracle(pkg, oracle, synth, dims, vs):
     """Config 5 in small: N instance volumes, one launch per frame, masked depth semantics of
-    src/Engine.cpp:192-193 and per-instance base/origin of src/Object.cpp:23-49."""
+    src/Engine.cpp:192-193 and per-instance base/origin of src/Object.cpp:23-49.  Fast axis 32: the
+    plain sparse body; 128 / 136 (ragged second window): the quarter work-list kernel
+    (k_integrate_q_batch), what BASELINE config 5's 128^3 instance volumes run."""
     import ctypes as C
-    n_inst, dims, vs = 6, (32, 32, 32), 0.02
+    n_inst = 6
     _, frames = synth.s_real((64, 64, 64), 0.08, n_frames=3, seed=91)
     masks, _ = synth.instance_masks(n_inst, seed=92)
     base = frames[0][2]
