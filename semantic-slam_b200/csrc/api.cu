@@ -6,8 +6,13 @@
 #include <stdarg.h>
 #include <stdlib.h>
 
+#include <unistd.h>
+
 #include <algorithm>
+#include <condition_variable>
 #include <limits>
+#include <mutex>
+#include <thread>
 
 #include <cuda.h>   // CUtensorMap types only: the encoder is fetched with cudaGetDriverEntryPoint (no -lcuda)
 
@@ -407,6 +412,102 @@ int copy_to_host(OutBuffers* ob, void* dst, const void* d_src, size_t bytes, cud
   return TSDF_OK;
 }
 
+// ---- pageable -> pinned staging copy on several host threads -----------------------------------
+// The reference hands over pageable memory (cv::Mat data, src/Object.cpp:160-164), so the drop-in
+// path starts with a host copy into the pinned ring; on one thread that copy (~12 GB/s) costs more
+// than the sparse kernels' whole frame (2.15 MB: 0.17 ms against 0.09-0.14 ms).  A few helper threads
+// (TSDF_B200_COPY_THREADS, default 3, 0 = off) split copies of 256 KB and more with the caller.  The
+// pool is created on first use, leaked on purpose (detached threads, nothing to destroy at exit) and
+// re-created in a forked child; a second caller that finds it busy copies on its own thread.
+namespace {
+struct CopyPool {
+  std::mutex m;
+  std::condition_variable cv_work, cv_done;
+  const char* src = nullptr;
+  char* dst = nullptr;
+  size_t bytes = 0, part = 0;
+  int parts = 0, next = 0, pending = 0;
+  uint64_t gen = 0;
+  int n_threads = 0;
+  std::mutex busy;   // one parallel copy at a time
+};
+CopyPool* g_copy_pool = nullptr;
+long g_copy_pool_pid = 0;
+std::mutex g_copy_pool_mu;
+
+void copy_worker(CopyPool* p) {
+  uint64_t seen = 0;
+  std::unique_lock<std::mutex> lk(p->m);
+  for (;;) {
+    p->cv_work.wait(lk, [&] { return p->gen != seen; });
+    seen = p->gen;
+    while (p->next < p->parts) {
+      const int i = p->next++;
+      const size_t off = (size_t)i * p->part, len = std::min(p->part, p->bytes - off);
+      const char* s = p->src;
+      char* d = p->dst;
+      lk.unlock();
+      memcpy(d + off, s + off, len);
+      lk.lock();
+      if (--p->pending == 0) p->cv_done.notify_all();
+    }
+  }
+}
+
+CopyPool* copy_pool() {
+  std::lock_guard<std::mutex> g(g_copy_pool_mu);
+  const long pid = (long)getpid();
+  if (g_copy_pool && g_copy_pool_pid == pid) return g_copy_pool->n_threads > 0 ? g_copy_pool : nullptr;
+  int n = 3;
+  if (const char* e = getenv("TSDF_B200_COPY_THREADS")) n = atoi(e);
+  const int hw = (int)std::thread::hardware_concurrency();
+  if (hw > 0 && n > hw - 1) n = hw - 1;
+  if (n > 15) n = 15;
+  CopyPool* p = new (std::nothrow) CopyPool();   // (a pool inherited through fork() has no threads: dropped)
+  if (!p) return nullptr;
+  p->n_threads = n > 0 ? n : 0;
+  try {
+    for (int i = 0; i < p->n_threads; ++i) std::thread(copy_worker, p).detach();
+  } catch (...) {
+    p->n_threads = 0;
+  }
+  g_copy_pool = p;
+  g_copy_pool_pid = pid;
+  return p->n_threads > 0 ? p : nullptr;
+}
+}  // namespace
+
+void host_copy(void* dst, const void* src, size_t bytes) {
+  CopyPool* p = bytes >= (256u << 10) ? copy_pool() : nullptr;
+  if (!p || !p->busy.try_lock()) {
+    memcpy(dst, src, bytes);
+    return;
+  }
+  {
+    std::unique_lock<std::mutex> lk(p->m);
+    p->src = static_cast<const char*>(src);
+    p->dst = static_cast<char*>(dst);
+    p->bytes = bytes;
+    p->parts = p->n_threads + 1;
+    p->part = ((bytes + p->parts - 1) / p->parts + 4095) & ~(size_t)4095;
+    p->parts = (int)((bytes + p->part - 1) / p->part);
+    p->next = 0;
+    p->pending = p->parts;
+    ++p->gen;
+    p->cv_work.notify_all();
+    while (p->next < p->parts) {   // the caller takes parts too
+      const int i = p->next++;
+      const size_t off = (size_t)i * p->part, len = std::min(p->part, bytes - off);
+      lk.unlock();
+      memcpy(p->dst + off, p->src + off, len);
+      lk.lock();
+      --p->pending;
+    }
+    p->cv_done.wait(lk, [&] { return p->pending == 0; });
+  }
+  p->busy.unlock();
+}
+
 // Moves `bytes` from src (any kind) to where the prep kernel can read it; returns the device
 // pointer to read from.  Pageable data goes through the slot's pinned buffer.
 int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,
@@ -423,7 +524,7 @@ int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, si
   if (k == PTR_PAGEABLE) {
     if (!s.h_pinned) CU_CHECK(cudaHostAlloc(&s.h_pinned, frame_pixels(v->cfg) * 7 + 64, cudaHostAllocDefault));
     char* stage = reinterpret_cast<char*>(s.h_pinned) + raw_off;
-    memcpy(stage, src, bytes);
+    host_copy(stage, src, bytes);
     src = stage;
   }
   CU_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, v->s_copy));

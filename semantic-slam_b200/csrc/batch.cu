@@ -161,7 +161,7 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
       cudaGetLastError();
       const void* src = crops;
       if (!(known && (a.type == cudaMemoryTypeHost || a.type == cudaMemoryTypeDevice || a.type == cudaMemoryTypeManaged))) {
-        memcpy(b->h_masks, crops, (size_t)total);  // pageable -> pinned staging
+        host_copy(b->h_masks, crops, (size_t)total);  // pageable -> pinned staging
         src = b->h_masks;
       }
       CU_CHECK(cudaMemcpyAsync(b->d_crops, src, (size_t)total, cudaMemcpyDefault, fo->s_copy));
@@ -179,7 +179,7 @@ static int batch_integrate(tsdf_batch* b, const float* depth, const uint8_t* rgb
     else {
       const bool pinned = a.type == cudaMemoryTypeHost;
       const void* src = masks;
-      if (!pinned) { memcpy(b->h_masks, masks, px * (size_t)n_active); src = b->h_masks; }
+      if (!pinned) { host_copy(b->h_masks, masks, px * (size_t)n_active); src = b->h_masks; }
       CU_CHECK(cudaMemcpyAsync(b->d_masks, src, px * (size_t)n_active, cudaMemcpyHostToDevice, fo->s_copy));
       d_masks = b->d_masks;
     }

@@ -291,6 +291,7 @@ int write_mesh_ply(const char* path, const float* verts, const float* norms, con
                    const int32_t* faces, int64_t nf);                                      // fusion.meshwrite
 int trace_mark(tsdf_vol* v, int which, cudaStream_t st);   // no-op unless tsdf_trace_enable(v, 1)
 int check_obs_weight(float obs_weight);  // one validation for every integrate entry point
+void host_copy(void* dst, const void* src, size_t bytes);   // memcpy, split over a few helper threads when large
 int ensure_bcast_slot(tsdf_vol* v, int index);
 // moves `bytes` of a frame (pageable / pinned host or device memory) to where the prep kernel reads it
 int frame_to_device(tsdf_vol* v, FrameSlot& s, const void* src, size_t bytes, size_t raw_off,

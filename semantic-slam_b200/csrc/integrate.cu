@@ -28,6 +28,15 @@
 
 namespace {
 
+// Dense kernels test the exponent window of camz once per run of 4 instead of per voxel: every fp32
+// operation of the camera transform is monotone in the fast index, so the run's camz values lie
+// between its two end voxels'; a run with an end outside the window (behind the camera, or absurdly
+// far) takes the literal path as a whole.  -DKI_NO_RUNSAFE: A/B builds.
+#ifdef KI_NO_RUNSAFE
+constexpr bool kRunSafe = false;
+#else
+constexpr bool kRunSafe = true;
+#endif
 #ifndef KI_MINBLOCKS
 #define KI_MINBLOCKS 4   // (A/B builds: -DKI_MINBLOCKS=3 lets the dense kernel take 80 registers)
 #endif
@@ -185,9 +194,10 @@ __device__ __forceinline__ Hit probe_exact(const FrameP& f, const GridP& g, cons
 struct Proj { bool ok; int pix; int px, py; };   // (px, py: only the staged-tile variant reads them)
 
 
-template <bool SELECT>
+// KNOWN_SAFE: the caller has shown camz inside the exponent window (dense kernels: once per run).
+template <bool SELECT, bool KNOWN_SAFE = false>
 __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, float camx, float camy, float camz) {
-  const bool inr = em::in_safe_range(camz);               // implies camz > 0            :39
+  const bool inr = KNOWN_SAFE || em::in_safe_range(camz); // implies camz > 0            :39
   const float yz = em::rcp_rn(camz);
   const float u = f.fx * em::div_rn(camx, camz, yz) + f.cx;   // :41
   const float v = f.fy * em::div_rn(camy, camz, yz) + f.cy;   // :42
@@ -656,9 +666,14 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           any = any || hit[f][j].ok;
         }
       } else {
+        constexpr bool kEnds = kRunSafe && CULL == 0 && VEC == 4;
         bool odd = false;  // a positive camz outside the exponent window of the exact forms
+        if constexpr (kEnds) {
+          odd = !(em::in_safe_range(camz[0]) && em::in_safe_range(camz[VEC - 1]));   // (dense frames: never)
+        } else {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
+          for (int j = 0; j < VEC; ++j) odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
+        }
         if (__builtin_expect(odd, 0)) {
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
@@ -671,7 +686,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           bool in_image = false;
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
-            pr[j] = project_exact<true>(P.f[f], g, camx[j], camy[j], camz[j]);
+            pr[j] = project_exact<true, kEnds>(P.f[f], g, camx[j], camy[j], camz[j]);
             in_image = in_image || pr[j].ok;
           }
           // CULL == 2 (sparse frames): a run that projects outside the image stops before the
@@ -1105,8 +1120,9 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
 #pragma unroll
       for (int j = 0; j < VEC; ++j) {
         cam_coords<ZFAST>(ea, eb, q[f][0][j], q[f][1][j], q[f][2][j], camx[j], camy[j], camz[j]);
-        odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
+        if constexpr (!kRunSafe) odd = odd || (!em::in_safe_range(camz[j]) && camz[j] > 0.0f);
       }
+      if constexpr (kRunSafe) odd = !(em::in_safe_range(camz[0]) && em::in_safe_range(camz[VEC - 1]));
       Hit hit[VEC];
       if (__builtin_expect(odd, 0)) {
 #pragma unroll
@@ -1116,7 +1132,7 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
       } else {
         Proj pr[VEC];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true>(P.f[f], g, camx[j], camy[j], camz[j]);
+        for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true, kRunSafe>(P.f[f], g, camx[j], camy[j], camz[j]);
 #pragma unroll
         for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false>(P.f[f], g, nullptr, pr[j], camz[j]);
       }
