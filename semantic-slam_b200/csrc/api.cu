@@ -415,10 +415,14 @@ int copy_to_host(OutBuffers* ob, void* dst, const void* d_src, size_t bytes, cud
 // ---- pageable -> pinned staging copy on several host threads -----------------------------------
 // The reference hands over pageable memory (cv::Mat data, src/Object.cpp:160-164), so the drop-in
 // path starts with a host copy into the pinned ring; on one thread that copy (~12 GB/s) costs more
-// than the sparse kernels' whole frame (2.15 MB: 0.17 ms against 0.09-0.14 ms).  A few helper threads
-// (TSDF_B200_COPY_THREADS, default 3, 0 = off) split copies of 256 KB and more with the caller.  The
-// pool is created on first use, leaked on purpose (detached threads, nothing to destroy at exit) and
-// re-created in a forked child; a second caller that finds it busy copies on its own thread.
+// than the sparse kernels' whole frame (2.15 MB: 0.10-0.12 ms on the GPU box against 0.09-0.14 ms).
+// Helper threads (TSDF_B200_COPY_THREADS = n, OFF by default) split copies of 256 KB and more with the
+// caller: 0.022 ms for the same 2.15 MB with 3 helpers.  Measured on the B200 box, three alternating
+// rounds (profiles/r2_v5_dropin_ab.jsonl): an asynchronous C2 stream gains (5400 -> 6700 frames/s),
+// but the helpers' sleep / wake-up latency makes the blocking 200^3 call erratic (0.15-0.34 ms against
+// a steady 0.19) and costs the batched-instance path 18 % (1640 -> 1330 keyframes/s) — hence opt-in.
+// The pool is created on first use, leaked on purpose (detached threads, nothing to destroy at exit)
+// and re-created in a forked child; a second caller that finds it busy copies on its own thread.
 namespace {
 struct CopyPool {
   std::mutex m;
@@ -458,7 +462,7 @@ CopyPool* copy_pool() {
   std::lock_guard<std::mutex> g(g_copy_pool_mu);
   const long pid = (long)getpid();
   if (g_copy_pool && g_copy_pool_pid == pid) return g_copy_pool->n_threads > 0 ? g_copy_pool : nullptr;
-  int n = 3;
+  int n = 0;
   if (const char* e = getenv("TSDF_B200_COPY_THREADS")) n = atoi(e);
   const int hw = (int)std::thread::hardware_concurrency();
   if (hw > 0 && n > hw - 1) n = hw - 1;
