@@ -195,6 +195,42 @@ int tsdf_extract_points(tsdf_vol* v, int predicate, float tsdf_thresh, float wei
 int tsdf_extract_points_device(tsdf_vol* v, int predicate, float tsdf_thresh, float weight_thresh,
                                float* d_xyz, uint8_t* d_rgb, int64_t* d_idx, int64_t cap,
                                int64_t* count);
+/* Point extraction that allocates nothing.  (No counterpart in the reference: its only extraction
+ * is the host loop of src/tsdf.cu:170-218.)
+ *
+ * Who needs it: a host that must not — or cannot — let this library allocate while it runs.  Examples:
+ * a tracking / mapping loop with a frame deadline (cudaMalloc and cudaFree stall every stream of the
+ * device, so a readback that grows its scratch would hiccup the integration running beside it); an
+ * application that gave all device memory to its own pool or to torch's caching allocator up front, so
+ * a cudaMalloc from a library simply fails; and a caller whose voxel arrays are its own device buffers
+ * rather than a tsdf_vol (every other extraction call needs a handle, and tsdf_create allocates).
+ *
+ * How: the ballot / count / offset scratch of the compaction sits in one fixed array compiled into the
+ * library's device image (about 16.2 MiB; every GPU that loads the library holds it until the process
+ * exits).  The voxel arrays and the outputs are the caller's device buffers.  The call makes no
+ * cudaMalloc / cudaFree / cudaHostAlloc and creates no stream or event.
+ *
+ *   cfg       dims, origin, voxel_size, semantics, device and (optionally) z_begin/z_end describe the
+ *             arrays; the other fields are ignored.
+ *   d_tsdf, d_weight, d_color   device arrays of the slab in the semantics' storage order (what
+ *             tsdf_download(..., global_layout = 0) returns); d_color may be NULL (rgb = 0 then).
+ *   d_xyz, d_rgb, d_idx, cap, count   as tsdf_extract_points_device; all three NULL = sizing call.
+ *   stream    a cudaStream_t of cfg->device, or NULL for the default stream.  The call returns after
+ *             the stream has drained (results are in the output buffers).
+ *
+ * Limits and rules:
+ *   - at most 2^27 voxels (512^3) per call; a larger slab is refused with TSDF_E_INVALID and a message
+ *     that names the limit (use a handle and tsdf_extract_points_device for those);
+ *   - the first call on each device looks up the array's device address (cudaGetSymbolAddress, checked,
+ *     cached per device).  Make that first call during set-up, before any stream capture is begun;
+ *   - all calls on a device share the one array, and it keeps whatever the previous call wrote.  No
+ *     part of it has to be zero on entry (each pass overwrites what the next one reads), but two calls
+ *     that overlap on the same GPU — two host threads, or two streams — trample each other's scratch:
+ *     serialise them.  Calls on different GPUs are independent.                                    */
+int tsdf_extract_points_static(const tsdf_config* cfg, const float* d_tsdf, const float* d_weight,
+                               const float* d_color, int predicate, float tsdf_thresh,
+                               float weight_thresh, float* d_xyz, uint8_t* d_rgb, int64_t* d_idx,
+                               int64_t cap, int64_t* count, void* stream);
 /* Triangle-mesh readback: replaces fusion.TSDFVolume.get_mesh(), called by the plugin's
  * SaveMesh (src/TSDFfusion.py.in:48-53).  Level-0 marching cubes of the handle's tsdf array
  * (no weight mask, as upstream), on the device: indexed mesh, one vertex per sign-crossing grid

@@ -71,6 +71,7 @@ SIGNATURES = {
     "tsdf_upload": (_I, [_VP, _VP, _VP, _VP, _I]),
     "tsdf_extract_points": (_I, [_VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
     "tsdf_extract_points_device": (_I, [_VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64)]),
+    "tsdf_extract_points_static": (_I, [C.POINTER(Config), _VP, _VP, _VP, _I, _F, _F, _VP, _VP, _VP, _I64, C.POINTER(_I64), _VP]),
     "tsdf_extract_mesh": (_I, [_VP, _VP, _VP, _VP, _I64, _VP, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
     "tsdf_extract_mesh_device": (_I, [_VP, _VP, _VP, _VP, _I64, _VP, _I64, C.POINTER(_I64), C.POINTER(_I64)]),
     "tsdf_save_mesh_ply": (_I, [_VP, C.c_char_p]),

@@ -377,3 +377,111 @@ int launch_merge_scatter(int64_t total, int nranks, const int64_t* d_offs, const
   CU_LAUNCHED();
   return TSDF_OK;
 }
+
+// ---- point extraction for callers that may not allocate (tsdf_extract_points_static) ---------------
+// No counterpart in the reference.  Same three passes as extract_device (k_mark -> scan -> k_emit), but
+// the ballots / tile counts / offsets live in ONE file-scope device array instead of a cudaMalloc'ed,
+// grow-on-demand buffer owned by a handle, and the voxel arrays and outputs are the caller's.  The host
+// path below calls no cudaMalloc / cudaFree / cudaHostAlloc / stream or event creation.
+namespace {
+
+constexpr int64_t kStaticMaxVoxels = (int64_t)1 << 27;  // 512^3; the reference's own grids are 200^3 / 500^3
+constexpr size_t pad256(size_t b) { return (b + 255) & ~(size_t)255; }
+constexpr int64_t kStaticMaxTiles = (kStaticMaxVoxels + kTileVox - 1) / kTileVox;
+constexpr size_t kStaticOffBytes = pad256((size_t)(kStaticMaxTiles + 1) * 8);
+constexpr size_t kStaticCntBytes = pad256((size_t)kStaticMaxTiles * 4);
+constexpr size_t kStaticBalBytes = pad256((size_t)((kStaticMaxVoxels + 127) / 128) * 16);
+constexpr size_t kStaticTotBytes = pad256((size_t)((kStaticMaxTiles + kScanTile - 1) / kScanTile + 1) * 8);
+constexpr size_t kStaticScratchBytes = kStaticOffBytes + kStaticCntBytes + kStaticBalBytes + kStaticTotBytes;  // ~16.2 MiB
+
+// Lives in every context that loads this module, from load until process exit.  Host code must never
+// hand `g_static_scratch` itself to a kernel: on the host the name is only a handle for the runtime's
+// symbol table; the device address comes from cudaGetSymbolAddress (static_scratch_for below).
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+constexpr int kStaticMaxDevices = 64;
+void* g_static_ptr[kStaticMaxDevices];          // device address of g_static_scratch, per device ordinal
+std::atomic<bool> g_static_known[kStaticMaxDevices];
+
+// Looks the array's device address up once per device.  `device` must be the current device (each
+// device has its own copy of the array at its own address).
+int static_scratch_for(int device, unsigned char** out) {
+  if (!g_static_known[device].load(std::memory_order_acquire)) {
+    void* p = nullptr;
+    CU_CHECK(cudaGetSymbolAddress(&p, g_static_scratch));
+    if (!p) {
+      tsdf_set_error("tsdf_extract_points_static: no device address for the static scratch on device %d", device);
+      return TSDF_E_CUDA;
+    }
+    g_static_ptr[device] = p;   // two racing first calls store the same value
+    g_static_known[device].store(true, std::memory_order_release);
+  }
+  *out = static_cast<unsigned char*>(g_static_ptr[device]);
+  return TSDF_OK;
+}
+
+}  // namespace
+
+extern "C" int tsdf_extract_points_static(const tsdf_config* cfg, const float* d_tsdf, const float* d_weight,
+                                          const float* d_color, int predicate, float tsdf_thresh,
+                                          float weight_thresh, float* d_xyz, uint8_t* d_rgb, int64_t* d_idx,
+                                          int64_t cap, int64_t* count, void* stream) {
+  REQUIRE(cfg && d_tsdf && d_weight && count, "null argument");
+  REQUIRE(cfg->dim_x > 0 && cfg->dim_y > 0 && cfg->dim_z > 0, "grid dims must be positive");
+  REQUIRE(predicate == TSDF_PRED_NONZERO || predicate == TSDF_PRED_ABS_LT, "unknown predicate");
+  REQUIRE(cfg->semantics == TSDF_SEM_TSDFCU || cfg->semantics == TSDF_SEM_FUSIONPY, "unknown semantics");
+  int z0 = cfg->z_begin, z1 = cfg->z_end;
+  if (z0 == 0 && z1 == 0) z1 = cfg->dim_z;
+  REQUIRE(z0 >= 0 && z0 < z1 && z1 <= cfg->dim_z, "bad z slab");
+  const int dzl = z1 - z0;
+  const int64_t n = (int64_t)cfg->dim_x * cfg->dim_y * dzl;
+  if (n > kStaticMaxVoxels) {
+    tsdf_set_error("tsdf_extract_points_static: %lld voxels exceed the static scratch limit of %lld "
+                   "(2^27 = 512^3); larger grids need tsdf_extract_points_device on a handle",
+                   (long long)n, (long long)kStaticMaxVoxels);
+    return TSDF_E_INVALID;
+  }
+  int ndev = 0;
+  int rc = tsdf_device_count(&ndev);
+  if (rc) return rc;
+  REQUIRE(cfg->device >= 0 && cfg->device < ndev && cfg->device < kStaticMaxDevices, "device ordinal out of range");
+  DeviceGuard g(cfg->device);
+  unsigned char* base = nullptr;
+  if ((rc = static_scratch_for(cfg->device, &base))) return rc;
+  const int64_t n_tiles = (n + kTileVox - 1) / kTileVox;
+  const int64_t n_chunks = (n + 127) / 128;
+  // same carve-up as extract_device, at the offsets of the LARGEST grid (so the layout is call-independent)
+  int64_t* d_off = reinterpret_cast<int64_t*>(base);
+  uint32_t* d_cnt = reinterpret_cast<uint32_t*>(base + kStaticOffBytes);
+  uint32_t* d_bal = reinterpret_cast<uint32_t*>(base + kStaticOffBytes + kStaticCntBytes);
+  int64_t* d_tot = reinterpret_cast<int64_t*>(base + kStaticOffBytes + kStaticCntBytes + kStaticBalBytes);
+  (void)n_chunks;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // Nothing in the array has to start at zero: k_mark writes every ballot word and tile count of this
+  // grid, the scan writes every offset (and off[n_tiles]) before k_emit reads them, so whatever the
+  // previous call left behind is overwritten before it is read.
+  k_mark<<<(unsigned)n_tiles, kThreads, 0, st>>>(d_tsdf, d_weight, n, predicate, tsdf_thresh, weight_thresh,
+                                                 d_bal, d_cnt);
+  CU_LAUNCHED();
+  if ((rc = launch_scan(d_cnt, n_tiles, d_off, d_tot, st))) return rc;
+  int64_t total = 0;
+  CU_CHECK(cudaMemcpyAsync(&total, d_off + n_tiles, 8, cudaMemcpyDeviceToHost, st));
+  CU_CHECK(cudaStreamSynchronize(st));
+  *count = total;
+  if (!d_xyz && !d_rgb && !d_idx) return TSDF_OK;  // sizing call
+  if (cap < total) {
+    tsdf_set_error("tsdf_extract_points_static: capacity %lld < %lld points", (long long)cap, (long long)total);
+    return TSDF_E_CAPACITY;
+  }
+  if (total == 0) return TSDF_OK;
+  EmitP p;
+  p.n = n;
+  p.dx = cfg->dim_x; p.dy = cfg->dim_y; p.dz = cfg->dim_z; p.dzl = dzl; p.z0 = z0;
+  p.zfast = cfg->semantics == TSDF_SEM_FUSIONPY ? 1 : 0;
+  p.ox = cfg->origin[0]; p.oy = cfg->origin[1]; p.oz = cfg->origin[2]; p.vs = cfg->voxel_size;
+  p.color = d_color;
+  k_emit<<<(unsigned)n_tiles, kThreads, 0, st>>>(d_bal, d_off, p, d_xyz, d_rgb, d_idx);
+  CU_LAUNCHED();
+  CU_CHECK(cudaStreamSynchronize(st));
+  return TSDF_OK;
+}
