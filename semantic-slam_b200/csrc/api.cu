@@ -222,7 +222,6 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaMalloc(&v->d_weight, bytes));
   if (c.with_color) CU_CHECK(cudaMalloc(&v->d_color, bytes));
   CU_CHECK(cudaMalloc(&v->d_written, sizeof(unsigned long long) * kWrittenRing));
-  CU_CHECK(cudaMemset(v->d_written, 0, sizeof(unsigned long long) * kWrittenRing));
   CU_CHECK(cudaHostAlloc(&v->h_written, sizeof(unsigned long long), cudaHostAllocMapped | cudaHostAllocPortable));
   CU_CHECK(cudaHostGetDevicePointer(reinterpret_cast<void**>(&v->hd_written), v->h_written, 0));
   *v->h_written = 0;
@@ -235,6 +234,9 @@ static int create_impl(const tsdf_config* cfg, tsdf_vol* v) {
   CU_CHECK(cudaStreamCreateWithPriority(&v->s_compute, cudaStreamNonBlocking, prio_least));
   CU_CHECK(cudaStreamCreateWithPriority(&v->s_copy, cudaStreamNonBlocking, prio_greatest));
   CU_CHECK(cudaStreamCreateWithPriority(&v->s_aux, cudaStreamNonBlocking, prio_greatest));
+  // on the stream whose kernels add into the counters: a plain cudaMemset runs on the legacy default
+  // stream, which a cudaStreamNonBlocking stream does not wait for
+  CU_CHECK(cudaMemsetAsync(v->d_written, 0, sizeof(unsigned long long) * kWrittenRing, v->s_compute));
   for (int i = 0; i < kWrittenRing; ++i) {
     CU_CHECK(cudaEventCreateWithFlags(&v->ev_int_done[i], cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&v->ev_pub_done[i], cudaEventDisableTiming));
@@ -328,8 +330,10 @@ static int ensure_slot(tsdf_vol* v, FrameSlot& s) {
   if (!s.d_raw) {
     CU_CHECK(cudaMalloc(&s.d_raw, px * 7 + 64));        // depth (<=4 B) + rgb (3 B) per pixel
     CU_CHECK(cudaMalloc(&s.d_frame, frame_alloc_bytes(v->cfg.im_h, v->cfg.im_w)));  // float4 per pixel (float when no colour) + tail
-    // tail = 0 from the start: preps that skip the memset rely on k_publish having cleared it
-    CU_CHECK(cudaMemset(frame_dmax_ptr(s.d_frame, px), 0, frame_tail_bytes(v->cfg.im_h, v->cfg.im_w)));
+    // tail = 0 from the start: preps that skip the memset rely on k_publish having cleared it.  Issued on
+    // the copy stream, where every prep into this slot runs (a plain cudaMemset would go to the legacy
+    // default stream, which the non-blocking copy stream is not ordered behind)
+    CU_CHECK(cudaMemsetAsync(frame_dmax_ptr(s.d_frame, px), 0, frame_tail_bytes(v->cfg.im_h, v->cfg.im_w), v->s_copy));
     CU_CHECK(cudaEventCreateWithFlags(&s.uploaded, cudaEventDisableTiming));
     CU_CHECK(cudaEventCreateWithFlags(&s.consumed, cudaEventDisableTiming));
     s.tmap_ok = encode_frame_tmap(v, s);
@@ -633,7 +637,9 @@ int submit_frames(tsdf_vol* v, FrameSlot** slots, const FrameP* fp, int nf, bool
   const int wi = (int)(v->lseq % kWrittenRing);
   // this launch adds into counter wi: the publish of the launch that last used it must have re-armed it
   if (v->lseq >= (uint64_t)kWrittenRing) CU_CHECK(cudaStreamWaitEvent(v->s_compute, v->ev_pub_done[wi], 0));
-  CU_CHECK(cudaEventRecord(k0, v->s_compute));
+  // a later submission of one tsdf_integrate_multi_async call keeps the call's first start event, so that
+  // tsdf_get_stats' last_kernel_ms spans the same k frames as its voxels_written / bytes_algorithmic
+  if (v->ktiming || !accumulate) CU_CHECK(cudaEventRecord(k0, v->s_compute));
   trace_mark(v, 2, v->s_compute);
   int rc = launch_integrate(v, fp, nf, color, v->s_compute);
   if (rc) return rc;

@@ -62,6 +62,9 @@ __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scal
         __threadfence_system();
       }
       timed_out = bad;
+      // a block that gives up still counts as arrived, so that the last-block detection of the tail stays
+      // armed for the next launch even when only SOME blocks of this one timed out; `done` is not raised
+      if (bad && sy.done_flag && atomicAdd(sy.arrive, 1u) == gridDim.x - 1) *sy.arrive = 0u;
     }
     __syncthreads();
     if (timed_out) return;   // block-uniform
@@ -136,7 +139,9 @@ __global__ void k_frame_prep(const void* __restrict__ depth, int fmt, float scal
           *reinterpret_cast<volatile int*>(sy.h_err) = 3;
         }
         __threadfence_system();
-        asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(sy.done_flag), "r"(sy.done_value));
+        // some blocks of this launch gave up on the wait: the frame is incomplete, the slot is not "consumed"
+        if (*reinterpret_cast<volatile int*>(sy.d_err) == 0)
+          asm volatile("st.volatile.global.u32 [%0], %1;" ::"l"(sy.done_flag), "r"(sy.done_value));
       }
     }
   }

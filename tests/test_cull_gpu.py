@@ -68,6 +68,14 @@ def test_cull_never_changes_results(pkg, oracle, synth, sem, color, dims):
     ft, fw, fc, _ = run_gpu(pkg, cfg, frames[:8], color, FORCE_CULL, fused=True)
     p8, t8, w8, c8, _ = oracle_run(oracle, dims, vs, origin, frames[:8], sem, color, max_depth=cfg.max_depth)
     assert_volume_equal(ft, fw, fc, t8, w8, c8)
+    # dense kernels forced: consecutive frames go through the two-frames-per-pass kernel (k_integrate2,
+    # launch_integrate pairs under variant 64), which here meets frustum edges, cameras facing away,
+    # holes and surfaces — frames its host-side "slab inside both frusta" test would never hand it
+    pt, pw, pc, _ = run_gpu(pkg, cfg, frames[:7], color, NO_CULL, fused=True)
+    p7, t7, w7, c7, _ = oracle_run(oracle, dims, vs, origin, frames[:7], sem, color, max_depth=cfg.max_depth)
+    assert_volume_equal(pt, pw, pc, t7, w7, c7)
+    if color:
+        assert np.array_equal(pc, c7)
 
 
 def test_depth_cull_wall_in_front(pkg, oracle, synth):
