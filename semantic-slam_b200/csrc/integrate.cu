@@ -22,7 +22,9 @@
 // Arithmetic: this file is compiled with -fmad=false; every fp32 operation below is a
 // single IEEE round-to-nearest op in the reference's source order,
 // so results are bit-identical to oracle/tsdf_oracle.c.
+#include <algorithm>
 #include <climits>
+#include <cmath>
 #include "common.cuh"
 #include "exactmath.cuh"
 
@@ -195,18 +197,27 @@ struct Proj { bool ok; int pix; int px, py; };   // (px, py: only the staged-til
 
 
 // KNOWN_SAFE: the caller has shown camz inside the exponent window (dense kernels: once per run).
-template <bool SELECT, bool KNOWN_SAFE = false>
+// INSIDE: the HOST has proved (slab_inside_with_margin: double-precision projection of the slab's 8 corners,
+// one pixel of margin, an fp32 error bound of a quarter pixel) that every voxel of the launch has camz in
+// the window and projects strictly inside the image, so the tests of :39 and :43 are true for every voxel
+// and are not evaluated: 4 compares, their combination and the pixel-index select leave the hot loop.
+template <bool SELECT, bool KNOWN_SAFE = false, bool INSIDE = false>
 __device__ __forceinline__ Proj project_exact(const FrameP& f, const GridP& g, float camx, float camy, float camz) {
-  const bool inr = KNOWN_SAFE || em::in_safe_range(camz); // implies camz > 0            :39
+  const bool inr = KNOWN_SAFE || INSIDE || em::in_safe_range(camz); // implies camz > 0            :39
   const float yz = em::rcp_rn(camz);
   const float u = f.fx * em::div_rn(camx, camz, yz) + f.cx;   // :41
   const float v = f.fy * em::div_rn(camy, camz, yz) + f.cy;   // :42
   // (int)roundf(u) in [0,W)  <=>  -0.5 < u < W-0.5   (roundf is half-away-from-zero)   :43
   Proj p;
-  p.ok = inr && u > -0.5f && u < g.w_lim && v > -0.5f && v < g.h_lim;
   const int px = em::round_half_away_nonneg_int(u);
   const int py = em::round_half_away_nonneg_int(v);
   p.px = px; p.py = py;
+  if constexpr (INSIDE) {
+    p.ok = true;
+    p.pix = py * g.W + px;
+    return p;
+  }
+  p.ok = inr && u > -0.5f && u < g.w_lim && v > -0.5f && v < g.h_lim;
   // select, not branch: the rounding of an out-of-image u/v is harmless, and a branch here
   // would sit between the four gathers of a run
   if constexpr (SELECT) {
@@ -375,6 +386,10 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
                                                int tpr_log2, int rows_per_block, int flags,
                                                const void* tmap = nullptr, float4* stage_tile = nullptr) {
   constexpr int NT = ZFAST ? 1 : 2;  // float4 per row per frame
+  // CULL: 0 dense (no segment cull, branch-free run), 3 dense + host-proved inside the image (project_exact
+  // INSIDE), 2 sparse (segment cull), 1 legacy one-piece probe (A/B)
+  constexpr bool kDense = CULL == 0 || CULL == 3;
+  constexpr bool kInside = CULL == 3;
   const GridP& g = P.g;
   const int pf = flags & 3;            // software prefetch: 0 off, 1 L2, 2 L1
   const int n_rows = g.n_mid * g.n_slow;
@@ -533,7 +548,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   // with box_is_skipped; one ballot per pass hands every lane the bit mask of its own
   // sequence.  No shared memory, no block barrier: warps start their rows independently.
   unsigned long long rowmask = 0ull;  // bit i: iteration i of this thread's row loop is culled
-  if constexpr (CULL != 0) {
+  if constexpr (!kDense) {
     const int tw_log2 = tpr_log2 < 5 ? tpr_log2 : 5;
     const int tw = 1 << tw_log2;                       // lanes per row group inside the warp
     const int lane = threadIdx.x & 31;
@@ -624,7 +639,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   float* pt = g.tsdf + off0;
   float* pw = g.weight + off0;
   float* pc = COLOR ? g.color + off0 : nullptr;
-  if (pf && live && row0 + tr < n_rows && !(CULL != 0 && (rowmask & 1ull))) {   // first row of the block
+  if (pf && live && row0 + tr < n_rows && !(!kDense && (rowmask & 1ull))) {   // first row of the block
     prefetch_line<CULL != 1>(pt, pf);
     prefetch_line<CULL != 1>(pw, pf);
     if constexpr (COLOR) prefetch_line<CULL != 1>(pc, pf);
@@ -632,7 +647,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
   for (int lr = tr; live && lr < rows_per_block; lr += rp, rowmask >>= 1, pt += step, pw += step, pc += COLOR ? step : 0) {
     const int r = row0 + lr;
     if (r >= n_rows) break;
-    if constexpr (CULL != 0) {
+    if constexpr (!kDense) {
       if ((threadIdx.x & 31) == 0) { DBG_ADD(2, 1); if (rowmask & 1ull) DBG_ADD(3, 1); }
       if (rowmask & 1ull) { any_prev = false; continue; }
     }
@@ -670,7 +685,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           any = any || hit[f][j].ok;
         }
       } else {
-        constexpr bool kEnds = kRunSafe && CULL == 0 && VEC == 4;
+        constexpr bool kEnds = kRunSafe && kDense && VEC == 4;
         bool odd = false;  // a positive camz outside the exponent window of the exact forms
         if constexpr (kEnds) {
           odd = !(em::in_safe_range(camz[0]) && em::in_safe_range(camz[VEC - 1]));   // (dense frames: never)
@@ -690,14 +705,14 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
           bool in_image = false;
 #pragma unroll
           for (int j = 0; j < VEC; ++j) {
-            pr[j] = project_exact<true, kEnds>(P.f[f], g, camx[j], camy[j], camz[j]);
+            pr[j] = project_exact<true, kEnds, kInside>(P.f[f], g, camx[j], camy[j], camz[j]);
             in_image = in_image || pr[j].ok;
           }
           // CULL == 2 (sparse frames): a run that projects outside the image stops before the
           // gather.  CULL == 0 (dense frames): no early-out, the run is branch-free from here, so
           // the four gathers issue back to back.
           if constexpr (CULL == 2) { DBG_ADD(4, 1); if (in_image) DBG_ADD(5, 1); }
-          if (CULL == 0 || in_image) {
+          if (kDense || in_image) {
 #pragma unroll
             for (int j = 0; j < VEC; ++j) {
               hit[f][j] = sample_exact<COLOR, LE_TRUNC, MASK>(P.f[f], g, mask, pr[j], camz[j], STAGE ? &stg : nullptr);
@@ -733,7 +748,7 @@ __device__ __forceinline__ void integrate_body(const LaunchP<NF>& P, const uint8
       // when diff >= trunc for the whole run, skip :57's when the stored tsdf is 1 as well — was built
       // and measured in round 2: 8 % SLOWER at full clocks, profiles/r2_v3_dense_update_ab.jsonl; the
       // kernel is HBM-bound and the extra control flow costs more than the arithmetic it saves.)
-      if constexpr (CULL == 0) {
+      if constexpr (kDense) {
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
           float nt = t[j], nw = w[j], nc = col[j];
@@ -1054,7 +1069,7 @@ k_integrate_staged(const __grid_constant__ LaunchP<1> P, const __grid_constant__
 // slower than NF passes: it keeps every frame's Hit live across the volume loads, 118-244
 // registers), a frame's probe results die in its own update, so the live set is one frame's.
 // ---------------------------------------------------------------------------------------
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE, bool INSIDE>
 __global__ void __launch_bounds__(kThreads, 3)
 k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_block, int flags) {
   constexpr int NT = ZFAST ? 1 : 2;
@@ -1135,7 +1150,7 @@ k_integrate2(const __grid_constant__ LaunchP<2> P, int tpr_log2, int rows_per_bl
       } else {
         Proj pr[VEC];
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true, kRunSafe>(P.f[f], g, camx[j], camy[j], camz[j]);
+        for (int j = 0; j < VEC; ++j) pr[j] = project_exact<true, kRunSafe, INSIDE>(P.f[f], g, camx[j], camy[j], camz[j]);
 #pragma unroll
         for (int j = 0; j < VEC; ++j) hit[j] = sample_exact<COLOR, LE_TRUNC, false>(P.f[f], g, nullptr, pr[j], camz[j]);
       }
@@ -1260,7 +1275,7 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   // sparse kernel: one warp per row segment (32 runs), 8 rows in parallel, so that a block is a
   // compact tile (128 rows x 128 voxels) the block-level hull test can reject as a whole
   Geometry q = plan(g.n_fast, g.n_mid * g.n_slow, VEC, 1, o.rows_mult, (o.kernel == 1 && o.compact) ? 32 : kThreads);
-  if (o.kernel == 0 && o.balance) {
+  if ((o.kernel == 0 || o.kernel == 3) && o.balance) {
     // resident blocks per SM of this instantiation (same on every B200); C++11 static
     // initialisation is thread-safe: handles may be driven from different host threads
     static const int occ = [] {
@@ -1297,8 +1312,15 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
       return TSDF_OK;
     }
   }
+  if constexpr (NF == 1 && VEC == 4 && MATH == MATH_EXACT) {
+    if (o.kernel == 3) {   // dense, and the host has shown every voxel strictly inside the image
+      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 3><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+      CU_LAUNCHED();
+      return TSDF_OK;
+    }
+  }
   if (o.kernel == 1)      k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 2><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf | (o.block_test ? 4 : 0));
-  else if (o.kernel == 0) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
+  else if (o.kernel == 0 || o.kernel == 3) k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 0><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
 #ifdef TSDF_B200_DEV
   else                  k_integrate<ZFAST, COLOR, LE_TRUNC, NF, VEC, MATH, WMODE, 1><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, pf);
 #endif
@@ -1306,8 +1328,8 @@ int launch_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStre
   return TSDF_OK;
 }
 
-template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
-int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE, bool INSIDE>
+int launch_pair_ti(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
   LaunchP<2> P;
   P.g = g;
   P.f[0] = frames[0];
@@ -1316,14 +1338,19 @@ int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cud
   if (o.balance) {
     static const int occ = [] {
       int n = 0;
-      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE>, kThreads, 0) != cudaSuccess) n = 0;
+      if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE, INSIDE>, kThreads, 0) != cudaSuccess) n = 0;
       return n;
     }();
     balance_waves(&q, g.n_mid * g.n_slow, occ * device_sm_count());
   }
-  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, o.prefetch ? 1 : 0);
+  k_integrate2<ZFAST, COLOR, LE_TRUNC, WMODE, INSIDE><<<q.grid, kThreads, 0, st>>>(P, q.tpr_log2, q.rows_per_block, o.prefetch ? 1 : 0);
   CU_LAUNCHED();
   return TSDF_OK;
+}
+template <bool ZFAST, bool COLOR, bool LE_TRUNC, int WMODE>
+int launch_pair_t(const GridP& g, const FrameP* frames, const LaunchOpts& o, cudaStream_t st) {
+  return o.kernel == 3 ? launch_pair_ti<ZFAST, COLOR, LE_TRUNC, WMODE, true>(g, frames, o, st)
+                       : launch_pair_ti<ZFAST, COLOR, LE_TRUNC, WMODE, false>(g, frames, o, st);
 }
 
 int launch_pair(bool zfast, bool color, int wmode, const GridP& g, const FrameP* fr, const LaunchOpts& o, cudaStream_t st) {
@@ -1397,6 +1424,40 @@ static bool slab_inside_every_frustum(const GridP& g, const FrameP* fr, int nf) 
   return true;
 }
 
+// The stronger statement the INSIDE kernels need: the test above (all 8 corners at least one pixel inside the
+// image, in double precision; slab and frustum are convex, and "u >= a, z > 0" is a half-space, so every voxel is
+// inside in exact arithmetic) AND the fp32 error of the kernel's own u / v stays below a quarter pixel, so the
+// COMPUTED u, v lie in [0.25, W - 1.25] x [0.25, H - 1.25]: :39 and :43 hold for every voxel, the rounded pixel
+// is inside the image.  Error model: a camera coordinate is a sum of three products of a rotation entry
+// (|c| <= ~1) and a difference "origin + index * vs - translation", about 12 roundings of quantities bounded by
+// M = |origin| + extent + |translation| (1-norms): |err| <= 12 * 2^-24 * M < 7.2e-7 M; E = 1.5e-6 M doubles it.
+// u = fx * (x / z) + cx then moves by at most fx * E * (1 + |x/z|) / z_min plus three roundings of values
+// below max(W, H) (< 3e-4 px), and |x/z| <= max(W, H) / min(fx, fy) inside the image.
+static bool slab_inside_with_margin(const GridP& g, const FrameP* fr, int nf) {
+  if (!slab_inside_every_frustum(g, fr, nf)) return false;
+  for (int f = 0; f < nf; ++f) {
+    const float* c = fr[f].c;
+    double rot = 0.0;
+    for (int i = 0; i < 12; ++i) if ((i & 3) != 3) rot = std::max(rot, (double)fabsf(c[i]));
+    if (!(rot <= 1.0001)) return false;   // not a rotation (a scaled base pose): keep the tested kernel
+    const double ext = ((double)g.nx_ + g.n_mid + g.z0 + g.nz_) * g.vs;
+    const double M = fabs((double)g.ox) + fabs((double)g.oy) + fabs((double)g.oz) + ext + fabs((double)c[3]) + fabs((double)c[7]) + fabs((double)c[11]);
+    double zmin = 1e300;
+    for (int corner = 0; corner < 8; ++corner) {
+      const int ix = (corner & 1) ? g.nx_ - 1 : 0, iy = (corner & 2) ? g.n_mid - 1 : 0, iz = g.z0 + ((corner & 4) ? g.nz_ - 1 : 0);
+      const double t0 = ((double)g.ox + (double)ix * g.vs) - c[3], t1 = ((double)g.oy + (double)iy * g.vs) - c[7],
+                   t2 = ((double)g.oz + (double)iz * g.vs) - c[11];
+      zmin = std::min(zmin, c[2] * t0 + c[6] * t1 + c[10] * t2);
+    }
+    const double fmax = std::max(fabs((double)fr[f].fx), fabs((double)fr[f].fy)), fmin = std::min(fabs((double)fr[f].fx), fabs((double)fr[f].fy));
+    if (!(zmin >= 1e-3 && zmin < 1e12 && fmin > 0.0 && M < 1e12)) return false;
+    const double E = 1.5e-6 * M;
+    const double du = fmax * E * (1.0 + std::max(g.W, g.H) / fmin) / zmin + 1e-3;
+    if (!(du < 0.25)) return false;
+  }
+  return true;
+}
+
 int launch_publish(tsdf_vol* v, bool accumulate, cudaStream_t st, void* d_frame_to_clear) {
   int* tail = d_frame_to_clear ? reinterpret_cast<int*>(frame_dmax_ptr(d_frame_to_clear, frame_pixels(v->cfg))) : nullptr;
   const int words = tail ? (int)(frame_tail_bytes(v->cfg.im_h, v->cfg.im_w) / 4) : 0;
@@ -1436,12 +1497,16 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
   // form of integrate_body (every frame's probe results live across the volume loads) was measured
   // slower than NF passes in round 1 — 4.1-5.7 ms per frame against 3.9 — and is not instantiated.
   const bool pairs_ok = vec4 && !literal && (v->variant & (1 << 14)) == 0 && o.kernel != 2;
+  // bit15: keep the image-bounds tests in the dense kernels even where the host can prove them true (A/B)
+  const bool inside_ok = vec4 && !literal && (v->variant & ((1 << 15) | 64 | 128 | 1024)) == 0;
   for (int i = 0; i < nf;) {
     int rc;
     // (variant bit 6 forces the dense kernels whatever the geometry, bit 7 the sparse one, bit 14 no pairs)
     if (pairs_ok && i + 1 < nf && !(v->variant & 128) &&
         ((v->variant & 64) || slab_inside_every_frustum(g, frames + i, 2))) {
-      rc = launch_pair(v->zfast, color, wmode, g, frames + i, o, st);
+      LaunchOpts o2 = o;
+      o2.kernel = (inside_ok && slab_inside_with_margin(g, frames + i, 2)) ? 3 : 0;
+      rc = launch_pair(v->zfast, color, wmode, g, frames + i, o2, st);
       if (rc) return rc;
       i += 2;
       continue;
@@ -1449,6 +1514,7 @@ int launch_integrate(tsdf_vol* v, const FrameP* frames, int nf, bool color, cuda
     LaunchOpts o1 = o;
     o1.tmap = (v->variant & (1 << 20)) ? frames[i].h_tmap : nullptr;   // bit20: staged image tile (A/B)
     if (!(v->variant & (64 | 128 | 1024))) o1.kernel = slab_inside_every_frustum(g, frames + i, 1) ? 0 : 1;
+    if (o1.kernel == 0 && inside_ok && slab_inside_with_margin(g, frames + i, 1)) o1.kernel = 3;
 #ifdef TSDF_B200_DEV
     if (literal) rc = vec4 ? launch_sem<1, 4, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st)
                            : launch_sem<1, 1, MATH_LITERAL>(v->zfast, color, 0, g, frames + i, o1, st);

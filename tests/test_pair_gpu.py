@@ -123,3 +123,26 @@ def test_bench_workload_slab_vs_oracle(pkg, omp, synth):
         assert vol.stats().voxels_written == n12
         assert 0.9 * vol.n_local < n0 < vol.n_local          # dense, but the sphere's inside/shadow is skipped
         compare(vol, t, w, c)
+
+
+def test_inside_kernels_equal_bounds_checked_kernels(pkg, omp, synth, dense_scene, dev_lib):
+    """When the host proves that every voxel projects strictly inside the image (slab_inside_with_margin,
+    csrc/integrate.cu) the dense kernels drop the image-bounds tests of src/tsdf.cu:39,43 (CULL = 3 /
+    k_integrate2<INSIDE>).  Variant bit 15 keeps the tests: both forms must give the same bits, single
+    launches and pairs, and equal the oracle."""
+    dims, vs, origin, frames = dense_scene
+    cfg = pkg.make_config(dims, vs, origin, semantics=SEM_FUSIONPY, with_color=True)
+    p = omp.params(dims, vs, cfg.trunc_margin, origin, synth.TUM3_HW, synth.TUM3_K, np.inf, SEM_FUSIONPY)
+    t, w, c = omp.new_volume(p, True)
+    for d, rgb, T in frames[:5]:
+        omp.integrate(p, T.reshape(16), d, omp.pack_color(rgb), 1.0, t, w, c)
+    out = {}
+    for variant in (0, 1 << 15):
+        with pkg.Volume(cfg) as vol:
+            vol.set_variant(variant)
+            vol.integrate(*frames[0][:2], frames[0][2])                                    # single launch
+            vol.integrate_multi([f[0] for f in frames[1:5]], [f[1] for f in frames[1:5]], [f[2] for f in frames[1:5]])  # two pairs
+            compare(vol, t, w, c)
+            out[variant] = vol.download()
+    for a, b in zip(out[0], out[1 << 15]):
+        assert np.array_equal(bits(a), bits(b))
