@@ -485,7 +485,7 @@ def run_b200(args, rank, world, local_rank):
                                      "timed window of --steps steps",
                 "roofline": {"bound": "hbm", "kernel": "k_integrate<ZFAST,COLOR,NF=1,VEC=4>", "achieved": achieved,
                              "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(world),
-                             "traffic_source": "committed ncu capture (profiles/traffic.json, S-full without the sphere), "
+                             "traffic_source": "committed ncu capture (profiles/traffic.json: the bench workload, round 3), "
                                                "NOT measured in this run",
                              "peak_source": peak_src, "kernel_ms": k_ms, "launches_timed": kn,
                              "algorithmic_bytes_per_launch": alg_bytes,

@@ -159,6 +159,9 @@ def share_of_active(local, active, boxes=None, crops=None, masks=None):
     rank's batch}.  Returns (local indices, boxes, concatenated crops, full masks) of the active
     instances this rank owns, in the order of `active`."""
     keep = [k for k, g in enumerate(active) if g in local]
+    if len(keep) == len(active) and boxes is not None and masks is None:   # this rank owns them all: nothing to cut
+        return (np.array([local[g] for g in active], np.int32), np.ascontiguousarray(boxes, np.int32).reshape(-1, 4),
+                np.ascontiguousarray(crops, np.uint8), None)
     loc = np.array([local[active[k]] for k in keep], np.int32)
     bx = cr = mk = None
     if boxes is not None:
